@@ -1,0 +1,9 @@
+"""centerpoly_b200 — B200 (sm_100a) implementation of CenterPoly v2's data-parallel hot path:
+the DCNv2 modulated deformable convolution of the DLA-34 neck (forward + backward) and the fused
+``polydet_decode``.  Host code is Python/PyTorch for memory and streams only; the arithmetic lives in
+``libcpoly.so`` (hand-written CUDA behind the C ABI of ``include/cpoly.h``).
+"""
+from .dcn_v2 import DCN, DCNv2, _DCNv2, dcn_v2_conv, set_dcn_path  # noqa: F401
+from .decode import polydet_decode, polydet_decode_from_logits  # noqa: F401
+
+__version__ = "0.1.0"

@@ -1,0 +1,130 @@
+"""ctypes binding of libcpoly.so (the C ABI declared in include/cpoly.h).
+
+There is deliberately NO fallback: if the shared library is missing or a call fails, we raise.
+torch is used only for device memory, streams and dtypes.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcpoly.so")
+
+F32, BF16 = 0, 1
+REP = {"cartesian": 0, "polar": 1, "polar_fixed": 2}
+PATH_AUTO, PATH_SIMT, PATH_TCGEN05 = 0, 1, 2
+
+EXPORTED_SYMBOLS = (
+    "cpoly_abi_version", "cpoly_last_error", "cpoly_device_supports_tcgen05", "cpoly_dcn_tcgen05_eligible",
+    "cpoly_dcn_packed_weight_bytes", "cpoly_dcn_pack_weights", "cpoly_dcn_forward",
+    "cpoly_dcn_backward_workspace_bytes", "cpoly_dcn_backward", "cpoly_decode_workspace_bytes", "cpoly_decode",
+)
+
+
+class Tensor4(Structure):
+    _fields_ = [("ptr", c_void_p), ("sb", c_int64), ("sc", c_int64), ("sh", c_int64), ("sw", c_int64)]
+
+
+class DcnFwdArgs(Structure):
+    _fields_ = [(n, c_int32) for n in (
+        "B", "Cin", "Cout", "H", "W", "kh", "kw", "stride_h", "stride_w", "pad_h", "pad_w", "dil_h", "dil_w",
+        "deformable_groups", "dtype", "om_dtype", "mask_is_logit", "path")] + [
+        ("x", Tensor4), ("offset", Tensor4), ("mask", Tensor4),
+        ("weight", c_void_p), ("bias", c_void_p), ("weight_packed", c_void_p), ("y", Tensor4)]
+
+
+class DcnBwdArgs(Structure):
+    _fields_ = [("f", DcnFwdArgs), ("gout", Tensor4), ("gx", Tensor4), ("goffset", Tensor4), ("gmask", Tensor4),
+                ("gweight", c_void_p), ("gbias", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+
+
+class DecodeArgs(Structure):
+    _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "n_poly", "K", "rep", "heat_is_logit", "dtype")] + [
+        ("heat", Tensor4), ("polys", Tensor4), ("depth", Tensor4), ("reg", Tensor4),
+        ("out", c_void_p), ("out_inds", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+
+
+_lib = None
+
+
+def lib():
+    """The loaded library; raises (loudly) when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m centerpoly_b200.build` "
+                "(centerpoly_b200 has no CPU or PyTorch fallback by design)")
+        L = ctypes.CDLL(LIB_PATH)
+        L.cpoly_abi_version.restype = c_int32
+        L.cpoly_last_error.restype = c_char_p
+        L.cpoly_device_supports_tcgen05.restype = c_int32
+        L.cpoly_dcn_tcgen05_eligible.restype = c_int32
+        L.cpoly_dcn_tcgen05_eligible.argtypes = [POINTER(DcnFwdArgs)]
+        L.cpoly_dcn_packed_weight_bytes.restype = c_size_t
+        L.cpoly_dcn_packed_weight_bytes.argtypes = [c_int32] * 5
+        L.cpoly_dcn_pack_weights.restype = c_int32
+        L.cpoly_dcn_pack_weights.argtypes = [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p]
+        L.cpoly_dcn_forward.restype = c_int32
+        L.cpoly_dcn_forward.argtypes = [POINTER(DcnFwdArgs), c_void_p]
+        L.cpoly_dcn_backward_workspace_bytes.restype = c_size_t
+        L.cpoly_dcn_backward_workspace_bytes.argtypes = [POINTER(DcnBwdArgs)]
+        L.cpoly_dcn_backward.restype = c_int32
+        L.cpoly_dcn_backward.argtypes = [POINTER(DcnBwdArgs), c_void_p]
+        L.cpoly_decode_workspace_bytes.restype = c_size_t
+        L.cpoly_decode_workspace_bytes.argtypes = [c_int32] * 5
+        L.cpoly_decode.restype = c_int32
+        L.cpoly_decode.argtypes = [POINTER(DecodeArgs), c_void_p]
+        if L.cpoly_abi_version() != 1:
+            raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
+        _lib = L
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().cpoly_last_error()
+        raise RuntimeError(f"{what} failed (code {rc}): {msg.decode() if msg else '?'}")
+
+
+def dtype_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise RuntimeError(f"centerpoly_b200 supports float32 and bfloat16 tensors, got {t.dtype}")
+
+
+def t4(t: torch.Tensor | None) -> Tensor4:
+    """Base pointer + element strides of a 4-d tensor (any memory format)."""
+    if t is None:
+        return Tensor4(None, 0, 0, 0, 0)
+    assert t.dim() == 4
+    sb, sc, sh, sw = t.stride()
+    return Tensor4(t.data_ptr(), sb, sc, sh, sw)
+
+
+def require_cuda(*tensors) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("centerpoly_b200 runs on CUDA (B200) tensors only; there is no CPU path")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError(f"tensors on different devices: {dev} vs {t.device}")
+    return dev
+
+
+def stream_ptr(dev: torch.device) -> c_void_p:
+    return c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def workspace(nbytes: int, dev: torch.device) -> torch.Tensor:
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)

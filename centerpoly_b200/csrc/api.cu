@@ -1,0 +1,112 @@
+// extern "C" surface of libcpoly.so — see include/cpoly.h for the contract and the reference
+// interfaces each entry point replaces.
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace cpoly {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+static int validate_dcn(const cpoly_dcn_fwd_args& a, bool need_y) {
+  CPOLY_REQUIRE(a.B >= 0 && a.Cin > 0 && a.Cout > 0 && a.H > 0 && a.W > 0, CPOLY_EINVAL, "bad tensor dims");
+  CPOLY_REQUIRE(a.kh > 0 && a.kw > 0 && a.stride_h > 0 && a.stride_w > 0 && a.dil_h > 0 && a.dil_w > 0 &&
+                    a.pad_h >= 0 && a.pad_w >= 0, CPOLY_EINVAL, "bad convolution geometry");
+  CPOLY_REQUIRE(a.deformable_groups > 0 && a.Cin % a.deformable_groups == 0, CPOLY_EINVAL,
+                "in_channels (%d) must be divisible by deformable_groups (%d)", a.Cin, a.deformable_groups);
+  CPOLY_REQUIRE(a.dtype == CPOLY_F32 || a.dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", a.dtype);
+  CPOLY_REQUIRE(a.om_dtype == CPOLY_F32 || a.om_dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported offset/mask dtype %d", a.om_dtype);
+  CPOLY_REQUIRE(a.x.ptr && a.offset.ptr && a.mask.ptr && a.weight, CPOLY_EINVAL, "NULL input pointer");
+  CPOLY_REQUIRE(!need_y || a.y.ptr, CPOLY_EINVAL, "NULL output pointer");
+  const DcnGeom g = make_geom(a);
+  CPOLY_REQUIRE(g.Ho > 0 && g.Wo > 0, CPOLY_EINVAL, "empty output (%d x %d)", g.Ho, g.Wo);
+  return CPOLY_OK;
+}
+
+}  // namespace cpoly
+
+using namespace cpoly;
+
+extern "C" {
+
+int cpoly_abi_version(void) { return CPOLY_ABI_VERSION; }
+
+const char* cpoly_last_error(void) { return g_error; }
+
+int cpoly_device_supports_tcgen05(void) {
+  int dev = 0, major = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return -1;
+  return major == 10 ? 1 : 0;
+}
+
+int cpoly_dcn_tcgen05_eligible(const cpoly_dcn_fwd_args* args) {
+  if (!args) return 0;
+  return dcn_tc_eligible(*args) ? 1 : 0;
+}
+
+size_t cpoly_dcn_packed_weight_bytes(int32_t Cin, int32_t Cout, int32_t kh, int32_t kw, int32_t dtype) {
+  return dcn_tc_packed_bytes(Cin, Cout, kh, kw, dtype);
+}
+
+int cpoly_dcn_pack_weights(const float* weight, void* packed, int32_t Cin, int32_t Cout, int32_t kh, int32_t kw,
+                           int32_t dtype, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(weight && packed, CPOLY_EINVAL, "NULL pointer");
+  CPOLY_REQUIRE(dcn_tc_packed_bytes(Cin, Cout, kh, kw, dtype) > 0, CPOLY_EUNSUPPORTED,
+                "shape Cin=%d Cout=%d k=%dx%d dtype=%d has no packed layout", Cin, Cout, kh, kw, dtype);
+  return dcn_tc_pack_weights(weight, packed, Cin, Cout, kh, kw, dtype, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int cpoly_dcn_forward(const cpoly_dcn_fwd_args* args, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(args, CPOLY_EINVAL, "NULL args");
+  if (int rc = validate_dcn(*args, true)) return rc;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const bool tc_ok = args->weight_packed && dcn_tc_eligible(*args);
+  if (args->path == CPOLY_PATH_TCGEN05) {
+    CPOLY_REQUIRE(tc_ok, CPOLY_EUNSUPPORTED, "tcgen05 path requested but the problem does not qualify (see cpoly_dcn_tcgen05_eligible)");
+    return dcn_forward_tc(*args, s);
+  }
+  if (args->path == CPOLY_PATH_AUTO && tc_ok) return dcn_forward_tc(*args, s);
+  return dcn_forward_simt(*args, s);
+}
+
+size_t cpoly_dcn_backward_workspace_bytes(const cpoly_dcn_bwd_args* args) {
+  if (!args) return 0;
+  return dcn_backward_simt_workspace(*args);
+}
+
+int cpoly_dcn_backward(const cpoly_dcn_bwd_args* args, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(args, CPOLY_EINVAL, "NULL args");
+  if (int rc = validate_dcn(args->f, false)) return rc;
+  CPOLY_REQUIRE(args->gout.ptr, CPOLY_EINVAL, "NULL grad_output");
+  return dcn_backward_simt(*args, reinterpret_cast<cudaStream_t>(stream));
+}
+
+size_t cpoly_decode_workspace_bytes(int32_t B, int32_t C, int32_t H, int32_t W, int32_t K) {
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || K <= 0) return 256;
+  return decode_workspace_bytes(B, C, H, W, K);
+}
+
+int cpoly_decode(const cpoly_decode_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->C > 0 && a->H > 0 && a->W > 0, CPOLY_EINVAL, "bad heat dims");
+  CPOLY_REQUIRE(a->n_poly > 0 && a->n_poly % 2 == 0, CPOLY_EINVAL, "poly head must have an even channel count, got %d", a->n_poly);
+  CPOLY_REQUIRE(a->K >= 1 && a->K <= 1024, CPOLY_EINVAL, "K must be in [1, 1024], got %d", a->K);
+  CPOLY_REQUIRE((int64_t)a->K <= (int64_t)a->H * a->W, CPOLY_EINVAL,
+                "K (%d) exceeds H*W (%d): the reference's per-class torch.topk would raise", a->K, a->H * a->W);
+  CPOLY_REQUIRE((int64_t)a->C * a->H * a->W < 0xffffffffLL, CPOLY_EINVAL, "C*H*W must fit in 32 bits");
+  CPOLY_REQUIRE(a->rep >= CPOLY_REP_CARTESIAN && a->rep <= CPOLY_REP_POLAR_FIXED, CPOLY_EINVAL, "bad rep %d", a->rep);
+  CPOLY_REQUIRE(a->dtype == CPOLY_F32 || a->dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", a->dtype);
+  CPOLY_REQUIRE(a->heat.ptr && a->polys.ptr && a->depth.ptr && a->out, CPOLY_EINVAL, "NULL pointer");
+  if (a->B == 0) return CPOLY_OK;
+  return decode_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

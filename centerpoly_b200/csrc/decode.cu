@@ -1,0 +1,456 @@
+// Fused polydet decode: [sigmoid] -> 3x3 max-pool NMS -> per-image top-K -> gather of the reg /
+// poly / pseudo-depth heads -> [polar -> cartesian] -> centre add -> bbox -> (B,K,2N+7), ONE launch.
+//
+// Replaces (reference paths): _nms decode.py:13-19, _topk decode.py:117-133,
+// _transpose_and_gather_feat models/utils.py:22-26, polydet_decode decode.py:512-670 and optionally
+// hm.sigmoid_() detectors/polydet.py:28.  The reference runs ~25 ATen kernels and transposes the whole
+// 64-channel poly map (33.5 MB at 2048x1024) to fetch K x 64 values; here the heat map is read once
+// and only K x (2N+3) head values are gathered.
+//
+// Structure (no inter-CTA waiting, so a single ordinary launch is safe):
+//   scan phase   every warp owns a 128-column band x RH rows of one (image, class) plane; rows roll
+//                through registers (vertical 3-max), the horizontal 3-max uses warp shuffles; a pixel is
+//                a peak iff it equals its 3x3 max (plateaus keep every member, like `hmax == heat`).
+//                Peaks are pushed as 64-bit keys (ordered score << 32 | ~flat_index) into a shared-memory
+//                list that is pruned by a block-level radix select whenever it could overflow; after the
+//                first prune the running K-th best key is a threshold that rejects most peaks at once.
+//   merge phase  each CTA publishes <= K keys; the last CTA of an image to finish (atomic ticket)
+//                radix-selects the global top-K, bitonic-sorts them (score desc, flat index asc — the
+//                oracle's tie rule), and runs the gather epilogue.
+//
+// The two-stage top-K of the reference (per class, then over C*K) equals the global top-K over
+// (class, y, x) whenever scores are tie-free; heat must be non-negative (it is post-sigmoid).
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace cpoly {
+namespace {
+
+constexpr int DNT = 256;           // threads per CTA
+constexpr int DWARPS = DNT / 32;
+constexpr int KMAX = 1024;         // largest supported K
+constexpr int BAND = 128;          // columns per warp (4 per lane)
+constexpr int ROUND_ROWS = 2;      // rows every warp scans between two block-level checks
+constexpr int ROUND_MAX = DWARPS * BAND * ROUND_ROWS;  // most keys a round can add
+constexpr int CAP = KMAX + ROUND_MAX;                  // shared list capacity
+
+struct DecodeParams {
+  int B, C, H, W, n_poly, K, rep, heat_is_logit, dtype;
+  cpoly_tensor4 heat, polys, depth, reg;
+  float* out;
+  int64_t* out_inds;
+  unsigned long long* cand;  // [B][ctas_per_image][K]
+  int* cand_count;           // [B][ctas_per_image]
+  unsigned int* done;        // [B]
+  int rh;                    // rows per warp work item
+  int nbands, nrowchunks, items_per_image, ctas_per_image;
+};
+
+__device__ __forceinline__ unsigned int float_to_ordered(float f) {
+  const unsigned int u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ordered_to_float(unsigned int o) {
+  return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
+}
+__device__ __forceinline__ unsigned long long make_key(float score, unsigned int flat) {
+  return ((unsigned long long)float_to_ordered(score) << 32) | (unsigned long long)(0xffffffffu - flat);
+}
+
+struct SelectScratch {
+  unsigned int hist[256];
+  unsigned long long outbuf[KMAX];
+  int out_count;
+  int digit;
+  int kth;
+};
+
+// Keeps the K largest keys of list[0..n) (keys are unique) in list[0..K), unsorted.  All DNT threads
+// must call it.  Returns the smallest kept key.
+__device__ unsigned long long block_select_topk(unsigned long long* list, int n, int K, SelectScratch& s) {
+  const int tid = threadIdx.x;
+  unsigned long long prefix = 0ull, mask = 0ull;
+  int kth = K;
+  for (int pass = 7; pass >= 0; --pass) {
+    const int shift = pass * 8;
+    s.hist[tid & 255] = 0;  // DNT == 256
+    __syncthreads();
+    for (int i = tid; i < n; i += DNT) {
+      const unsigned long long key = list[i];
+      if ((key & mask) == prefix) atomicAdd(&s.hist[(unsigned int)(key >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (tid < 32) {
+      // lane l owns digits 255-8l .. 248-8l (descending); find where the running count reaches kth
+      unsigned int mine[8], lane_sum = 0;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) { mine[q] = s.hist[255 - 8 * tid - q]; lane_sum += mine[q]; }
+      unsigned int incl = lane_sum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (tid >= d) incl += t;
+      }
+      const unsigned int excl = incl - lane_sum;
+      if (excl < (unsigned)kth && incl >= (unsigned)kth) {
+        unsigned int run = excl;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (run + mine[q] >= (unsigned)kth) { s.digit = 255 - 8 * tid - q; s.kth = kth - (int)run; break; }
+          run += mine[q];
+        }
+      }
+    }
+    __syncthreads();
+    const int digit = s.digit;
+    const unsigned int in_bucket = s.hist[digit];
+    kth = s.kth;
+    prefix |= (unsigned long long)digit << shift;
+    mask |= 0xffull << shift;
+    __syncthreads();
+    if ((int)in_bucket == kth) break;  // the whole bucket is taken: (key & mask) >= prefix selects exactly K
+  }
+  if (tid == 0) s.out_count = 0;
+  __syncthreads();
+  for (int i = tid; i < n; i += DNT) {
+    const unsigned long long key = list[i];
+    if ((key & mask) >= prefix) {
+      const int pos = atomicAdd(&s.out_count, 1);
+      if (pos < KMAX) s.outbuf[pos] = key;
+    }
+  }
+  __syncthreads();
+  unsigned long long lo = ~0ull;
+  for (int i = tid; i < K; i += DNT) {
+    const unsigned long long key = s.outbuf[i];
+    list[i] = key;
+    lo = key < lo ? key : lo;
+  }
+  // block-wide min of the kept keys
+  __shared__ unsigned long long red[DWARPS];
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) {
+    const unsigned long long o = __shfl_xor_sync(0xffffffffu, lo, d);
+    lo = o < lo ? o : lo;
+  }
+  if ((tid & 31) == 0) red[tid >> 5] = lo;
+  __syncthreads();
+  lo = red[0];
+#pragma unroll
+  for (int w = 1; w < DWARPS; ++w) lo = red[w] < lo ? red[w] : lo;
+  __syncthreads();
+  return lo;
+}
+
+template <typename T>
+__device__ __forceinline__ float load_heat(const T* p, bool logit) {
+  float v = ld_as_float(p);
+  return logit ? sigmoidf_accurate(v) : v;
+}
+
+// Row `y` of a band as 4 values per lane plus the two halo columns; out-of-image -> -inf.
+template <typename T>
+__device__ __forceinline__ void load_row(const T* plane, int64_t sh, int64_t sw, int y, int H, int W, int x0, int lane,
+                                         bool logit, float v[4], float& left, float& right) {
+  const float NEG = -CUDART_INF_F;
+  const int xb = x0 + lane * 4;
+  if (y < 0 || y >= H) {
+    v[0] = v[1] = v[2] = v[3] = NEG; left = right = NEG;
+    return;
+  }
+  const T* row = plane + (int64_t)y * sh;
+  if (sizeof(T) == 4 && sw == 1 && xb + 3 < W && ((reinterpret_cast<uintptr_t>(row + xb) & 15) == 0)) {
+    const float4 q = __ldg(reinterpret_cast<const float4*>(row + xb));
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+    if (logit) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = sigmoidf_accurate(v[j]);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = (xb + j < W) ? load_heat(row + (int64_t)(xb + j) * sw, logit) : NEG;
+  }
+  // neighbours inside the band come from the adjacent lanes; the band edges are loaded
+  left = __shfl_up_sync(0xffffffffu, v[3], 1);
+  right = __shfl_down_sync(0xffffffffu, v[0], 1);
+  if (lane == 0) left = (x0 > 0) ? load_heat(row + (int64_t)(x0 - 1) * sw, logit) : NEG;
+  if (lane == 31) right = (x0 + BAND < W) ? load_heat(row + (int64_t)(x0 + BAND) * sw, logit) : NEG;
+}
+
+__device__ __forceinline__ void hmax3(const float v[4], float left, float right, float h[4]) {
+  h[0] = fmaxf(fmaxf(left, v[0]), v[1]);
+  h[1] = fmaxf(fmaxf(v[0], v[1]), v[2]);
+  h[2] = fmaxf(fmaxf(v[1], v[2]), v[3]);
+  h[3] = fmaxf(fmaxf(v[2], v[3]), right);
+}
+
+template <typename T>
+__device__ __forceinline__ float head_value(const cpoly_tensor4& t, int b, int ch, int y, int x) {
+  return ld_as_float(reinterpret_cast<const T*>(t.ptr) + (int64_t)b * t.sb + (int64_t)ch * t.sc + (int64_t)y * t.sh +
+                     (int64_t)x * t.sw);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(DNT) decode_kernel(DecodeParams p) {
+  __shared__ unsigned long long list[CAP];
+  __shared__ SelectScratch scratch;
+  __shared__ int s_count;
+  __shared__ int s_is_last;
+  __shared__ unsigned char s_taken[KMAX];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int b = blockIdx.y;
+  const int K = p.K;
+  const int HW = p.H * p.W;
+  const bool logit = p.heat_is_logit != 0;
+
+  if (tid == 0) s_count = 0;
+  __syncthreads();
+
+  // ------------------------------------------------------------------ scan phase
+  const int item = blockIdx.x * DWARPS + warp;
+  const bool active = item < p.items_per_image;
+  int c = 0, r0 = 0, x0 = 0;
+  if (active) {
+    int t = item;
+    const int band = t % p.nbands; t /= p.nbands;
+    const int rc = t % p.nrowchunks;
+    c = t / p.nrowchunks;
+    r0 = rc * p.rh;
+    x0 = band * BAND;
+  }
+  const T* plane = reinterpret_cast<const T*>(p.heat.ptr) + (int64_t)b * p.heat.sb + (int64_t)c * p.heat.sc;
+  unsigned long long threshold = 0ull;  // keys <= threshold cannot enter the top-K any more
+
+  float v_cur[4], h_prev[4], h_cur[4];
+  {
+    float l, r, v[4];
+    if (active) {
+      load_row(plane, p.heat.sh, p.heat.sw, r0 - 1, p.H, p.W, x0, lane, logit, v, l, r);
+      hmax3(v, l, r, h_prev);
+      load_row(plane, p.heat.sh, p.heat.sw, r0, p.H, p.W, x0, lane, logit, v_cur, l, r);
+      hmax3(v_cur, l, r, h_cur);
+    }
+  }
+  for (int rr = 0; rr < p.rh; rr += ROUND_ROWS) {
+    if (active) {
+#pragma unroll
+      for (int q = 0; q < ROUND_ROWS; ++q) {
+        const int y = r0 + rr + q;
+        float v_next[4], h_next[4], l, r;
+        load_row(plane, p.heat.sh, p.heat.sw, y + 1, p.H, p.W, x0, lane, logit, v_next, l, r);
+        hmax3(v_next, l, r, h_next);
+        if (y < p.H) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float m = fmaxf(fmaxf(h_prev[j], h_cur[j]), h_next[j]);
+            const int x = x0 + lane * 4 + j;
+            if (x < p.W && v_cur[j] == m && v_cur[j] > 0.f) {
+              const unsigned long long key = make_key(v_cur[j], (unsigned int)(c * HW + y * p.W + x));
+              if (key > threshold) {
+                const int pos = atomicAdd(&s_count, 1);
+                if (pos < CAP) list[pos] = key;  // cannot overflow: a prune precedes any round that could
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { h_prev[j] = h_cur[j]; h_cur[j] = h_next[j]; v_cur[j] = v_next[j]; }
+      }
+    }
+    __syncthreads();
+    const int n = s_count;
+    if (n > CAP - ROUND_MAX) {  // uniform branch
+      threshold = block_select_topk(list, n, K, scratch);
+      if (tid == 0) s_count = K;
+      __syncthreads();
+    }
+  }
+  {
+    const int n = s_count;
+    if (n > K) {
+      block_select_topk(list, n, K, scratch);
+      if (tid == 0) s_count = K;
+      __syncthreads();
+    }
+  }
+  // ------------------------------------------------------------------ publish + ticket
+  const int my_count = s_count;
+  unsigned long long* my_cand = p.cand + ((int64_t)b * p.ctas_per_image + blockIdx.x) * K;
+  for (int i = tid; i < my_count; i += DNT) my_cand[i] = list[i];
+  if (tid == 0) p.cand_count[b * p.ctas_per_image + blockIdx.x] = my_count;
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned int ticket = atomicAdd(&p.done[b], 1u);
+    s_is_last = (ticket == (unsigned int)p.ctas_per_image - 1u);
+  }
+  __syncthreads();
+  if (!s_is_last) return;
+  __threadfence();
+
+  // ------------------------------------------------------------------ merge phase (one CTA per image)
+  if (tid == 0) s_count = 0;
+  __syncthreads();
+  int n = 0;
+  for (int j = 0; j < p.ctas_per_image; ++j) {
+    const int cnt = __ldcg(p.cand_count + b * p.ctas_per_image + j);
+    const unsigned long long* src = p.cand + ((int64_t)b * p.ctas_per_image + j) * K;
+    if (n + cnt > CAP) {  // uniform
+      block_select_topk(list, n, K, scratch);
+      n = K;
+    }
+    for (int i = tid; i < cnt; i += DNT) list[n + i] = __ldcg(src + i);
+    n += cnt;
+    __syncthreads();
+  }
+  if (n > K) {
+    block_select_topk(list, n, K, scratch);
+    n = K;
+  }
+  // Fewer than K positive peaks: fill with zero-score pixels in ascending flat order (our tie rule;
+  // the reference returns arbitrary zero-score indices here).
+  if (n < K) {
+    for (int i = tid; i < K; i += DNT) s_taken[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += DNT) {
+      const unsigned int flat = 0xffffffffu - (unsigned int)(list[i] & 0xffffffffull);
+      if (flat < (unsigned int)K) s_taken[flat] = 1;
+    }
+    __syncthreads();
+    const int need = K - n;
+    for (int f = tid; f < K; f += DNT) {
+      if (s_taken[f]) continue;
+      int rank = 0;
+      for (int u = 0; u < f; ++u) rank += s_taken[u] ? 0 : 1;
+      if (rank < need) list[n + rank] = make_key(0.f, (unsigned int)f);
+    }
+    __syncthreads();
+    n = K;
+  }
+  // bitonic sort, descending, on the next power of two (padding keys are 0 = smallest)
+  int npow = 1;
+  while (npow < K) npow <<= 1;
+  for (int i = K + tid; i < npow; i += DNT) list[i] = 0ull;
+  __syncthreads();
+  for (int size = 2; size <= npow; size <<= 1)
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int i = tid; i < npow; i += DNT) {
+        const int partner = i ^ stride;
+        if (partner > i) {
+          const bool desc = ((i & size) == 0);
+          const unsigned long long a = list[i], bb = list[partner];
+          if ((a < bb) == desc) { list[i] = bb; list[partner] = a; }
+        }
+      }
+      __syncthreads();
+    }
+
+  // ------------------------------------------------------------------ gather epilogue: one warp per detection
+  const int N = p.n_poly / 2;
+  const int row_len = p.n_poly + 7;
+  for (int k = warp; k < K; k += DWARPS) {
+    const unsigned long long key = list[k];
+    const unsigned int flat = 0xffffffffu - (unsigned int)(key & 0xffffffffull);
+    const float score = ordered_to_float((unsigned int)(key >> 32));
+    const int cls = (int)(flat / (unsigned int)HW);
+    const int pix = (int)(flat - (unsigned int)cls * (unsigned int)HW);
+    const int y = pix / p.W, x = pix - y * p.W;
+    float xs, ys;
+    if (p.reg.ptr) {  // decode.py:523-527
+      xs = __fadd_rn((float)x, head_value<T>(p.reg, b, 0, y, x));
+      ys = __fadd_rn((float)y, head_value<T>(p.reg, b, 1, y, x));
+    } else {          // decode.py:529-530
+      xs = (float)x + 0.5f;
+      ys = (float)y + 0.5f;
+    }
+    float* orow = p.out + ((int64_t)b * K + k) * row_len;
+    float xmin = CUDART_INF_F, ymin = CUDART_INF_F, xmax = -CUDART_INF_F, ymax = -CUDART_INF_F;
+    for (int vtx = lane; vtx < N; vtx += 32) {
+      float px = head_value<T>(p.polys, b, 2 * vtx, y, x);
+      float py = head_value<T>(p.polys, b, 2 * vtx + 1, y, x);
+      if (p.rep != CPOLY_REP_CARTESIAN) {  // decode.py:582-614: cos/sin in double, product in fp32
+        const double ang = (p.rep == CPOLY_REP_POLAR_FIXED)
+                               ? (2 * 3.14 - 2 * 3.14 / (double)p.n_poly * (double)(2 * vtx))
+                               : (double)py;
+        const float r = px;
+        px = __fmul_rn(r, (float)cos(ang));
+        py = __fmul_rn(r, (float)sin(ang));
+      }
+      px = __fadd_rn(px, xs);  // decode.py:624-625
+      py = __fadd_rn(py, ys);
+      orow[6 + 2 * vtx] = px;
+      orow[6 + 2 * vtx + 1] = py;
+      xmin = fminf(xmin, px); xmax = fmaxf(xmax, px);
+      ymin = fminf(ymin, py); ymax = fmaxf(ymax, py);
+    }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+      xmin = fminf(xmin, __shfl_xor_sync(0xffffffffu, xmin, d));
+      ymin = fminf(ymin, __shfl_xor_sync(0xffffffffu, ymin, d));
+      xmax = fmaxf(xmax, __shfl_xor_sync(0xffffffffu, xmax, d));
+      ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, d));
+    }
+    if (lane == 0) {
+      orow[0] = xmin; orow[1] = ymin; orow[2] = xmax; orow[3] = ymax;  // decode.py:647-659
+      orow[4] = score;
+      orow[5] = (float)cls;
+      orow[6 + p.n_poly] = head_value<T>(p.depth, b, 0, y, x);
+      if (p.out_inds) p.out_inds[(int64_t)b * K + k] = pix;
+    }
+  }
+}
+
+void plan(int B, int C, int H, int W, DecodeParams& p) {
+  p.nbands = (W + BAND - 1) / BAND;
+  int rh = 32;
+  // enough CTAs to cover the machine a couple of times when the problem allows it
+  while (rh > ROUND_ROWS) {
+    const int64_t items = (int64_t)C * ((H + rh - 1) / rh) * p.nbands;
+    const int64_t ctas = (items + DWARPS - 1) / DWARPS * B;
+    if (ctas >= 2 * 148) break;
+    rh >>= 1;
+  }
+  p.rh = rh;
+  p.nrowchunks = (H + rh - 1) / rh;
+  p.items_per_image = C * p.nrowchunks * p.nbands;
+  p.ctas_per_image = (p.items_per_image + DWARPS - 1) / DWARPS;
+}
+
+size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+
+}  // namespace
+
+size_t decode_workspace_bytes(int B, int C, int H, int W, int K) {
+  DecodeParams p;
+  plan(B, C, H, W, p);
+  return align256((size_t)B * p.ctas_per_image * K * sizeof(unsigned long long)) +
+         align256((size_t)B * p.ctas_per_image * sizeof(int)) + align256((size_t)B * sizeof(unsigned int)) + 256;
+}
+
+int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
+  DecodeParams p;
+  p.B = a.B; p.C = a.C; p.H = a.H; p.W = a.W; p.n_poly = a.n_poly; p.K = a.K; p.rep = a.rep;
+  p.heat_is_logit = a.heat_is_logit; p.dtype = a.dtype;
+  p.heat = a.heat; p.polys = a.polys; p.depth = a.depth; p.reg = a.reg;
+  p.out = a.out; p.out_inds = a.out_inds;
+  plan(a.B, a.C, a.H, a.W, p);
+  const size_t need = decode_workspace_bytes(a.B, a.C, a.H, a.W, a.K);
+  CPOLY_REQUIRE(a.workspace && a.workspace_bytes >= need, CPOLY_EWORKSPACE,
+                "decode workspace too small: need %zu bytes, have %zu", need, a.workspace_bytes);
+  CPOLY_REQUIRE((reinterpret_cast<uintptr_t>(a.workspace) & 255) == 0, CPOLY_EINVAL, "decode workspace must be 256-byte aligned");
+  char* ws = reinterpret_cast<char*>(a.workspace);
+  p.cand = reinterpret_cast<unsigned long long*>(ws);
+  ws += align256((size_t)a.B * p.ctas_per_image * a.K * sizeof(unsigned long long));
+  p.cand_count = reinterpret_cast<int*>(ws);
+  ws += align256((size_t)a.B * p.ctas_per_image * sizeof(int));
+  p.done = reinterpret_cast<unsigned int*>(ws);
+  CPOLY_CUDA_OK(cudaMemsetAsync(p.done, 0, (size_t)a.B * sizeof(unsigned int), stream));
+  dim3 grid((unsigned)p.ctas_per_image, (unsigned)a.B);
+  if (a.dtype == CPOLY_BF16) decode_kernel<__nv_bfloat16><<<grid, DNT, 0, stream>>>(p);
+  else decode_kernel<float><<<grid, DNT, 0, stream>>>(p);
+  return check_launch("decode_kernel");
+}
+
+}  // namespace cpoly

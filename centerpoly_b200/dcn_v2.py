@@ -1,0 +1,282 @@
+"""Drop-in replacement for the DCNv2 extension's Python module ``dcn_v2.py``.
+
+The reference imports ``from .DCNv2.dcn_v2 import DCN`` (src/lib/models/networks/pose_dla_dcn.py:16,
+resnet_dcn.py:18) and constructs ``DCN(chi, cho, kernel_size=(3,3), stride=1, padding=1, dilation=1,
+deformable_groups=1)`` (pose_dla_dcn.py:354, resnet_dcn.py:221-223).  The DCNv2 sources themselves are
+a git submodule that is not vendored in the reference; this module mirrors the upstream public API —
+``DCN``, ``DCNv2``, ``dcn_v2_conv``, ``_DCNv2`` — with the same constructor signature, parameter names
+(``weight``, ``bias``, ``conv_offset_mask.{weight,bias}``: checkpoints load unchanged,
+src/lib/models/model.py:52-99), init (weight ~ U(+-1/sqrt(Cin*kh*kw)), bias 0, zero offset conv) and
+error behaviour (RuntimeError on failure), and routes the arithmetic to libcpoly.so through the C ABI
+of include/cpoly.h.  No CPU path, no PyTorch fallback.
+"""
+from __future__ import annotations
+
+import math
+from ctypes import byref, c_void_p
+
+import torch
+from torch import nn
+from torch.autograd import Function
+from torch.autograd.function import once_differentiable
+from torch.nn.modules.utils import _pair
+
+from . import _lib
+
+__all__ = ["DCN", "DCNv2", "dcn_v2_conv", "_DCNv2", "set_dcn_path"]
+
+_FORCED_PATH = _lib.PATH_AUTO
+
+
+def set_dcn_path(path: str) -> None:
+    """'auto' (default), 'simt' or 'tcgen05' — used by tests and profiling to pin a kernel family."""
+    global _FORCED_PATH
+    _FORCED_PATH = {"auto": _lib.PATH_AUTO, "simt": _lib.PATH_SIMT, "tcgen05": _lib.PATH_TCGEN05}[path]
+
+
+def _out_hw(H, W, k, s, p, d):
+    return ((H + 2 * p[0] - (d[0] * (k[0] - 1) + 1)) // s[0] + 1,
+            (W + 2 * p[1] - (d[1] * (k[1] - 1) + 1)) // s[1] + 1)
+
+
+class _PackedWeights:
+    """Derived, non-persistent cache of the tap-major / swizzled weight image (never in state_dict)."""
+
+    def __init__(self):
+        self._entries = {}
+
+    def get(self, weight: torch.Tensor, dtype_code: int):
+        Cout, Cin, kh, kw = weight.shape
+        L = _lib.lib()
+        nbytes = L.cpoly_dcn_packed_weight_bytes(Cin, Cout, kh, kw, dtype_code)
+        if nbytes == 0:
+            return None
+        key = (weight.device, dtype_code)
+        tag = (weight.data_ptr(), weight._version, tuple(weight.shape))
+        hit = self._entries.get(key)
+        if hit is not None and hit[0] == tag:
+            return hit[1]
+        w32 = weight.detach()
+        if w32.dtype != torch.float32 or not w32.is_contiguous():
+            w32 = w32.float().contiguous()
+        packed = torch.empty(nbytes, dtype=torch.uint8, device=weight.device)
+        _lib.check(L.cpoly_dcn_pack_weights(w32.data_ptr(), packed.data_ptr(), Cin, Cout, kh, kw, dtype_code,
+                                            _lib.stream_ptr(weight.device)), "cpoly_dcn_pack_weights")
+        self._entries[key] = (tag, packed)
+        return packed
+
+
+_GLOBAL_PACK_CACHE = _PackedWeights()
+
+
+def _fwd_args(x, offset, mask, weight32, bias32, stride, padding, dilation, dg, mask_is_logit, packed, y):
+    a = _lib.DcnFwdArgs()
+    a.B, a.Cin, a.H, a.W = x.shape
+    a.Cout, _, a.kh, a.kw = weight32.shape
+    a.stride_h, a.stride_w = stride
+    a.pad_h, a.pad_w = padding
+    a.dil_h, a.dil_w = dilation
+    a.deformable_groups = dg
+    a.dtype = _lib.dtype_code(x)
+    a.om_dtype = _lib.dtype_code(offset)
+    a.mask_is_logit = int(mask_is_logit)
+    a.path = _FORCED_PATH
+    a.x, a.offset, a.mask = _lib.t4(x), _lib.t4(offset), _lib.t4(mask)
+    a.weight = weight32.data_ptr()
+    a.bias = bias32.data_ptr() if bias32 is not None else None
+    a.weight_packed = packed.data_ptr() if packed is not None else None
+    a.y = _lib.t4(y)
+    return a
+
+
+def _as_f32_contig(t):
+    if t is None:
+        return None
+    t = t.detach()
+    return t if (t.dtype == torch.float32 and t.is_contiguous()) else t.float().contiguous()
+
+
+def _check_shapes(x, offset, mask, weight, stride, padding, dilation, dg):
+    if x.dim() != 4 or weight.dim() != 4:
+        raise RuntimeError("dcn_v2: input and weight must be 4-d")
+    B, Cin, H, W = x.shape
+    Cout, Cin_w, kh, kw = weight.shape
+    if Cin != Cin_w:
+        raise RuntimeError(f"dcn_v2: input has {Cin} channels but weight expects {Cin_w}")
+    Ho, Wo = _out_hw(H, W, (kh, kw), stride, padding, dilation)
+    if tuple(offset.shape) != (B, dg * 2 * kh * kw, Ho, Wo):
+        raise RuntimeError(f"dcn_v2: offset shape {tuple(offset.shape)} != {(B, dg * 2 * kh * kw, Ho, Wo)}")
+    if tuple(mask.shape) != (B, dg * kh * kw, Ho, Wo):
+        raise RuntimeError(f"dcn_v2: mask shape {tuple(mask.shape)} != {(B, dg * kh * kw, Ho, Wo)}")
+    if offset.dtype != mask.dtype:
+        raise RuntimeError("dcn_v2: offset and mask must share a dtype")
+    return Ho, Wo
+
+
+def _forward_impl(x, offset, mask, weight, bias, stride, padding, dilation, dg, mask_is_logit):
+    dev = _lib.require_cuda(x, offset, mask, weight, bias)
+    Ho, Wo = _check_shapes(x, offset, mask, weight, stride, padding, dilation, dg)
+    L = _lib.lib()
+    w32, b32 = _as_f32_contig(weight), _as_f32_contig(bias)
+    with torch.cuda.device(dev):
+        packed = _GLOBAL_PACK_CACHE.get(weight, _lib.dtype_code(x)) if _FORCED_PATH != _lib.PATH_SIMT else None
+        if packed is not None and not x.is_contiguous(memory_format=torch.channels_last):
+            # the tensor-core path reads NHWC; run the model channels_last to make this a no-op
+            x = x.contiguous(memory_format=torch.channels_last)
+        y = torch.empty((x.shape[0], weight.shape[0], Ho, Wo), dtype=x.dtype, device=dev,
+                        memory_format=torch.channels_last)
+        a = _fwd_args(x, offset, mask, w32, b32, stride, padding, dilation, dg, mask_is_logit, packed, y)
+        _lib.check(L.cpoly_dcn_forward(byref(a), _lib.stream_ptr(dev)), "cpoly_dcn_forward")
+    return y, x
+
+
+def _backward_impl(x, offset, mask, weight, gout, stride, padding, dilation, dg, mask_is_logit, needs):
+    """needs = (x, offset, mask, weight, bias) booleans.  Returns fp32 gradients (None where not needed)."""
+    dev = _lib.require_cuda(x, offset, mask, weight, gout)
+    L = _lib.lib()
+    w32 = _as_f32_contig(weight)
+    if gout.dtype != x.dtype:
+        gout = gout.to(x.dtype)
+    with torch.cuda.device(dev):
+        gx = torch.empty_like(x, dtype=torch.float32) if needs[0] else None
+        goff = torch.empty_like(offset, dtype=torch.float32) if needs[1] else None
+        gmask = torch.empty_like(mask, dtype=torch.float32) if needs[2] else None
+        gw = torch.empty(weight.shape, dtype=torch.float32, device=dev) if needs[3] else None
+        gb = torch.empty(weight.shape[0], dtype=torch.float32, device=dev) if needs[4] else None
+        b = _lib.DcnBwdArgs()
+        b.f = _fwd_args(x, offset, mask, w32, None, stride, padding, dilation, dg, mask_is_logit, None, None)
+        b.gout = _lib.t4(gout)
+        b.gx, b.goffset, b.gmask = _lib.t4(gx), _lib.t4(goff), _lib.t4(gmask)
+        b.gweight = gw.data_ptr() if gw is not None else None
+        b.gbias = gb.data_ptr() if gb is not None else None
+        nbytes = L.cpoly_dcn_backward_workspace_bytes(byref(b))
+        ws = _lib.workspace(nbytes, dev)
+        b.workspace, b.workspace_bytes = ws.data_ptr(), ws.numel()
+        _lib.check(L.cpoly_dcn_backward(byref(b), _lib.stream_ptr(dev)), "cpoly_dcn_backward")
+    return gx, goff, gmask, gw, gb
+
+
+def _cast(g, like):
+    return None if g is None else (g if g.dtype == like.dtype else g.to(like.dtype))
+
+
+class _DCNv2(Function):
+    """Upstream-compatible autograd seam: forward(ctx, input, offset, mask, weight, bias, stride, padding,
+    dilation, deformable_groups); backward returns 5 gradients + 4 Nones; once_differentiable."""
+
+    @staticmethod
+    def forward(ctx, input, offset, mask, weight, bias, stride, padding, dilation, deformable_groups):
+        ctx.stride, ctx.padding, ctx.dilation = _pair(stride), _pair(padding), _pair(dilation)
+        ctx.deformable_groups = deformable_groups
+        y, x_used = _forward_impl(input, offset, mask, weight, bias, ctx.stride, ctx.padding, ctx.dilation,
+                                  deformable_groups, mask_is_logit=False)
+        ctx.save_for_backward(x_used, offset, mask, weight, bias)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_output):
+        x, offset, mask, weight, bias = ctx.saved_tensors
+        needs = ctx.needs_input_grad[:5]
+        gx, goff, gmask, gw, gb = _backward_impl(x, offset, mask, weight, grad_output, ctx.stride, ctx.padding,
+                                                 ctx.dilation, ctx.deformable_groups, False, needs)
+        return (_cast(gx, x), _cast(goff, offset), _cast(gmask, mask), _cast(gw, weight),
+                _cast(gb, bias) if bias is not None else None, None, None, None, None)
+
+
+class _DCNFused(Function):
+    """DCN.forward's body with the chunk/cat/sigmoid of the offset-conv output fused into the kernels:
+    takes the raw 3*dg*kh*kw-channel tensor ``om`` (offsets | mask logits) and returns d/d(om)."""
+
+    @staticmethod
+    def forward(ctx, input, om, weight, bias, stride, padding, dilation, deformable_groups):
+        ctx.stride, ctx.padding, ctx.dilation = stride, padding, dilation
+        ctx.deformable_groups = deformable_groups
+        n_off = om.shape[1] // 3 * 2
+        y, x_used = _forward_impl(input, om[:, :n_off], om[:, n_off:], weight, bias, stride, padding, dilation,
+                                  deformable_groups, mask_is_logit=True)
+        ctx.save_for_backward(x_used, om, weight, bias)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, grad_output):
+        x, om, weight, bias = ctx.saved_tensors
+        n_off = om.shape[1] // 3 * 2
+        needs = ctx.needs_input_grad
+        gom = torch.empty_like(om, dtype=torch.float32) if needs[1] else None
+        # the kernels write straight into the two channel ranges of d/d(om)
+        dev = x.device
+        L = _lib.lib()
+        w32 = _as_f32_contig(weight)
+        gout = grad_output if grad_output.dtype == x.dtype else grad_output.to(x.dtype)
+        with torch.cuda.device(dev):
+            gx = torch.empty_like(x, dtype=torch.float32) if needs[0] else None
+            gw = torch.empty(weight.shape, dtype=torch.float32, device=dev) if needs[2] else None
+            gb = torch.empty(weight.shape[0], dtype=torch.float32, device=dev) if (needs[3] and bias is not None) else None
+            b = _lib.DcnBwdArgs()
+            b.f = _fwd_args(x, om[:, :n_off], om[:, n_off:], w32, None, ctx.stride, ctx.padding, ctx.dilation,
+                            ctx.deformable_groups, True, None, None)
+            b.gout = _lib.t4(gout)
+            b.gx = _lib.t4(gx)
+            b.goffset = _lib.t4(gom[:, :n_off] if gom is not None else None)
+            b.gmask = _lib.t4(gom[:, n_off:] if gom is not None else None)
+            b.gweight = gw.data_ptr() if gw is not None else None
+            b.gbias = gb.data_ptr() if gb is not None else None
+            ws = _lib.workspace(L.cpoly_dcn_backward_workspace_bytes(byref(b)), dev)
+            b.workspace, b.workspace_bytes = ws.data_ptr(), ws.numel()
+            _lib.check(L.cpoly_dcn_backward(byref(b), _lib.stream_ptr(dev)), "cpoly_dcn_backward")
+        return (_cast(gx, x), _cast(gom, om), _cast(gw, weight), _cast(gb, bias) if bias is not None else None,
+                None, None, None, None)
+
+
+dcn_v2_conv = _DCNv2.apply
+
+
+class DCNv2(nn.Module):
+    """Modulated deformable convolution whose offsets and mask are supplied by the caller."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride, padding, dilation=1, deformable_groups=1):
+        super().__init__()
+        self.in_channels = in_channels
+        self.out_channels = out_channels
+        self.kernel_size = _pair(kernel_size)
+        self.stride = _pair(stride)
+        self.padding = _pair(padding)
+        self.dilation = _pair(dilation)
+        self.deformable_groups = deformable_groups
+        self.weight = nn.Parameter(torch.empty(out_channels, in_channels, *self.kernel_size))
+        self.bias = nn.Parameter(torch.empty(out_channels))
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        fan = self.in_channels * self.kernel_size[0] * self.kernel_size[1]
+        bound = 1.0 / math.sqrt(fan)
+        with torch.no_grad():
+            self.weight.uniform_(-bound, bound)
+            self.bias.zero_()
+
+    def forward(self, input, offset, mask):
+        return dcn_v2_conv(input, offset, mask, self.weight, self.bias, self.stride, self.padding, self.dilation,
+                           self.deformable_groups)
+
+
+class DCN(DCNv2):
+    """DCNv2 that predicts its own offsets/mask with a zero-initialised regular conv (a2 in SURVEY §8)."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride, padding, dilation=1, deformable_groups=1):
+        super().__init__(in_channels, out_channels, kernel_size, stride, padding, dilation, deformable_groups)
+        n = self.deformable_groups * 3 * self.kernel_size[0] * self.kernel_size[1]
+        self.conv_offset_mask = nn.Conv2d(self.in_channels, n, kernel_size=self.kernel_size, stride=self.stride,
+                                          padding=self.padding, bias=True)
+        self.init_offset()
+
+    def init_offset(self):
+        with torch.no_grad():
+            self.conv_offset_mask.weight.zero_()
+            self.conv_offset_mask.bias.zero_()
+
+    def forward(self, input):
+        om = self.conv_offset_mask(input)
+        return _DCNFused.apply(input, om, self.weight, self.bias, self.stride, self.padding, self.dilation,
+                               self.deformable_groups)

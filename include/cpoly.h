@@ -1,0 +1,151 @@
+/*
+ * cpoly.h — C ABI of libcpoly.so, the B200 (sm_100a) implementation of CenterPoly v2's
+ * data-parallel hot path.  Plain pointers, sizes and ints only: no torch / C++ types.
+ *
+ * What each entry point replaces in the reference (paths relative to the reference checkout):
+ *
+ *   cpoly_dcn_forward    <- `_ext.dcn_v2_forward(input, weight, bias, offset, mask, kh,kw, sh,sw, ph,pw,
+ *                           dh,dw, deformable_group)` of the DCNv2 extension, reached through
+ *                           `DCN.forward` from src/lib/models/networks/pose_dla_dcn.py:354-359 (DeformConv)
+ *                           and src/lib/models/networks/resnet_dcn.py:221-223.  The extension itself is the
+ *                           git submodule src/lib/models/networks/DCNv2 (pinned dee2e77e…, not vendored).
+ *   cpoly_dcn_backward   <- `_ext.dcn_v2_backward(input, weight, bias, offset, mask, grad_output, …)` of the
+ *                           same extension (autograd of the 16 DCN layers; driven by
+ *                           src/lib/trains/base_trainer.py:97-98 `loss.backward()`).
+ *   cpoly_dcn_pack_weights  (new) derived tap-major / MMA-swizzled weight cache; the stored parameter stays
+ *                           (Cout,Cin,kh,kw) so checkpoints (src/lib/models/model.py:31-130) are unaffected.
+ *   cpoly_decode         <- `polydet_decode(heat, polys, depth, reg, cat_spec_poly, K, rep)`
+ *                           src/lib/models/decode.py:512-670, i.e. `_nms` :13-19, `_topk` :117-133,
+ *                           `_transpose_and_gather_feat` src/lib/models/utils.py:22-26, and (optionally, with
+ *                           heat_is_logit=1) the `hm.sigmoid_()` of src/lib/detectors/polydet.py:28.
+ *
+ * Ownership: the caller allocates every input, output and workspace in device memory and passes raw
+ * device pointers; the library allocates nothing, keeps no global state and never synchronises the
+ * host.  All work is enqueued on `stream`.  Re-entrant (one Python thread per GPU under
+ * nn.DataParallel, src/lib/models/data_parallel.py:80-81, is fine).
+ *
+ * Errors: every int-returning function returns 0 on success or a CPOLY_E* code; a human-readable
+ * message for the calling thread is then available from cpoly_last_error().  The Python shim turns
+ * a non-zero code into RuntimeError (what the upstream extension's AT_ASSERTM did).
+ *
+ * Tensors are described by a base pointer plus four ELEMENT strides in logical (b, c, h, w) order,
+ * so NCHW-contiguous (the reference's default) and channels_last (NHWC physical) are both accepted.
+ */
+#ifndef CPOLY_H_
+#define CPOLY_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CPOLY_ABI_VERSION 1
+
+/* element types */
+#define CPOLY_F32 0
+#define CPOLY_BF16 1
+
+/* error codes */
+#define CPOLY_OK 0
+#define CPOLY_EINVAL 1      /* bad argument (shape, dtype, NULL pointer, unsupported geometry) */
+#define CPOLY_EWORKSPACE 2  /* workspace too small */
+#define CPOLY_ECUDA 3       /* a CUDA runtime call or kernel launch failed */
+#define CPOLY_EUNSUPPORTED 4
+
+/* polygon representation of the poly head (src/lib/opts.py:72-74, decode.py:582,603) */
+#define CPOLY_REP_CARTESIAN 0   /* also what 'polar_confined' / any other string decodes as */
+#define CPOLY_REP_POLAR 1
+#define CPOLY_REP_POLAR_FIXED 2
+
+/* which DCN kernel family cpoly_dcn_forward / backward should use */
+#define CPOLY_PATH_AUTO 0    /* tensor-core path when the shape allows, else SIMT */
+#define CPOLY_PATH_SIMT 1    /* generic CUDA-core implicit GEMM (any geometry, any strides) */
+#define CPOLY_PATH_TCGEN05 2 /* tcgen05/TMEM path; CPOLY_EUNSUPPORTED if the shape does not qualify */
+
+typedef struct CUstream_st* cpoly_stream_t; /* == cudaStream_t */
+
+typedef struct {
+  void* ptr;          /* device pointer to element (0,0,0,0) */
+  int64_t sb, sc, sh, sw; /* element strides of the logical (batch, channel, row, column) axes */
+} cpoly_tensor4;
+
+/* ------------------------------------------------------------------------------------------ DCN */
+
+typedef struct {
+  int32_t B, Cin, Cout, H, W;              /* input is (B,Cin,H,W); output (B,Cout,Ho,Wo) */
+  int32_t kh, kw, stride_h, stride_w, pad_h, pad_w, dil_h, dil_w;
+  int32_t deformable_groups;
+  int32_t dtype;         /* CPOLY_F32 | CPOLY_BF16: element type of x and y (and of gout in backward) */
+  int32_t om_dtype;      /* element type of offset and mask */
+  int32_t mask_is_logit; /* 1: `mask` holds pre-sigmoid logits; the sigmoid of DCN.forward is fused */
+  int32_t path;          /* CPOLY_PATH_* */
+  cpoly_tensor4 x;       /* (B,Cin,H,W)                       */
+  cpoly_tensor4 offset;  /* (B,dg*2*kh*kw,Ho,Wo): channel 2k = dy, 2k+1 = dx of tap k = i*kw+j */
+  cpoly_tensor4 mask;    /* (B,dg*kh*kw,Ho,Wo)                */
+  const float* weight;   /* (Cout,Cin,kh,kw) dense fp32 master weights (always required)        */
+  const float* bias;     /* (Cout) fp32 or NULL                                                 */
+  const void* weight_packed; /* output of cpoly_dcn_pack_weights for `dtype`, or NULL (=> SIMT)  */
+  cpoly_tensor4 y;       /* (B,Cout,Ho,Wo), element type `dtype`                                */
+} cpoly_dcn_fwd_args;
+
+typedef struct {
+  cpoly_dcn_fwd_args f;  /* forward problem (f.y is ignored) */
+  cpoly_tensor4 gout;    /* (B,Cout,Ho,Wo), element type f.dtype */
+  /* outputs — all fp32, any may have ptr == NULL to skip it (ctx.needs_input_grad) */
+  cpoly_tensor4 gx;      /* (B,Cin,H,W)      */
+  cpoly_tensor4 goffset; /* like offset      */
+  cpoly_tensor4 gmask;   /* like mask; d/d(logit) when f.mask_is_logit */
+  float* gweight;        /* (Cout,Cin,kh,kw) dense */
+  float* gbias;          /* (Cout) */
+  void* workspace;       /* >= cpoly_dcn_backward_workspace_bytes(&args) bytes, 256-byte aligned */
+  size_t workspace_bytes;
+} cpoly_dcn_bwd_args;
+
+int cpoly_abi_version(void);
+const char* cpoly_last_error(void);
+/* 1 when the running device is sm_100 (tcgen05 available), 0 otherwise, <0 on CUDA error */
+int cpoly_device_supports_tcgen05(void);
+
+/* 1 if (args) qualifies for the tcgen05 path: 3x3, stride 1, pad 1, dil 1, dg 1, channels_last x and y
+ * (sc == 1), Cin % 64 == 0 (bf16) or % 32 == 0 (fp32), Cout % 16 == 0 and <= 256. */
+int cpoly_dcn_tcgen05_eligible(const cpoly_dcn_fwd_args* args);
+
+size_t cpoly_dcn_packed_weight_bytes(int32_t Cin, int32_t Cout, int32_t kh, int32_t kw, int32_t dtype);
+/* weight (Cout,Cin,kh,kw) fp32 -> tap-major, K-chunked, 128B-swizzled smem image in `dtype`
+ * (bf16, or fp32 rounded to tf32) that the tcgen05 kernels bulk-copy straight into shared memory. */
+int cpoly_dcn_pack_weights(const float* weight, void* packed, int32_t Cin, int32_t Cout, int32_t kh,
+                           int32_t kw, int32_t dtype, cpoly_stream_t stream);
+
+int cpoly_dcn_forward(const cpoly_dcn_fwd_args* args, cpoly_stream_t stream);
+
+size_t cpoly_dcn_backward_workspace_bytes(const cpoly_dcn_bwd_args* args);
+int cpoly_dcn_backward(const cpoly_dcn_bwd_args* args, cpoly_stream_t stream);
+
+/* --------------------------------------------------------------------------------------- decode */
+
+typedef struct {
+  int32_t B, C, H, W;   /* heat is (B,C,H,W) */
+  int32_t n_poly;       /* 2N: channels of the poly head */
+  int32_t K;            /* detections per image, 1..1024 and <= H*W */
+  int32_t rep;          /* CPOLY_REP_* */
+  int32_t heat_is_logit; /* 1: apply the logistic first (fuses detectors/polydet.py:28) */
+  int32_t dtype;        /* element type of heat/polys/depth/reg: CPOLY_F32 | CPOLY_BF16 */
+  cpoly_tensor4 heat;   /* (B,C,H,W); post-sigmoid unless heat_is_logit */
+  cpoly_tensor4 polys;  /* (B,2N,H,W) */
+  cpoly_tensor4 depth;  /* (B,1,H,W)  */
+  cpoly_tensor4 reg;    /* (B,2,H,W) or ptr == NULL => centres get +0.5 (decode.py:529-530) */
+  float* out;           /* (B,K,2N+7) dense fp32: xmin,ymin,xmax,ymax,score,class,x0,y0,…,depth */
+  int64_t* out_inds;    /* optional (B,K) flat y*W+x of every detection, or NULL */
+  void* workspace;      /* >= cpoly_decode_workspace_bytes(B,C,H,W,K), 256-byte aligned */
+  size_t workspace_bytes;
+} cpoly_decode_args;
+
+size_t cpoly_decode_workspace_bytes(int32_t B, int32_t C, int32_t H, int32_t W, int32_t K);
+int cpoly_decode(const cpoly_decode_args* args, cpoly_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CPOLY_H_ */

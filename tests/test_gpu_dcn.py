@@ -1,0 +1,188 @@
+"""GPU parity: the CUDA DCN (through the C ABI) against the CPU oracle and the committed golden vectors.
+Tolerances (BASELINE.json north_star): 1e-3 relative for fp32 I/O (tf32 tensor-core products), 1e-2 for bf16."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from util import gate, make_dcn_case
+
+pytestmark = pytest.mark.gpu
+
+DCN_GOLDEN = sorted(glob.glob(os.path.join(GOLDEN, "dcn_*.npz")))
+
+
+def _cuda(t, dtype=None, channels_last=False):
+    t = t.cuda()
+    if dtype is not None:
+        t = t.to(dtype)
+    if channels_last:
+        t = t.contiguous(memory_format=torch.channels_last)
+    return t
+
+
+def run_ours(case, path, dtype=torch.float32, channels_last=False, stride=1, pad=1, dil=1, dg=1, backward=True):
+    import centerpoly_b200 as cp
+    cp.set_dcn_path(path)
+    try:
+        x = _cuda(case["x"], dtype, channels_last).requires_grad_(True)
+        off = _cuda(case["offset"], dtype).requires_grad_(True)
+        msk = _cuda(case["mask"], dtype).requires_grad_(True)
+        w = _cuda(case["weight"]).requires_grad_(True)
+        b = _cuda(case["bias"]).requires_grad_(True)
+        y = cp.dcn_v2_conv(x, off, msk, w, b, stride, pad, dil, dg)
+        out = {"y": y.detach().float().cpu().numpy()}
+        if backward:
+            y.backward(_cuda(case["gout"], dtype))
+            for name, leaf in (("gx", x), ("goffset", off), ("gmask", msk), ("gw", w), ("gb", b)):
+                out[name] = leaf.grad.detach().float().cpu().numpy()
+        torch.cuda.synchronize()
+        return out
+    finally:
+        cp.set_dcn_path("auto")
+
+
+def oracle(case, stride=1, pad=1, dil=1, dg=1, backward=True):
+    from oracle import dcn_oracle
+    a = {k: v.double().numpy() for k, v in case.items()}
+    out = {"y": dcn_oracle.dcn_forward(a["x"], a["offset"], a["mask"], a["weight"], a["bias"], stride, pad, dil, dg)}
+    if backward:
+        gx, go, gm, gw, gb = dcn_oracle.dcn_backward(a["x"], a["offset"], a["mask"], a["weight"], a["gout"], stride, pad, dil, dg)
+        out.update(gx=gx, goffset=go, gmask=gm, gw=gw, gb=gb)
+    return out
+
+
+@pytest.mark.parametrize("path", DCN_GOLDEN, ids=lambda p: os.path.basename(p)[:-4])
+def test_simt_vs_golden_all_geometries(path):
+    """Generic path against the committed torchvision-fp64 vectors (stride 2, dilation 2, 2 deformable groups,
+    far out-of-bounds offsets, zero offsets, integer offsets)."""
+    g = np.load(path)
+    s, p, d, dg = (int(v) for v in g["geom"])
+    case = {k: torch.from_numpy(g[k]).float() for k in ("x", "offset", "mask", "weight", "bias", "gout")}
+    got = run_ours(case, "simt", stride=s, pad=p, dil=d, dg=dg)
+    want = oracle(case, s, p, d, dg)  # C oracle == golden except the documented p == -1 grad_offset convention
+    np.testing.assert_allclose(want["y"], g["y"], atol=1e-5)
+    for name in ("y", "gx", "goffset", "gmask", "gw", "gb"):
+        gate(got[name], want[name], 1e-4, name)
+
+
+TC_SHAPES = [  # (B, Cin, Cout, H, W) — reduced-resolution versions of the 7 IDAUp shape classes + ragged sizes
+    (1, 64, 64, 16, 32), (2, 128, 64, 24, 40), (1, 128, 128, 16, 16), (1, 256, 64, 8, 16),
+    (1, 256, 128, 9, 21), (1, 256, 256, 8, 16), (1, 512, 256, 8, 16), (3, 64, 64, 5, 7),
+]
+
+
+@pytest.mark.parametrize("shape", TC_SHAPES, ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "fp32"])
+def test_tcgen05_forward_vs_oracle(shape, dtype):
+    B, Cin, Cout, H, W = shape
+    case = make_dcn_case(317 + Cin + Cout, B, Cin, Cout, H, W, dtype=dtype)
+    got = run_ours(case, "tcgen05", dtype=dtype, channels_last=True, backward=False)
+    want = oracle(case, backward=False)
+    gate(got["y"], want["y"], 1e-2 if dtype == torch.bfloat16 else 1e-3, "y")
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "fp32"])
+def test_tcgen05_zero_offsets(dtype):
+    case = make_dcn_case(5, 1, 64, 64, 16, 32, offset_mode="zero", dtype=dtype)
+    got = run_ours(case, "tcgen05", dtype=dtype, channels_last=True, backward=False)
+    want = oracle(case, backward=False)
+    gate(got["y"], want["y"], 1e-2 if dtype == torch.bfloat16 else 1e-3, "y")
+
+
+@pytest.mark.parametrize("shape", [(1, 64, 64, 12, 20), (2, 128, 64, 9, 11)], ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "fp32"])
+def test_backward_vs_oracle(shape, dtype):
+    B, Cin, Cout, H, W = shape
+    case = make_dcn_case(99 + Cin, B, Cin, Cout, H, W, dtype=dtype)
+    got = run_ours(case, "auto", dtype=dtype, channels_last=True)
+    want = oracle(case)
+    tol = 1e-2 if dtype == torch.bfloat16 else 1e-3
+    for name in ("y", "gx", "goffset", "gmask", "gw", "gb"):
+        gate(got[name], want[name], tol, name)
+
+
+def test_backward_is_deterministic_for_weights():
+    case = make_dcn_case(7, 2, 64, 64, 12, 20)
+    a = run_ours(case, "auto", channels_last=True)
+    b = run_ours(case, "auto", channels_last=True)
+    for name in ("y", "goffset", "gmask", "gw", "gb"):
+        np.testing.assert_array_equal(a[name], b[name], err_msg=name)
+
+
+def test_nchw_input_is_accepted():
+    case = make_dcn_case(11, 1, 64, 64, 10, 12)
+    got = run_ours(case, "auto", channels_last=False)
+    want = oracle(case)
+    for name in ("y", "gx", "gw"):
+        gate(got[name], want[name], 1e-3, name)
+
+
+def test_full_size_zero_offset_identity_and_linearity():
+    """BASELINE full size (64->64 @ 256x512, the stride-4 node layers): size-independent properties.
+    (1) zero conv_offset_mask => DCN(x) == 0.5*conv2d(x, W) + b  (the reference's true init state);
+    (2) linearity in x for fixed offsets/mask."""
+    import centerpoly_b200 as cp
+    torch.manual_seed(0)
+    m = cp.DCN(64, 64, (3, 3), 1, 1).cuda().to(memory_format=torch.channels_last)
+    x = torch.randn(1, 64, 256, 512, device="cuda").contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        y = m(x)
+        ref = 0.5 * torch.nn.functional.conv2d(x.double(), m.weight.double(), None, padding=1) + m.bias.double().view(1, -1, 1, 1)
+        gate(y.double().cpu().numpy(), ref.cpu().numpy(), 1e-3, "identity")
+        m.conv_offset_mask.weight.normal_(std=0.05)
+        m.conv_offset_mask.bias.normal_(std=1.0)
+        om = m.conv_offset_mask(x)
+        x2 = torch.randn_like(x)
+        f = lambda t: cp.dcn_v2_conv(t, om[:, :18].float(), torch.sigmoid(om[:, 18:]).float(), m.weight, None, 1, 1, 1, 1)
+        lhs = f(x + 2 * x2)
+        rhs = f(x) + 2 * f(x2)
+        gate(lhs.double().cpu().numpy(), rhs.double().cpu().numpy(), 2e-3, "linearity")
+
+
+def test_module_matches_torchvision_module():
+    """DCN module (fused sigmoid/chunk path) vs the torchvision-backed oracle module, same state_dict."""
+    import centerpoly_b200 as cp
+    from oracle.tv_dcn import TVDCN
+    torch.manual_seed(3)
+    ref = TVDCN(64, 64, (3, 3), 1, 1)
+    torch.nn.init.normal_(ref.conv_offset_mask.weight, std=0.05)
+    torch.nn.init.normal_(ref.conv_offset_mask.bias, std=1.0)
+    ours = cp.DCN(64, 64, (3, 3), 1, 1)
+    assert list(ours.state_dict().keys()) == list(ref.state_dict().keys())
+    ours.load_state_dict(ref.state_dict())
+    ours = ours.cuda()
+    x = torch.randn(2, 64, 14, 18)
+    xr = x.clone().requires_grad_(True)
+    yr = ref(xr)
+    gout = torch.randn_like(yr)
+    yr.backward(gout)
+    xo = x.cuda().requires_grad_(True)
+    yo = ours(xo)
+    yo.backward(gout.cuda())
+    gate(yo.detach().cpu().numpy(), yr.detach().numpy(), 1e-3, "y")
+    gate(xo.grad.cpu().numpy(), xr.grad.numpy(), 1e-3, "gx")
+    for (n, po), (_, pr) in zip(ours.named_parameters(), ref.named_parameters()):
+        gate(po.grad.cpu().numpy(), pr.grad.numpy(), 2e-3, n)
+
+
+def test_frozen_weights_get_no_grad():
+    import centerpoly_b200 as cp
+    m = cp.DCN(64, 64, (3, 3), 1, 1).cuda()
+    m.weight.requires_grad_(False)
+    x = torch.randn(1, 64, 8, 8, device="cuda", requires_grad=True)
+    m(x).sum().backward()
+    assert m.weight.grad is None and x.grad is not None and m.bias.grad is not None
+
+
+def test_errors_are_runtime_errors():
+    import centerpoly_b200 as cp
+    x = torch.randn(1, 4, 8, 8, device="cuda")
+    w = torch.randn(4, 4, 3, 3, device="cuda")
+    with pytest.raises(RuntimeError):
+        cp.dcn_v2_conv(x, torch.zeros(1, 17, 8, 8, device="cuda"), torch.zeros(1, 9, 8, 8, device="cuda"), w, None, 1, 1, 1, 1)
+    with pytest.raises(RuntimeError):
+        cp.dcn_v2_conv(x.cpu(), torch.zeros(1, 18, 8, 8), torch.zeros(1, 9, 8, 8), w.cpu(), None, 1, 1, 1, 1)
