@@ -33,7 +33,7 @@ constexpr int A_STAGE_BYTES = TILE_PX * ROW_BYTES;  // 16 KB
 constexpr int MAX_STAGES = 6;
 constexpr int EPI_WARPS = 4;
 constexpr int SAMPLER_WARP0 = 6;
-constexpr int SAMPLER_WARPS = 8;
+constexpr int SAMPLER_WARPS = 16;
 constexpr int NS = SAMPLER_WARPS * 32;         // sampler threads
 constexpr int NTHREADS = (SAMPLER_WARP0 + SAMPLER_WARPS) * 32;
 constexpr int ROWS_PER_PASS = NS / 8;          // 8 lanes x 16 B cover one 128-byte row
@@ -229,7 +229,7 @@ template <> struct OutConv<float> {
 
 // ---------------------------------------------------------------------------------------- kernel
 template <typename T>
-__global__ void __launch_bounds__(NTHREADS, 1) dcn_fwd_tc_kernel(const TcParams p) {
+__global__ void __maxnreg__(88) dcn_fwd_tc_kernel(const TcParams p) {
   constexpr bool kTF32 = sizeof(T) == 4;
   constexpr int kVec = Blend<T>::kVec;       // channels per 16 B
   constexpr int kChunk = ROW_BYTES / sizeof(T);  // channels per K chunk (64 bf16 / 32 fp32)
@@ -281,26 +281,47 @@ __global__ void __launch_bounds__(NTHREADS, 1) dcn_fwd_tc_kernel(const TcParams 
     const int st = threadIdx.x - SAMPLER_WARP0 * 32;
     const int row_in_pass = st >> 3, cg = st & 7;
     const T* xg = reinterpret_cast<const T*>(p.x);
+    constexpr int ITEMS = (NUM_TAPS * TILE_PX + NS - 1) / NS;  // (pixel, tap) items per thread and tile
+    float raw_dy[ITEMS], raw_dx[ITEMS], raw_m[ITEMS];
+    // raw offsets / mask of one tile -> registers (issued one tile ahead so the latency hides behind sampling)
+    auto fetch_raw = [&](int tile) {
+      const int b = tile / tiles_per_img;
+      const int trem = tile - b * tiles_per_img;
+      const int ty0 = (trem / p.tiles_x) * TILE_H, tx0 = (trem % p.tiles_x) * TILE_W;
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
+        const int item = st + i * NS;
+        const int k = item / TILE_PX, r = item - k * TILE_PX;
+        const int y = ty0 + r / TILE_W, x = tx0 + r % TILE_W;
+        raw_dy[i] = raw_dx[i] = raw_m[i] = 0.f;
+        if (item < NUM_TAPS * TILE_PX && y < p.H && x < p.W) {
+          const int64_t opix = (int64_t)b * p.offset.sb + (int64_t)y * p.offset.sh + (int64_t)x * p.offset.sw;
+          raw_dy[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k) * p.offset.sc, p.om_dtype);
+          raw_dx[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k + 1) * p.offset.sc, p.om_dtype);
+          raw_m[i] = ld_dyn(p.mask.ptr, (int64_t)b * p.mask.sb + (int64_t)k * p.mask.sc + (int64_t)y * p.mask.sh + (int64_t)x * p.mask.sw, p.om_dtype);
+        }
+      }
+    };
     uint32_t it = 0;
+    if ((int)blockIdx.x < p.num_tiles) fetch_raw(blockIdx.x);
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
       const int b = tile / tiles_per_img;
       const int trem = tile - b * tiles_per_img;
       const int ty0 = (trem / p.tiles_x) * TILE_H, tx0 = (trem % p.tiles_x) * TILE_W;
       named_bar_sync(1, NS);  // everyone finished reading the previous tile's params
-      for (int item = st; item < NUM_TAPS * TILE_PX; item += NS) {
+#pragma unroll
+      for (int i = 0; i < ITEMS; ++i) {
+        const int item = st + i * NS;
+        if (item >= NUM_TAPS * TILE_PX) break;
         const int k = item / TILE_PX, r = item - k * TILE_PX;
         const int y = ty0 + r / TILE_W, x = tx0 + r % TILE_W;
         TapParam tp;
 #pragma unroll
         for (int q = 0; q < 4; ++q) { tp.off[q] = 0; tp.w[q] = 0.f; }
         if (y < p.H && x < p.W) {
-          const int64_t opix = (int64_t)b * p.offset.sb + (int64_t)y * p.offset.sh + (int64_t)x * p.offset.sw;
-          const float dy = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k) * p.offset.sc, p.om_dtype);
-          const float dx = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k + 1) * p.offset.sc, p.om_dtype);
-          float m = ld_dyn(p.mask.ptr, (int64_t)b * p.mask.sb + (int64_t)k * p.mask.sc + (int64_t)y * p.mask.sh + (int64_t)x * p.mask.sw, p.om_dtype);
-          if (p.mask_is_logit) m = sigmoidf_accurate(m);
-          const float py = (float)(y - 1 + k / 3) + dy;
-          const float px = (float)(x - 1 + k % 3) + dx;
+          const float m = p.mask_is_logit ? sigmoidf_accurate(raw_m[i]) : raw_m[i];
+          const float py = (float)(y - 1 + k / 3) + raw_dy[i];
+          const float px = (float)(x - 1 + k % 3) + raw_dx[i];
           const TapSample t = make_tap(py, px, p.H, p.W, (int64_t)b * p.H * p.W * p.Cin, (int64_t)p.W * p.Cin, (int64_t)p.Cin);
 #pragma unroll
           for (int q = 0; q < 4; ++q)
@@ -311,24 +332,34 @@ __global__ void __launch_bounds__(NTHREADS, 1) dcn_fwd_tc_kernel(const TcParams 
         dst[1] = make_uint4(__float_as_uint(tp.w[0]), __float_as_uint(tp.w[1]), __float_as_uint(tp.w[2]), __float_as_uint(tp.w[3]));
       }
       named_bar_sync(1, NS);
+      if (tile + (int)gridDim.x < p.num_tiles) fetch_raw(tile + gridDim.x);
       for (int k = 0; k < NUM_TAPS; ++k) {
         for (int cc = 0; cc < p.nchunk; ++cc, ++it) {
           const uint32_t s = it % (uint32_t)p.stages, ph = (it / (uint32_t)p.stages) & 1u;
-          mbar_wait(bar_empty + 8 * s, ph ^ 1u);
-          const uint32_t a_base = smem_base + SMEM_STAGE_OFF + s * p.stage_bytes;
           const int chan = cc * kChunk + cg * kVec;
+          // phase 1: every corner load of this thread's rows goes out before anything is consumed
+          uint4 c[PASSES][4];
+          uint4 pw[PASSES];
 #pragma unroll
           for (int pass = 0; pass < PASSES; ++pass) {
             const int r = pass * ROWS_PER_PASS + row_in_pass;
             const uint4* pp = reinterpret_cast<const uint4*>(&params[k * TILE_PX + r]);
-            const uint4 po = pp[0], pw = pp[1];
-            uint4 c[4];
-            c[0] = ldg16(xg + (int)po.x + chan);
-            c[1] = ldg16(xg + (int)po.y + chan);
-            c[2] = ldg16(xg + (int)po.z + chan);
-            c[3] = ldg16(xg + (int)po.w + chan);
-            const float w[4] = {__uint_as_float(pw.x), __uint_as_float(pw.y), __uint_as_float(pw.z), __uint_as_float(pw.w)};
-            const uint4 v = Blend<T>::run(c, w);
+            const uint4 po = pp[0];
+            pw[pass] = pp[1];
+            c[pass][0] = ldg16(xg + (int)po.x + chan);
+            c[pass][1] = ldg16(xg + (int)po.y + chan);
+            c[pass][2] = ldg16(xg + (int)po.z + chan);
+            c[pass][3] = ldg16(xg + (int)po.w + chan);
+          }
+          mbar_wait(bar_empty + 8 * s, ph ^ 1u);
+          const uint32_t a_base = smem_base + SMEM_STAGE_OFF + s * p.stage_bytes;
+          // phase 2: blend and write the swizzled A rows
+#pragma unroll
+          for (int pass = 0; pass < PASSES; ++pass) {
+            const int r = pass * ROWS_PER_PASS + row_in_pass;
+            const float w[4] = {__uint_as_float(pw[pass].x), __uint_as_float(pw[pass].y), __uint_as_float(pw[pass].z),
+                                __uint_as_float(pw[pass].w)};
+            const uint4 v = Blend<T>::run(c[pass], w);
             sts16(a_base + r * ROW_BYTES + ((cg ^ (r & 7)) << 4), v);
           }
           fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)

@@ -1,0 +1,127 @@
+"""Inference engine around the hot path: DLA-34 polydet network (harness/dla34.py) -> ``hm.sigmoid_()`` ->
+``polydet_decode``, i.e. what ``PolydetDetector.process`` does (src/lib/detectors/polydet.py:25-43), captured
+once into a CUDA graph so the ~250 launches of a frame replay without host overhead.
+
+``infer_resident`` replays on a frame already in HBM; ``infer_host`` is the end-to-end call: pinned host
+image -> H2D -> graph -> D2H of the (B,K,2N+7) detections, double-buffered so the copy of frame i+1 overlaps
+the compute of frame i (the reference's ``images.to(device)`` / ``dets.cpu()``, base_detector.py:134,
+detectors/polydet.py:46).
+"""
+from __future__ import annotations
+
+import contextlib
+
+import torch
+
+from .. import decode as cdecode
+from .dla34 import PolydetDLA34, calibrate_random_init
+
+HEADS = {"hm": 8, "poly": 64, "pseudo_depth": 1, "reg": 2}
+
+
+class PolydetEngine:
+    def __init__(self, height=1024, width=2048, batch=1, dtype="bf16", K=100, rep="cartesian", heads=None,
+                 device="cuda:0", seed=317, calibrate=True, use_graph=True, n_slots=2):
+        self.device = torch.device(device)
+        self.dtype = dtype
+        self.K, self.rep = K, rep
+        self.heads = dict(heads or HEADS)
+        self.shape = (batch, 3, height, width)
+        torch.manual_seed(seed)
+        net = PolydetDLA34(self.heads).to(self.device).to(memory_format=torch.channels_last)
+        if calibrate:
+            calibrate_random_init(net, height, width, seed=seed)
+        self.net = net.eval()
+        self.n_dcn_per_frame = sum(1 for m in net.modules() if hasattr(m, "conv_offset_mask"))
+        self.stream = torch.cuda.Stream(self.device)
+        self.copy_stream = torch.cuda.Stream(self.device)   # H2D
+        self.d2h_stream = torch.cuda.Stream(self.device)    # D2H (separate, or it would serialise behind the next H2D)
+        self.use_graph = use_graph
+        n_poly = self.heads["poly"]
+        self.slots = []
+        for _ in range(n_slots):
+            self.slots.append(dict(
+                x=torch.zeros(self.shape, device=self.device).contiguous(memory_format=torch.channels_last),
+                dets=torch.zeros((batch, K, n_poly + 7), device=self.device),
+                host_out=torch.zeros((batch, K, n_poly + 7)).pin_memory(),
+                graph=None, h2d_done=torch.cuda.Event(), compute_done=torch.cuda.Event(), d2h_done=torch.cuda.Event()))
+        self._warm_and_capture()
+
+    # ------------------------------------------------------------------------------------------
+    def _autocast(self):
+        if self.dtype == "bf16":
+            return torch.autocast("cuda", dtype=torch.bfloat16)
+        return contextlib.nullcontext()
+
+    def _step(self, x):
+        """One frame: network -> sigmoid -> decode (the body of PolydetDetector.process)."""
+        with torch.no_grad(), self._autocast():
+            out = self.net(x)[-1]
+            hm = out["hm"].sigmoid_()
+            return cdecode.polydet_decode(hm, out["poly"], out["pseudo_depth"], reg=out.get("reg"), K=self.K, rep=self.rep)
+
+    def _warm_and_capture(self):
+        with torch.cuda.stream(self.stream):
+            for slot in self.slots:
+                for _ in range(2):  # fills the packed-weight cache, cuDNN plans, allocator pools
+                    slot["dets"].copy_(self._step(slot["x"]))
+            self.stream.synchronize()
+            if self.use_graph:
+                for slot in self.slots:
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=self.stream):
+                        slot["dets"].copy_(self._step(slot["x"]))
+                    slot["graph"] = g
+        self.stream.synchronize()
+
+    def _run_slot(self, slot):
+        if slot["graph"] is not None:
+            slot["graph"].replay()
+        else:
+            slot["dets"].copy_(self._step(slot["x"]))
+
+    # ------------------------------------------------------------------------------------------
+    def set_resident_frames(self, frames):
+        """frames: list of device tensors (B,3,H,W); copies them into the static slots."""
+        for slot, f in zip(self.slots, frames):
+            slot["x"].copy_(f)
+
+    def infer_resident(self, slot_idx=0):
+        """Enqueue one step on self.stream for the frame already resident in slot `slot_idx`."""
+        with torch.cuda.stream(self.stream):
+            self._run_slot(self.slots[slot_idx % len(self.slots)])
+
+    def infer_host_stream(self, host_frames, n_steps):
+        """End-to-end: n_steps frames taken round-robin from pinned `host_frames`; returns the last detections
+        (host tensor).  H2D of step i+1 overlaps compute of step i; every step's detections are copied back."""
+        nslots = len(self.slots)
+        for i in range(n_steps):
+            slot = self.slots[i % nslots]
+            src = host_frames[i % len(host_frames)]
+            with torch.cuda.stream(self.copy_stream):
+                # the slot's previous compute must have consumed x before it is overwritten
+                self.copy_stream.wait_event(slot["compute_done"])
+                slot["x"].copy_(src, non_blocking=True)
+                slot["h2d_done"].record(self.copy_stream)
+            with torch.cuda.stream(self.stream):
+                self.stream.wait_event(slot["h2d_done"])
+                self.stream.wait_event(slot["d2h_done"])     # previous D2H of this slot's dets finished
+                self._run_slot(slot)
+                slot["compute_done"].record(self.stream)
+            with torch.cuda.stream(self.d2h_stream):
+                self.d2h_stream.wait_event(slot["compute_done"])
+                slot["host_out"].copy_(slot["dets"], non_blocking=True)
+                slot["d2h_done"].record(self.d2h_stream)
+        self.copy_stream.synchronize()
+        self.stream.synchronize()
+        self.d2h_stream.synchronize()
+        return self.slots[(n_steps - 1) % nslots]["host_out"]
+
+    @property
+    def h2d_bytes_per_step(self):
+        b, c, h, w = self.shape
+        return b * c * h * w * 4
+
+    @property
+    def d2h_bytes_per_step(self):
+        return self.slots[0]["host_out"].numel() * 4
