@@ -229,7 +229,7 @@ template <> struct OutConv<float> {
 
 // ---------------------------------------------------------------------------------------- kernel
 template <typename T>
-__global__ void __maxnreg__(88) dcn_fwd_tc_kernel(const TcParams p) {
+__global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   constexpr bool kTF32 = sizeof(T) == 4;
   constexpr int kVec = Blend<T>::kVec;       // channels per 16 B
   constexpr int kChunk = ROW_BYTES / sizeof(T);  // channels per K chunk (64 bf16 / 32 fp32)
