@@ -20,7 +20,8 @@ PATH_AUTO, PATH_SIMT, PATH_TCGEN05 = 0, 1, 2
 
 EXPORTED_SYMBOLS = (
     "cpoly_abi_version", "cpoly_last_error", "cpoly_device_supports_tcgen05", "cpoly_dcn_tcgen05_eligible",
-    "cpoly_dcn_packed_weight_bytes", "cpoly_dcn_pack_weights", "cpoly_dcn_forward",
+    "cpoly_dcn_packed_weight_bytes", "cpoly_dcn_pack_weights", "cpoly_dcn_forward_workspace_bytes", "cpoly_dcn_forward",
+    "cpoly_idaup_upsample_forward",
     "cpoly_dcn_backward_workspace_bytes", "cpoly_dcn_backward", "cpoly_decode_workspace_bytes", "cpoly_decode",
 )
 
@@ -34,12 +35,19 @@ class DcnFwdArgs(Structure):
         "B", "Cin", "Cout", "H", "W", "kh", "kw", "stride_h", "stride_w", "pad_h", "pad_w", "dil_h", "dil_w",
         "deformable_groups", "dtype", "om_dtype", "mask_is_logit", "path")] + [
         ("x", Tensor4), ("offset", Tensor4), ("mask", Tensor4),
-        ("weight", c_void_p), ("bias", c_void_p), ("weight_packed", c_void_p), ("y", Tensor4)]
+        ("weight", c_void_p), ("bias", c_void_p), ("weight_packed", c_void_p), ("y", Tensor4),
+        ("out_scale", c_void_p), ("relu", c_int32), ("reserved0", c_int32),
+        ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
 
 
 class DcnBwdArgs(Structure):
     _fields_ = [("f", DcnFwdArgs), ("gout", Tensor4), ("gx", Tensor4), ("goffset", Tensor4), ("gmask", Tensor4),
                 ("gweight", c_void_p), ("gbias", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+
+
+class UpsampleArgs(Structure):
+    _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "f", "dtype")] + [
+        ("x", Tensor4), ("weight", c_void_p), ("skip", Tensor4), ("y", Tensor4)]
 
 
 class DecodeArgs(Structure):
@@ -69,6 +77,10 @@ def lib():
         L.cpoly_dcn_packed_weight_bytes.argtypes = [c_int32] * 5
         L.cpoly_dcn_pack_weights.restype = c_int32
         L.cpoly_dcn_pack_weights.argtypes = [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p]
+        L.cpoly_dcn_forward_workspace_bytes.restype = c_size_t
+        L.cpoly_dcn_forward_workspace_bytes.argtypes = [POINTER(DcnFwdArgs)]
+        L.cpoly_idaup_upsample_forward.restype = c_int32
+        L.cpoly_idaup_upsample_forward.argtypes = [POINTER(UpsampleArgs), c_void_p]
         L.cpoly_dcn_forward.restype = c_int32
         L.cpoly_dcn_forward.argtypes = [POINTER(DcnFwdArgs), c_void_p]
         L.cpoly_dcn_backward_workspace_bytes.restype = c_size_t
@@ -79,7 +91,7 @@ def lib():
         L.cpoly_decode_workspace_bytes.argtypes = [c_int32] * 5
         L.cpoly_decode.restype = c_int32
         L.cpoly_decode.argtypes = [POINTER(DecodeArgs), c_void_p]
-        if L.cpoly_abi_version() != 1:
+        if L.cpoly_abi_version() != 2:
             raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
         _lib = L
     return _lib

@@ -23,7 +23,7 @@ static int validate_dcn(const cpoly_dcn_fwd_args& a, bool need_y) {
                 "in_channels (%d) must be divisible by deformable_groups (%d)", a.Cin, a.deformable_groups);
   CPOLY_REQUIRE(a.dtype == CPOLY_F32 || a.dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", a.dtype);
   CPOLY_REQUIRE(a.om_dtype == CPOLY_F32 || a.om_dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported offset/mask dtype %d", a.om_dtype);
-  CPOLY_REQUIRE(a.x.ptr && a.offset.ptr && a.mask.ptr && a.weight, CPOLY_EINVAL, "NULL input pointer");
+  CPOLY_REQUIRE(a.x.ptr && a.offset.ptr && a.mask.ptr && (a.weight || a.weight_packed), CPOLY_EINVAL, "NULL input pointer");
   CPOLY_REQUIRE(!need_y || a.y.ptr, CPOLY_EINVAL, "NULL output pointer");
   const DcnGeom g = make_geom(a);
   CPOLY_REQUIRE(g.Ho > 0 && g.Wo > 0, CPOLY_EINVAL, "empty output (%d x %d)", g.Ho, g.Wo);
@@ -64,6 +64,11 @@ int cpoly_dcn_pack_weights(const float* weight, void* packed, int32_t Cin, int32
   return dcn_tc_pack_weights(weight, packed, Cin, Cout, kh, kw, dtype, reinterpret_cast<cudaStream_t>(stream));
 }
 
+size_t cpoly_dcn_forward_workspace_bytes(const cpoly_dcn_fwd_args* args) {
+  if (!args || !dcn_tc_eligible(*args)) return 256;
+  return dcn_tc_forward_workspace(*args);
+}
+
 int cpoly_dcn_forward(const cpoly_dcn_fwd_args* args, cpoly_stream_t stream) {
   CPOLY_REQUIRE(args, CPOLY_EINVAL, "NULL args");
   if (int rc = validate_dcn(*args, true)) return rc;
@@ -74,6 +79,7 @@ int cpoly_dcn_forward(const cpoly_dcn_fwd_args* args, cpoly_stream_t stream) {
     return dcn_forward_tc(*args, s);
   }
   if (args->path == CPOLY_PATH_AUTO && tc_ok) return dcn_forward_tc(*args, s);
+  CPOLY_REQUIRE(args->weight, CPOLY_EINVAL, "the generic path needs the dense fp32 weights");
   return dcn_forward_simt(*args, s);
 }
 
@@ -85,7 +91,7 @@ size_t cpoly_dcn_backward_workspace_bytes(const cpoly_dcn_bwd_args* args) {
 int cpoly_dcn_backward(const cpoly_dcn_bwd_args* args, cpoly_stream_t stream) {
   CPOLY_REQUIRE(args, CPOLY_EINVAL, "NULL args");
   if (int rc = validate_dcn(args->f, false)) return rc;
-  CPOLY_REQUIRE(args->gout.ptr, CPOLY_EINVAL, "NULL grad_output");
+  CPOLY_REQUIRE(args->gout.ptr && args->f.weight, CPOLY_EINVAL, "NULL grad_output / weight");
   return dcn_backward_simt(*args, reinterpret_cast<cudaStream_t>(stream));
 }
 
@@ -107,6 +113,15 @@ int cpoly_decode(const cpoly_decode_args* a, cpoly_stream_t stream) {
   CPOLY_REQUIRE(a->heat.ptr && a->polys.ptr && a->depth.ptr && a->out, CPOLY_EINVAL, "NULL pointer");
   if (a->B == 0) return CPOLY_OK;
   return decode_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int cpoly_idaup_upsample_forward(const cpoly_upsample_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->C > 0 && a->H > 0 && a->W > 0 && a->f >= 1, CPOLY_EINVAL, "bad upsample dims");
+  CPOLY_REQUIRE(a->dtype == CPOLY_F32 || a->dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", a->dtype);
+  CPOLY_REQUIRE(a->x.ptr && a->weight && a->y.ptr, CPOLY_EINVAL, "NULL pointer");
+  if (a->B == 0) return CPOLY_OK;
+  return idaup_upsample_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -74,7 +74,8 @@ __device__ __forceinline__ float sample_channel(const T* xp, const PixelTap& pt,
 template <typename T>
 __global__ void __launch_bounds__(NT) dcn_fwd_simt_kernel(DcnGeom g, cpoly_tensor4 x, cpoly_tensor4 offset,
                                                           cpoly_tensor4 mask, const float* __restrict__ weight,
-                                                          const float* __restrict__ bias, cpoly_tensor4 y) {
+                                                          const float* __restrict__ bias, cpoly_tensor4 y,
+                                                          const float* __restrict__ out_scale, int relu) {
   __shared__ PixelTap taps[BM];
   __shared__ float As[BK][BM + 4];
   __shared__ float Bs[BK][BN + 4];
@@ -132,7 +133,11 @@ __global__ void __launch_bounds__(NT) dcn_fwd_simt_kernel(DcnGeom g, cpoly_tenso
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int o = o0 + tx * 4 + j;
-      if (o < g.Cout) st_from_float(yp + ybase + (int64_t)o * y.sc, acc[i][j] + (bias ? __ldg(bias + o) : 0.f));
+      if (o < g.Cout) {
+        float v = fmaf(acc[i][j], out_scale ? __ldg(out_scale + o) : 1.f, bias ? __ldg(bias + o) : 0.f);
+        if (relu) v = fmaxf(v, 0.f);
+        st_from_float(yp + ybase + (int64_t)o * y.sc, v);
+      }
     }
   }
 }
@@ -414,9 +419,9 @@ int dcn_forward_simt(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   if (npix == 0) return CPOLY_OK;
   dim3 grid((unsigned)((npix + BM - 1) / BM), (unsigned)((g.Cout + BN - 1) / BN));
   if (a.dtype == CPOLY_BF16)
-    dcn_fwd_simt_kernel<__nv_bfloat16><<<grid, NT, 0, stream>>>(g, a.x, a.offset, a.mask, a.weight, a.bias, a.y);
+    dcn_fwd_simt_kernel<__nv_bfloat16><<<grid, NT, 0, stream>>>(g, a.x, a.offset, a.mask, a.weight, a.bias, a.y, a.out_scale, a.relu);
   else
-    dcn_fwd_simt_kernel<float><<<grid, NT, 0, stream>>>(g, a.x, a.offset, a.mask, a.weight, a.bias, a.y);
+    dcn_fwd_simt_kernel<float><<<grid, NT, 0, stream>>>(g, a.x, a.offset, a.mask, a.weight, a.bias, a.y, a.out_scale, a.relu);
   return check_launch("dcn_fwd_simt_kernel");
 }
 

@@ -5,30 +5,36 @@
 // src/lib/models/networks/DCNv2).  Upstream materialises columns[9*Cin, H*W] in HBM (9x the input)
 // and calls cuBLAS SGEMM; here the column tile never leaves the SM.
 //
-//   out[px, o] = bias[o] + sum_{tap, c} A[px, (tap, c)] * W[o, c, tap],   A = mask * bilinear(x, p_tap)
+//   out[px, o] = act(scale[o] * sum_{tap, c} A[px, (tap, c)] * W[o, c, tap] + bias[o]),  A = mask * bilinear(x, p_tap)
 //
-// Persistent, warp-specialised CTA (one per SM), 128-pixel tiles (8 rows x 16 columns of the image so
-// that neighbouring pixels share bilinear corners in L1):
+// Persistent, warp-specialised CTA (one per SM).  A work item is (128-pixel tile, tap group): tiles are
+// 8 rows x 16 columns of the image so that neighbouring pixels share bilinear corners in L1; the 9 taps are
+// processed by one item (big maps) or split over 3 / 9 items whose fp32 partial sums are combined by a
+// second, fixed-order kernel (small maps, which could not otherwise fill 148 SMs).
 //
-//   warps 0-3   epilogue   tcgen05.ld accumulator rows -> +bias -> bf16/fp32 -> NHWC global stores
+//   warps 0-3   epilogue   tcgen05.ld accumulator rows -> scale/bias/ReLU -> bf16/fp32 NHWC stores (or fp32 partials)
 //   warp  4     B loader   one thread: cp.async.bulk (TMA engine, UBLKCP) of pre-swizzled weight chunks
 //   warp  5     MMA        TMEM alloc; one thread issues tcgen05.mma (M=128, N=Cout, K=16 bf16 / 8 tf32)
-//   warps 6..   samplers   per tile: stage (corner offsets, mask*bilinear weights) of all 9 taps in smem,
-//                          then per (tap, 128-byte channel chunk) gather 4 corners with 16-byte loads, blend in
-//                          fp32 and write the A tile straight into the 128B-swizzled K-major UMMA layout
+//   warps 6..   samplers   per item: stage (corner offsets, mask*bilinear weights) of the item's taps in smem,
+//                          then per (tap, 128-byte channel chunk) gather 4 corners with 16-byte loads, blend
+//                          (packed bf16x2 FMAs / fp32 FMAs) and write the A tile straight into the 128B-swizzled
+//                          K-major UMMA layout
 //
 // Pipelines: smem ring (fullA/fullB/empty mbarriers) between samplers+loader and the MMA thread; two TMEM
-// accumulators (tmem_full/tmem_empty) between the MMA thread and the epilogue, so the epilogue of tile t
-// overlaps the MMAs of tile t+1.  Every mbarrier wait has a clock-based timeout that traps instead of
-// hanging the GPU.
-#include "common.cuh"
+// accumulators (tmem_full/tmem_empty) between the MMA thread and the epilogue, so the epilogue of item t
+// overlaps the MMAs of item t+1.  Every mbarrier wait is a hardware-suspended try_wait with a clock-based
+// timeout that traps instead of hanging the GPU.
+#include <stdlib.h>
+
+#include "tc_common.cuh"
 
 namespace cpoly {
 namespace {
 
+using namespace tc;
+
 constexpr int TILE_H = 8, TILE_W = 16, TILE_PX = TILE_H * TILE_W;  // 128 = UMMA M
 constexpr int NUM_TAPS = 9;
-constexpr int ROW_BYTES = 128;                 // one swizzle row: 64 bf16 or 32 fp32 channels
 constexpr int A_STAGE_BYTES = TILE_PX * ROW_BYTES;  // 16 KB
 constexpr int MAX_STAGES = 6;
 constexpr int EPI_WARPS = 4;
@@ -38,184 +44,71 @@ constexpr int NS = SAMPLER_WARPS * 32;         // sampler threads
 constexpr int NTHREADS = (SAMPLER_WARP0 + SAMPLER_WARPS) * 32;
 constexpr int ROWS_PER_PASS = NS / 8;          // 8 lanes x 16 B cover one 128-byte row
 constexpr int PASSES = TILE_PX / ROWS_PER_PASS;
-constexpr long long WAIT_TIMEOUT_CYCLES = 4000000000LL;  // ~2 s: trap instead of hanging the box
+constexpr int MAX_ITEMS = (NUM_TAPS * TILE_PX + NS - 1) / NS;  // (pixel, tap) parameter items per sampler thread
 
 // shared-memory map (dynamic, 1024-byte aligned)
 constexpr int SMEM_BAR_OFF = 0;        // mbarriers + tmem pointer
-constexpr int SMEM_BIAS_OFF = 1024;    // Cout floats (<= 256)
-constexpr int SMEM_PARAM_OFF = 2048;   // NUM_TAPS * TILE_PX * 32 B
-constexpr int SMEM_PARAM_BYTES = NUM_TAPS * TILE_PX * 32;
-constexpr int SMEM_STAGE_OFF = ((SMEM_PARAM_OFF + SMEM_PARAM_BYTES + 1023) / 1024) * 1024;
+constexpr int SMEM_VEC_OFF = 1024;     // scale[256] + bias[256] floats
+constexpr int SMEM_POFF_OFF = 3072;    // corner offsets: NUM_TAPS * TILE_PX * 16 B
+constexpr int SMEM_PW_OFF = SMEM_POFF_OFF + NUM_TAPS * TILE_PX * 16;  // corner weights: same size
+constexpr int SMEM_STAGE_OFF = ((SMEM_PW_OFF + NUM_TAPS * TILE_PX * 16 + 1023) / 1024) * 1024;
 constexpr int SMEM_LIMIT = 226 * 1024;  // 227 KB per CTA minus the alignment slack
-
-struct TapParam {   // 32 bytes: what a sampler needs for one (pixel, tap)
-  int off[4];       // element offset of the corner's channel vector in x (dead corner -> 0, weight 0)
-  float w[4];       // mask * bilinear weight
-};
 
 struct TcParams {
   const void* x;
   cpoly_tensor4 offset, mask;
   const void* wpacked;
   const float* bias;
+  const float* scale;
   void* y;
+  float* partial;  // [split][B*H*W][Cout] fp32 when split > 1
   int B, Cin, Cout, H, W;
-  int om_dtype, mask_is_logit;
-  int tiles_x, tiles_y, num_tiles;
+  int om_dtype, mask_is_logit, relu;
+  int tiles_x, tiles_y, num_tiles, num_items;
+  int split, taps_per_item;
   int nchunk;      // channel chunks per tap
   int stages, b_stage_bytes, stage_bytes;
   int acc_cols, tmem_cols;
 };
 
-// ------------------------------------------------------------------------------------------ PTX
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.b32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok;
-}
-__device__ __noinline__ void mbar_timeout(uint32_t bar, uint32_t parity) {
-  printf("cpoly dcn_tc: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
-  __trap();
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > WAIT_TIMEOUT_CYCLES) mbar_timeout(bar, parity);
-  }
-}
-__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-               "l"(src), "r"(bytes), "r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
-
-// K-major, 128-byte-swizzled operand tile: rows of 128 B, 8-row groups 1024 B apart (SBO), version 1.
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr & 0x3ffffu) >> 4);
-  d |= (uint64_t)1 << 16;            // leading byte offset (unused for swizzled K-major)
-  d |= (uint64_t)(1024 >> 4) << 32;  // stride byte offset
-  d |= (uint64_t)1 << 46;            // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;            // SWIZZLE_128B
-  return d;
-}
-
-template <bool kTF32>
-__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  if (kTF32)
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-  else
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-__device__ __forceinline__ uint4 ldg16(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
-__device__ __forceinline__ void sts16(uint32_t addr, uint4 v) {
-  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-__device__ __forceinline__ uint32_t to_tf32(float f) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(f));
-  return r;
-}
-
 // ---- blend of the four corner vectors (16 B each) into one 16-B piece of the A row ----------------
+// bf16: weights arrive as bf16x2 pairs (w, w); products and sums are packed bf16x2 FMAs — half the issue slots of
+// unpack + fp32 FMA + repack, and the A operand is rounded to bf16 anyway (tolerance 1e-2 in bf16 mode).
+// fp32: fp32 FMAs, result rounded to tf32 (round-to-nearest) for kind::tf32.
 template <typename T> struct Blend;
 template <> struct Blend<__nv_bfloat16> {
   static constexpr int kVec = 8;  // channels per 16 bytes
-  __device__ static __forceinline__ uint4 run(const uint4 (&c)[4], const float (&w)[4]) {
+  __device__ static __forceinline__ uint32_t weight(float w) { return pack_bf16x2(w, w); }
+  __device__ static __forceinline__ uint4 run(const uint4 (&c)[4], const uint4 w) {
     uint4 out;
-    const uint32_t* cw[4] = {&c[0].x, &c[1].x, &c[2].x, &c[3].x};
-    uint32_t* o = &out.x;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float lo = 0.f, hi = 0.f;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const uint32_t word = cw[q][j];
-        lo = fmaf(w[q], __uint_as_float(word << 16), lo);
-        hi = fmaf(w[q], __uint_as_float(word & 0xffff0000u), hi);
-      }
-      const __nv_bfloat162 pk = __floats2bfloat162_rn(lo, hi);
-      o[j] = *reinterpret_cast<const uint32_t*>(&pk);
-    }
+    out.x = bf16x2_fma(w.w, c[3].x, bf16x2_fma(w.z, c[2].x, bf16x2_fma(w.y, c[1].x, bf16x2_mul(w.x, c[0].x))));
+    out.y = bf16x2_fma(w.w, c[3].y, bf16x2_fma(w.z, c[2].y, bf16x2_fma(w.y, c[1].y, bf16x2_mul(w.x, c[0].y))));
+    out.z = bf16x2_fma(w.w, c[3].z, bf16x2_fma(w.z, c[2].z, bf16x2_fma(w.y, c[1].z, bf16x2_mul(w.x, c[0].z))));
+    out.w = bf16x2_fma(w.w, c[3].w, bf16x2_fma(w.z, c[2].w, bf16x2_fma(w.y, c[1].w, bf16x2_mul(w.x, c[0].w))));
     return out;
   }
 };
 template <> struct Blend<float> {
   static constexpr int kVec = 4;
-  __device__ static __forceinline__ uint4 run(const uint4 (&c)[4], const float (&w)[4]) {
+  __device__ static __forceinline__ uint32_t weight(float w) { return __float_as_uint(w); }
+  __device__ static __forceinline__ uint4 run(const uint4 (&c)[4], const uint4 w) {
+    const float w0 = __uint_as_float(w.x), w1 = __uint_as_float(w.y), w2 = __uint_as_float(w.z), w3 = __uint_as_float(w.w);
     uint4 out;
-    const uint32_t* cw[4] = {&c[0].x, &c[1].x, &c[2].x, &c[3].x};
-    uint32_t* o = &out.x;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float v = 0.f;
-#pragma unroll
-      for (int q = 0; q < 4; ++q) v = fmaf(w[q], __uint_as_float(cw[q][j]), v);
-      o[j] = to_tf32(v);
-    }
+#define CPOLY_BLEND1(f) \
+  out.f = to_tf32(fmaf(w3, __uint_as_float(c[3].f), fmaf(w2, __uint_as_float(c[2].f), fmaf(w1, __uint_as_float(c[1].f), w0 * __uint_as_float(c[0].f)))))
+    CPOLY_BLEND1(x); CPOLY_BLEND1(y); CPOLY_BLEND1(z); CPOLY_BLEND1(w);
+#undef CPOLY_BLEND1
     return out;
   }
 };
 
 template <typename T> struct OutConv;
 template <> struct OutConv<__nv_bfloat16> {
-  // 16 fp32 accumulators -> 32 bytes
+  // 16 fp32 values -> 32 bytes
   __device__ static __forceinline__ void store(__nv_bfloat16* dst, const float (&v)[16]) {
     uint4 a, b;
-    uint32_t* pa = &a.x;
-    uint32_t* pb = &b.x;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const __nv_bfloat162 p0 = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
-      const __nv_bfloat162 p1 = __floats2bfloat162_rn(v[8 + 2 * j], v[8 + 2 * j + 1]);
-      pa[j] = *reinterpret_cast<const uint32_t*>(&p0);
-      pb[j] = *reinterpret_cast<const uint32_t*>(&p1);
-    }
+    a.x = pack_bf16x2(v[0], v[1]);  a.y = pack_bf16x2(v[2], v[3]);   a.z = pack_bf16x2(v[4], v[5]);   a.w = pack_bf16x2(v[6], v[7]);
+    b.x = pack_bf16x2(v[8], v[9]);  b.y = pack_bf16x2(v[10], v[11]); b.z = pack_bf16x2(v[12], v[13]); b.w = pack_bf16x2(v[14], v[15]);
     reinterpret_cast<uint4*>(dst)[0] = a;
     reinterpret_cast<uint4*>(dst)[1] = b;
   }
@@ -227,25 +120,34 @@ template <> struct OutConv<float> {
   }
 };
 
+__device__ __forceinline__ void item_coords(const TcParams& p, int item, int& b, int& ty0, int& tx0, int& tap0) {
+  const int tile = item / p.split;
+  tap0 = (item - tile * p.split) * p.taps_per_item;
+  const int tiles_per_img = p.tiles_x * p.tiles_y;
+  b = tile / tiles_per_img;
+  const int trem = tile - b * tiles_per_img;
+  const int tyi = trem / p.tiles_x;
+  ty0 = tyi * TILE_H;
+  tx0 = (trem - tyi * p.tiles_x) * TILE_W;
+}
+
 // ---------------------------------------------------------------------------------------- kernel
 template <typename T>
 __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   constexpr bool kTF32 = sizeof(T) == 4;
-  constexpr int kVec = Blend<T>::kVec;       // channels per 16 B
-  constexpr int kChunk = ROW_BYTES / sizeof(T);  // channels per K chunk (64 bf16 / 32 fp32)
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operand tiles need 1024-byte alignment: align the window ourselves (+1 KB is requested)
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const uint32_t smem_base = smem_u32(smem);
-  // barrier indices
   const uint32_t bar_fullA = smem_base + SMEM_BAR_OFF;                 // [MAX_STAGES]
   const uint32_t bar_fullB = bar_fullA + 8 * MAX_STAGES;               // [MAX_STAGES]
   const uint32_t bar_empty = bar_fullB + 8 * MAX_STAGES;               // [MAX_STAGES]
   const uint32_t bar_tfull = bar_empty + 8 * MAX_STAGES;               // [2]
   const uint32_t bar_tempty = bar_tfull + 16;                          // [2]
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SMEM_BAR_OFF + 8 * (3 * MAX_STAGES + 4));
-  float* bias_s = reinterpret_cast<float*>(smem + SMEM_BIAS_OFF);
-  TapParam* params = reinterpret_cast<TapParam*>(smem + SMEM_PARAM_OFF);
+  float* scale_s = reinterpret_cast<float*>(smem + SMEM_VEC_OFF);
+  float* bias_s = scale_s + 256;
+  const uint32_t poff_s = smem_base + SMEM_POFF_OFF, pw_s = smem_base + SMEM_PW_OFF;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -260,41 +162,37 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       mbar_init(bar_tfull + 8 * a, 1);
       mbar_init(bar_tempty + 8 * a, EPI_WARPS * 32);
     }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    fence_mbar_init();
   }
-  if (warp == 5) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"((uint32_t)p.tmem_cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  if (warp == 5) tmem_alloc(smem_u32(tmem_ptr_smem), (uint32_t)p.tmem_cols);
+  for (int i = threadIdx.x; i < p.Cout; i += NTHREADS) {
+    scale_s[i] = p.scale ? __ldg(p.scale + i) : 1.f;
+    bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
   }
-  for (int i = threadIdx.x; i < p.Cout; i += NTHREADS) bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-
-  const int chunks_per_tile = NUM_TAPS * p.nchunk;
-  const int tiles_per_img = p.tiles_x * p.tiles_y;
+  const int chunks_per_item = p.taps_per_item * p.nchunk;
+  const uint32_t nstages = (uint32_t)p.stages;
 
   if (warp >= SAMPLER_WARP0) {
     // =========================================================================== samplers
     const int st = threadIdx.x - SAMPLER_WARP0 * 32;
     const int row_in_pass = st >> 3, cg = st & 7;
-    const T* xg = reinterpret_cast<const T*>(p.x);
-    constexpr int ITEMS = (NUM_TAPS * TILE_PX + NS - 1) / NS;  // (pixel, tap) items per thread and tile
-    float raw_dy[ITEMS], raw_dx[ITEMS], raw_m[ITEMS];
-    // raw offsets / mask of one tile -> registers (issued one tile ahead so the latency hides behind sampling)
-    auto fetch_raw = [&](int tile) {
-      const int b = tile / tiles_per_img;
-      const int trem = tile - b * tiles_per_img;
-      const int ty0 = (trem / p.tiles_x) * TILE_H, tx0 = (trem % p.tiles_x) * TILE_W;
+    const int n_param = p.taps_per_item * TILE_PX;
+    float raw_dy[MAX_ITEMS], raw_dx[MAX_ITEMS], raw_m[MAX_ITEMS];
+    // raw offsets / mask of one item -> registers (issued one item ahead so the latency hides behind sampling)
+    auto fetch_raw = [&](int item) {
+      int b, ty0, tx0, tap0;
+      item_coords(p, item, b, ty0, tx0, tap0);
 #pragma unroll
-      for (int i = 0; i < ITEMS; ++i) {
-        const int item = st + i * NS;
-        const int k = item / TILE_PX, r = item - k * TILE_PX;
-        const int y = ty0 + r / TILE_W, x = tx0 + r % TILE_W;
+      for (int i = 0; i < MAX_ITEMS; ++i) {
+        const int e = st + i * NS;
+        const int k = tap0 + (e >> 7), r = e & (TILE_PX - 1);
+        const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
         raw_dy[i] = raw_dx[i] = raw_m[i] = 0.f;
-        if (item < NUM_TAPS * TILE_PX && y < p.H && x < p.W) {
+        if (e < n_param && y < p.H && x < p.W) {
           const int64_t opix = (int64_t)b * p.offset.sb + (int64_t)y * p.offset.sh + (int64_t)x * p.offset.sw;
           raw_dy[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k) * p.offset.sc, p.om_dtype);
           raw_dx[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k + 1) * p.offset.sc, p.om_dtype);
@@ -302,110 +200,124 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
         }
       }
     };
-    uint32_t it = 0;
-    if ((int)blockIdx.x < p.num_tiles) fetch_raw(blockIdx.x);
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-      const int b = tile / tiles_per_img;
-      const int trem = tile - b * tiles_per_img;
-      const int ty0 = (trem / p.tiles_x) * TILE_H, tx0 = (trem % p.tiles_x) * TILE_W;
-      named_bar_sync(1, NS);  // everyone finished reading the previous tile's params
+    RingCursor rc;
+    if ((int)blockIdx.x < p.num_items) fetch_raw(blockIdx.x);
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      int b, ty0, tx0, tap0;
+      item_coords(p, item, b, ty0, tx0, tap0);
+      const int img_base = b * p.H * p.W * p.Cin;   // element offset; bytes < 2^32 (checked on the host)
+      named_bar_sync(1, NS);  // everyone finished reading the previous item's params
 #pragma unroll
-      for (int i = 0; i < ITEMS; ++i) {
-        const int item = st + i * NS;
-        if (item >= NUM_TAPS * TILE_PX) break;
-        const int k = item / TILE_PX, r = item - k * TILE_PX;
-        const int y = ty0 + r / TILE_W, x = tx0 + r % TILE_W;
-        TapParam tp;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) { tp.off[q] = 0; tp.w[q] = 0.f; }
+      for (int i = 0; i < MAX_ITEMS; ++i) {
+        const int e = st + i * NS;
+        if (e >= n_param) continue;
+        const int kl = e >> 7, k = tap0 + kl, r = e & (TILE_PX - 1);
+        const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
+        uint4 po = make_uint4(0u, 0u, 0u, 0u), pw = make_uint4(0u, 0u, 0u, 0u);  // dead corner: offset 0, weight 0
         if (y < p.H && x < p.W) {
           const float m = p.mask_is_logit ? sigmoidf_accurate(raw_m[i]) : raw_m[i];
-          const float py = (float)(y - 1 + k / 3) + raw_dy[i];
-          const float px = (float)(x - 1 + k % 3) + raw_dx[i];
-          const TapSample t = make_tap(py, px, p.H, p.W, (int64_t)b * p.H * p.W * p.Cin, (int64_t)p.W * p.Cin, (int64_t)p.Cin);
-#pragma unroll
-          for (int q = 0; q < 4; ++q)
-            if (t.off[q] >= 0) { tp.off[q] = (int)t.off[q]; tp.w[q] = t.w[q] * m; }
+          const int ki = k / 3;
+          const float py = (float)(y - 1 + ki) + raw_dy[i];
+          const float px = (float)(x - 1 + (k - 3 * ki)) + raw_dx[i];
+          if (py > -1.0f && px > -1.0f && py < (float)p.H && px < (float)p.W) {
+            const float fy = floorf(py), fx = floorf(px);
+            const int y0 = (int)fy, x0 = (int)fx;
+            const float ly = py - fy, lx = px - fx, hy = 1.0f - ly, hx = 1.0f - lx;
+            const bool vy0 = y0 >= 0, vy1 = y0 + 1 <= p.H - 1, vx0 = x0 >= 0, vx1 = x0 + 1 <= p.W - 1;
+            const uint32_t pixb = (uint32_t)p.Cin * (uint32_t)sizeof(T), rowb = (uint32_t)p.W * pixb;
+            const uint32_t o00 = (uint32_t)img_base * (uint32_t)sizeof(T) + (uint32_t)(y0 * p.W + x0) * pixb;  // may wrap for dead corners
+            if (vy0 && vx0) { po.x = o00;               pw.x = Blend<T>::weight(hy * hx * m); }
+            if (vy0 && vx1) { po.y = o00 + pixb;        pw.y = Blend<T>::weight(hy * lx * m); }
+            if (vy1 && vx0) { po.z = o00 + rowb;        pw.z = Blend<T>::weight(ly * hx * m); }
+            if (vy1 && vx1) { po.w = o00 + rowb + pixb; pw.w = Blend<T>::weight(ly * lx * m); }
+          }
         }
-        uint4* dst = reinterpret_cast<uint4*>(&params[k * TILE_PX + r]);
-        dst[0] = make_uint4((uint32_t)tp.off[0], (uint32_t)tp.off[1], (uint32_t)tp.off[2], (uint32_t)tp.off[3]);
-        dst[1] = make_uint4(__float_as_uint(tp.w[0]), __float_as_uint(tp.w[1]), __float_as_uint(tp.w[2]), __float_as_uint(tp.w[3]));
+        sts16(poff_s + (uint32_t)(kl * TILE_PX + r) * 16u, po);
+        sts16(pw_s + (uint32_t)(kl * TILE_PX + r) * 16u, pw);
       }
       named_bar_sync(1, NS);
-      if (tile + (int)gridDim.x < p.num_tiles) fetch_raw(tile + gridDim.x);
-      for (int k = 0; k < NUM_TAPS; ++k) {
-        for (int cc = 0; cc < p.nchunk; ++cc, ++it) {
-          const uint32_t s = it % (uint32_t)p.stages, ph = (it / (uint32_t)p.stages) & 1u;
-          const int chan = cc * kChunk + cg * kVec;
-          // phase 1: every corner load of this thread's rows goes out before anything is consumed
-          uint4 c[PASSES][4];
-          uint4 pw[PASSES];
+      if (item + (int)gridDim.x < p.num_items) fetch_raw(item + gridDim.x);
+      // Rolling software pipeline over the item's chunks: the corner loads of chunk q+1 are issued while chunk q
+      // is blended, so every sampler warp keeps one pass (4 x 16 B per thread) in flight at all times instead of
+      // alternating between a load phase and a blend phase.
+      uint4 c[PASSES][4], pw[PASSES];
+      const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x);
+      auto issue = [&](uint32_t pidx, uint32_t cbyte, int pass) {   // params + corner loads of one (chunk, pass)
+        const uint32_t idx = pidx + (uint32_t)(pass * ROWS_PER_PASS) * 16u;
+        const uint4 po = lds16(poff_s + idx);   // BYTE offsets of the four corner vectors
+        pw[pass] = lds16(pw_s + idx);
+        c[pass][0] = ldg16(xb + (po.x + cbyte));
+        c[pass][1] = ldg16(xb + (po.y + cbyte));
+        c[pass][2] = ldg16(xb + (po.z + cbyte));
+        c[pass][3] = ldg16(xb + (po.w + cbyte));
+      };
+      // (tap, channel chunk) cursor of the NEXT chunk to issue: parameter row index and channel byte offset
+      const uint32_t cbyte0 = (uint32_t)(cg * 16);
+      uint32_t n_pidx = (uint32_t)row_in_pass * 16u, n_cbyte = cbyte0;
+      int n_cc = 0;
+      auto next_chunk = [&]() {
+        n_cbyte += ROW_BYTES;
+        if (++n_cc == p.nchunk) { n_cc = 0; n_cbyte = cbyte0; n_pidx += TILE_PX * 16u; }
+      };
 #pragma unroll
-          for (int pass = 0; pass < PASSES; ++pass) {
-            const int r = pass * ROWS_PER_PASS + row_in_pass;
-            const uint4* pp = reinterpret_cast<const uint4*>(&params[k * TILE_PX + r]);
-            const uint4 po = pp[0];
-            pw[pass] = pp[1];
-            c[pass][0] = ldg16(xg + (int)po.x + chan);
-            c[pass][1] = ldg16(xg + (int)po.y + chan);
-            c[pass][2] = ldg16(xg + (int)po.z + chan);
-            c[pass][3] = ldg16(xg + (int)po.w + chan);
-          }
-          mbar_wait(bar_empty + 8 * s, ph ^ 1u);
-          const uint32_t a_base = smem_base + SMEM_STAGE_OFF + s * p.stage_bytes;
-          // phase 2: blend and write the swizzled A rows
+      for (int pass = 0; pass < PASSES; ++pass) issue(n_pidx, n_cbyte, pass);
+      next_chunk();
+      for (int q = 0; q < chunks_per_item; ++q) {
+        mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u);
+        const uint32_t a_base = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
+        const bool more = q + 1 < chunks_per_item;
 #pragma unroll
-          for (int pass = 0; pass < PASSES; ++pass) {
-            const int r = pass * ROWS_PER_PASS + row_in_pass;
-            const float w[4] = {__uint_as_float(pw[pass].x), __uint_as_float(pw[pass].y), __uint_as_float(pw[pass].z),
-                                __uint_as_float(pw[pass].w)};
-            const uint4 v = Blend<T>::run(c[pass], w);
-            sts16(a_base + r * ROW_BYTES + ((cg ^ (r & 7)) << 4), v);
-          }
-          fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar_fullA + 8 * s);
+        for (int pass = 0; pass < PASSES; ++pass) {
+          const int r = pass * ROWS_PER_PASS + row_in_pass;
+          sts16(a_base + r * ROW_BYTES + ((cg ^ (r & 7)) << 4), Blend<T>::run(c[pass], pw[pass]));
+          if (more) issue(n_pidx, n_cbyte, pass);
         }
+        next_chunk();
+        fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_fullA + 8 * rc.s);
+        rc.advance(nstages);
       }
     }
   } else if (warp == 4) {
     // =========================================================================== weight loader
     if (lane == 0) {
-      uint32_t it = 0;
+      RingCursor rc;
       const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.wpacked);
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        for (int q = 0; q < chunks_per_tile; ++q, ++it) {
-          const uint32_t s = it % (uint32_t)p.stages, ph = (it / (uint32_t)p.stages) & 1u;
-          mbar_wait(bar_empty + 8 * s, ph ^ 1u);
-          mbar_arrive_expect_tx(bar_fullB + 8 * s, (uint32_t)p.b_stage_bytes);
-          bulk_copy_g2s(smem_base + SMEM_STAGE_OFF + s * p.stage_bytes + A_STAGE_BYTES, wsrc + (size_t)q * p.b_stage_bytes,
-                        (uint32_t)p.b_stage_bytes, bar_fullB + 8 * s);
+      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+        const int q0 = (item % p.split) * chunks_per_item;
+        for (int q = 0; q < chunks_per_item; ++q) {
+          mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u);
+          mbar_arrive_expect_tx(bar_fullB + 8 * rc.s, (uint32_t)p.b_stage_bytes);
+          bulk_copy_g2s(smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes + A_STAGE_BYTES,
+                        wsrc + (size_t)(q0 + q) * p.b_stage_bytes, (uint32_t)p.b_stage_bytes, bar_fullB + 8 * rc.s);
+          rc.advance(nstages);
         }
       }
     }
   } else if (warp == 5) {
     // =========================================================================== MMA issuer
     if (lane == 0) {
-      const uint32_t idesc = (1u << 4) | ((kTF32 ? 2u : 1u) << 7) | ((kTF32 ? 2u : 1u) << 10) |
-                             ((uint32_t)(p.Cout >> 3) << 17) | ((uint32_t)(TILE_PX >> 4) << 24);
-      uint32_t it = 0, tcount = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+      const uint32_t idesc = umma_idesc(kTF32, TILE_PX, p.Cout);
+      RingCursor rc;
+      uint32_t tcount = 0;
+      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++tcount) {
         const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
         mbar_wait(bar_tempty + 8 * acc, accph ^ 1u);  // epilogue drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.acc_cols;
-        for (int q = 0; q < chunks_per_tile; ++q, ++it) {
-          const uint32_t s = it % (uint32_t)p.stages, ph = (it / (uint32_t)p.stages) & 1u;
-          mbar_wait(bar_fullA + 8 * s, ph);
-          mbar_wait(bar_fullB + 8 * s, ph);
+        for (int q = 0; q < chunks_per_item; ++q) {
+          mbar_wait(bar_fullA + 8 * rc.s, rc.ph);
+          mbar_wait(bar_fullB + 8 * rc.s, rc.ph);
           tc_fence_after();
-          const uint32_t a_addr = smem_base + SMEM_STAGE_OFF + s * p.stage_bytes;
+          const uint32_t a_addr = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
           const uint64_t adesc = umma_desc_sw128(a_addr);
           const uint64_t bdesc = umma_desc_sw128(a_addr + A_STAGE_BYTES);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)  // 4 x 32 bytes of K per 128-byte row
             umma<kTF32>(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (q | kk) != 0 ? 1u : 0u);
-          umma_commit(bar_empty + 8 * s);          // frees the smem stage when these MMAs retire
+          umma_commit(bar_empty + 8 * rc.s);       // frees the smem stage when these MMAs retire
+          rc.advance(nstages);
         }
         umma_commit(bar_tfull + 8 * acc);          // accumulator complete -> epilogue
       }
@@ -413,27 +325,46 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   } else {
     // =========================================================================== epilogue (warps 0-3)
     T* yg = reinterpret_cast<T*>(p.y);
+    const int64_t npix = (int64_t)p.B * p.H * p.W;
     uint32_t tcount = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++tcount) {
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++tcount) {
       const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
-      const int b = tile / tiles_per_img;
-      const int trem = tile - b * tiles_per_img;
+      int b, ty0, tx0, tap0;
+      item_coords(p, item, b, ty0, tx0, tap0);
       const int r = warp * 32 + lane;
-      const int y = (trem / p.tiles_x) * TILE_H + r / TILE_W, x = (trem % p.tiles_x) * TILE_W + r % TILE_W;
+      const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
       const bool valid = (y < p.H) && (x < p.W);
-      T* yrow = yg + (((int64_t)b * p.H + y) * p.W + x) * p.Cout;
+      const int64_t pix = ((int64_t)b * p.H + y) * p.W + x;
       mbar_wait(bar_tfull + 8 * acc, accph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + acc * (uint32_t)p.acc_cols;
-      for (int c0 = 0; c0 < p.Cout; c0 += 16) {
-        uint32_t raw[16];
-        tmem_ld16(t_row + (uint32_t)c0, raw);
-        tmem_ld_wait();
-        if (valid) {
-          float v[16];
+      if (p.split == 1) {
+        T* yrow = yg + pix * p.Cout;
+        for (int c0 = 0; c0 < p.Cout; c0 += 16) {
+          uint32_t raw[16];
+          tmem_ld16(t_row + (uint32_t)c0, raw);
+          tmem_ld_wait();
+          if (valid) {
+            float v[16];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(raw[j]) + bias_s[c0 + j];
-          OutConv<T>::store(yrow + c0, v);
+            for (int j = 0; j < 16; ++j) {
+              v[j] = fmaf(__uint_as_float(raw[j]), scale_s[c0 + j], bias_s[c0 + j]);
+              if (p.relu) v[j] = fmaxf(v[j], 0.f);
+            }
+            OutConv<T>::store(yrow + c0, v);
+          }
+        }
+      } else {
+        float* prow = p.partial + ((int64_t)(item % p.split) * npix + pix) * p.Cout;
+        for (int c0 = 0; c0 < p.Cout; c0 += 16) {
+          uint32_t raw[16];
+          tmem_ld16(t_row + (uint32_t)c0, raw);
+          tmem_ld_wait();
+          if (valid) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              reinterpret_cast<uint4*>(prow + c0)[j] = make_uint4(raw[4 * j], raw[4 * j + 1], raw[4 * j + 2], raw[4 * j + 3]);
+          }
         }
       }
       tc_fence_before();
@@ -447,7 +378,34 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   __syncthreads();
   if (warp == 5) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols) : "memory");
+    tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+  }
+}
+
+// Fixed-order combination of the tap-split partial sums: y = act(scale * sum_g partial[g] + bias).
+template <typename T>
+__global__ void __launch_bounds__(256) dcn_fwd_tc_combine_kernel(const float* __restrict__ partial, T* __restrict__ y,
+                                                                 const float* __restrict__ scale, const float* __restrict__ bias,
+                                                                 int64_t npix, int Cout, int split, int relu) {
+  const int64_t n4 = npix * Cout / 4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const int o = (int)((i * 4) % Cout);
+    float4 s = __ldcs(reinterpret_cast<const float4*>(partial) + i);
+    for (int g = 1; g < split; ++g) {
+      const float4 t = __ldcs(reinterpret_cast<const float4*>(partial + (int64_t)g * npix * Cout) + i);
+      s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+    }
+    float v[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[j] = fmaf(v[j], scale ? __ldg(scale + o + j) : 1.f, bias ? __ldg(bias + o + j) : 0.f);
+      if (relu) v[j] = fmaxf(v[j], 0.f);
+    }
+    if (sizeof(T) == 4) {
+      reinterpret_cast<float4*>(y)[i] = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+      reinterpret_cast<uint2*>(y)[i] = make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
+    }
   }
 }
 
@@ -476,9 +434,7 @@ __global__ void pack_weights_kernel(const float* __restrict__ w, uint4* __restri
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const int c = cc * kChunk + j * kVec + 2 * e;
-        const __nv_bfloat162 pk = __floats2bfloat162_rn(w[((int64_t)n * Cin + c) * NUM_TAPS + tap],
-                                                        w[((int64_t)n * Cin + c + 1) * NUM_TAPS + tap]);
-        words[e] = *reinterpret_cast<const uint32_t*>(&pk);
+        words[e] = pack_bf16x2(w[((int64_t)n * Cin + c) * NUM_TAPS + tap], w[((int64_t)n * Cin + c + 1) * NUM_TAPS + tap]);
       }
     }
     const int64_t blob = (int64_t)tap * nchunk + cc;
@@ -496,6 +452,17 @@ int pow2_at_least(int v) {
   return p;
 }
 
+// Tap split of the schedule: 1 when the pixel tiles alone fill the machine, else 3 or 9.
+int choose_split(int num_tiles) {
+  if (num_tiles >= 148) return 1;
+  if (num_tiles * 3 >= 148) return 3;
+  return 9;
+}
+
+size_t split_workspace(int split, int64_t npix, int Cout) {
+  return split > 1 ? (size_t)split * (size_t)npix * Cout * sizeof(float) : 0;
+}
+
 }  // namespace
 
 bool dcn_tc_eligible(const cpoly_dcn_fwd_args& a) {
@@ -509,8 +476,13 @@ bool dcn_tc_eligible(const cpoly_dcn_fwd_args& a) {
   if ((reinterpret_cast<uintptr_t>(a.x.ptr) & 15) || (reinterpret_cast<uintptr_t>(a.y.ptr) & 15) ||
       (reinterpret_cast<uintptr_t>(a.weight_packed) & 15))
     return false;
-  if ((int64_t)a.B * a.H * a.W * a.Cin >= (1LL << 31)) return false;
+  if ((int64_t)a.B * a.H * a.W * a.Cin * esize >= (1LL << 32)) return false;  // 32-bit byte offsets in the sampler
   return true;
+}
+
+size_t dcn_tc_forward_workspace(const cpoly_dcn_fwd_args& a) {
+  const int tiles = a.B * ((a.W + TILE_W - 1) / TILE_W) * ((a.H + TILE_H - 1) / TILE_H);
+  return split_workspace(choose_split(tiles), (int64_t)a.B * a.H * a.W, a.Cout) + 256;
 }
 
 size_t dcn_tc_packed_bytes(int Cin, int Cout, int kh, int kw, int dtype) {
@@ -532,18 +504,31 @@ int dcn_tc_pack_weights(const float* weight, void* packed, int Cin, int Cout, in
 int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   TcParams p;
   const int esize = a.dtype == CPOLY_BF16 ? 2 : 4;
-  p.x = a.x.ptr; p.offset = a.offset; p.mask = a.mask; p.wpacked = a.weight_packed; p.bias = a.bias; p.y = a.y.ptr;
+  p.x = a.x.ptr; p.offset = a.offset; p.mask = a.mask; p.wpacked = a.weight_packed; p.bias = a.bias; p.scale = a.out_scale;
+  p.y = a.y.ptr;
   p.B = a.B; p.Cin = a.Cin; p.Cout = a.Cout; p.H = a.H; p.W = a.W;
-  p.om_dtype = a.om_dtype; p.mask_is_logit = a.mask_is_logit;
+  p.om_dtype = a.om_dtype; p.mask_is_logit = a.mask_is_logit; p.relu = a.relu;
   p.tiles_x = (a.W + TILE_W - 1) / TILE_W;
   p.tiles_y = (a.H + TILE_H - 1) / TILE_H;
   p.num_tiles = a.B * p.tiles_x * p.tiles_y;
   if (p.num_tiles == 0) return CPOLY_OK;
+  const int64_t npix = (int64_t)a.B * a.H * a.W;
+  p.split = choose_split(p.num_tiles);
+  const size_t need = split_workspace(p.split, npix, a.Cout);
+  if (p.split > 1 && (!a.workspace || a.workspace_bytes < need || (reinterpret_cast<uintptr_t>(a.workspace) & 15)))
+    p.split = 1;  // no scratch supplied: unsplit schedule (same result, fewer busy SMs)
+  p.partial = p.split > 1 ? reinterpret_cast<float*>(a.workspace) : nullptr;
+  p.taps_per_item = NUM_TAPS / p.split;
+  p.num_items = p.num_tiles * p.split;
   p.nchunk = a.Cin / (ROW_BYTES / esize);
   p.b_stage_bytes = a.Cout * ROW_BYTES;
   p.stage_bytes = A_STAGE_BYTES + p.b_stage_bytes;
   int stages = (SMEM_LIMIT - SMEM_STAGE_OFF) / p.stage_bytes;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
+  if (const char* e = getenv("CPOLY_TC_STAGES")) {  // profiling knob: fewer stages leave more of the 256 KB to L1
+    const int v = atoi(e);
+    if (v >= 2 && v < stages) stages = v;
+  }
   CPOLY_REQUIRE(stages >= 2, CPOLY_EUNSUPPORTED, "not enough shared memory for a 2-stage pipeline");
   p.stages = stages;
   p.acc_cols = a.Cout;
@@ -553,7 +538,7 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   int dev = 0, sms = 0;
   CPOLY_CUDA_OK(cudaGetDevice(&dev));
   CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int grid = p.num_tiles < sms ? p.num_tiles : sms;
+  const int grid = p.num_items < sms ? p.num_items : sms;
   if (a.dtype == CPOLY_BF16) {
     CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_fwd_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     dcn_fwd_tc_kernel<__nv_bfloat16><<<grid, NTHREADS, smem_bytes, stream>>>(p);
@@ -561,7 +546,17 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
     CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_fwd_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     dcn_fwd_tc_kernel<float><<<grid, NTHREADS, smem_bytes, stream>>>(p);
   }
-  return check_launch("dcn_fwd_tc_kernel");
+  if (int rc = check_launch("dcn_fwd_tc_kernel")) return rc;
+  if (p.split > 1) {
+    const int64_t n4 = npix * a.Cout / 4;
+    const unsigned blocks = (unsigned)((n4 + 255) / 256 < 148 * 8 ? (n4 + 255) / 256 : 148 * 8);
+    if (a.dtype == CPOLY_BF16)
+      dcn_fwd_tc_combine_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(p.partial, reinterpret_cast<__nv_bfloat16*>(a.y.ptr), a.out_scale, a.bias, npix, a.Cout, p.split, a.relu);
+    else
+      dcn_fwd_tc_combine_kernel<float><<<blocks, 256, 0, stream>>>(p.partial, reinterpret_cast<float*>(a.y.ptr), a.out_scale, a.bias, npix, a.Cout, p.split, a.relu);
+    return check_launch("dcn_fwd_tc_combine_kernel");
+  }
+  return CPOLY_OK;
 }
 
 }  // namespace cpoly

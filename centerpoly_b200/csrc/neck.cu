@@ -1,0 +1,155 @@
+// IDAUp up-sampling: depthwise ConvTranspose2d(C, C, 2f, stride f, padding f/2, groups=C, bias=False)
+// (reference src/lib/models/networks/pose_dla_dcn.py:372-375, applied at :385) fused with the skip add
+// `layers[i] + layers[i-1]` of :387.  cuDNN runs this as a generic dgrad (170 us per call at 256x512x64);
+// it is a pure streaming op: every output pixel reads a 2x2 input neighbourhood and 4 weights per channel.
+//
+//   y[b,c,oy,ox] = sum_{iy,ix} x[b,c,iy,ix] * w[c, oy + pad - iy*f, ox + pad - ix*f]  (+ skip[b,c,oy,ox])
+//
+// With kernel 2f and stride f exactly two input rows / columns contribute: iy1 = (oy + pad) / f with
+// ky = (oy + pad) % f, and iy0 = iy1 - 1 with ky + f.  HBM bound: algorithmic bytes = s * B*C*(H*W + [2] * Ho*Wo).
+#include "common.cuh"
+
+namespace cpoly {
+namespace {
+
+struct UpParams {
+  int B, C, H, W, f, Ho, Wo;
+  cpoly_tensor4 x, skip, y;
+  const float* w;
+};
+
+template <typename T, int VEC>
+struct Vec;
+template <> struct Vec<float, 4> {
+  __device__ static __forceinline__ void load(const float* p, float (&v)[4]) {
+    const float4 q = __ldg(reinterpret_cast<const float4*>(p));
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+  }
+  __device__ static __forceinline__ void store(float* p, const float (&v)[4]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+template <> struct Vec<__nv_bfloat16, 8> {
+  __device__ static __forceinline__ void load(const __nv_bfloat16* p, float (&v)[8]) {
+    const uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[2 * j] = __uint_as_float(w[j] << 16);
+      v[2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+    }
+  }
+  __device__ static __forceinline__ void store(__nv_bfloat16* p, const float (&v)[8]) {
+    uint4 q;
+    uint32_t* w = &q.x;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __nv_bfloat162 pk = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+      w[j] = *reinterpret_cast<const uint32_t*>(&pk);
+    }
+    *reinterpret_cast<uint4*>(p) = q;
+  }
+};
+
+// channels_last fast path: one thread per (output pixel, VEC-channel piece); pieces of a pixel are adjacent
+// threads, so loads and stores are 16-byte vectors over contiguous channels.
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256) upsample_nhwc_kernel(UpParams p) {
+  const int pieces = p.C / VEC;
+  const int64_t total = (int64_t)p.B * p.Ho * p.Wo * pieces;
+  const int K = 2 * p.f, pad = p.f / 2;
+  const T* xg = reinterpret_cast<const T*>(p.x.ptr);
+  const T* sg = reinterpret_cast<const T*>(p.skip.ptr);
+  T* yg = reinterpret_cast<T*>(p.y.ptr);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int piece = (int)(i % pieces);
+    int64_t t = i / pieces;
+    const int ox = (int)(t % p.Wo); t /= p.Wo;
+    const int oy = (int)(t % p.Ho);
+    const int b = (int)(t / p.Ho);
+    const int c0 = piece * VEC;
+    const int iy1 = (oy + pad) / p.f, ky1 = (oy + pad) - iy1 * p.f;
+    const int ix1 = (ox + pad) / p.f, kx1 = (ox + pad) - ix1 * p.f;
+    float acc[VEC];
+    if (sg) Vec<T, VEC>::load(sg + (int64_t)b * p.skip.sb + (int64_t)oy * p.skip.sh + (int64_t)ox * p.skip.sw + c0, acc);
+    else {
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) acc[j] = 0.f;
+    }
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy) {
+      const int iy = iy1 - dy, ky = ky1 + dy * p.f;
+      if (iy < 0 || iy >= p.H) continue;
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const int ix = ix1 - dx, kx = kx1 + dx * p.f;
+        if (ix < 0 || ix >= p.W) continue;
+        float v[VEC];
+        Vec<T, VEC>::load(xg + (int64_t)b * p.x.sb + (int64_t)iy * p.x.sh + (int64_t)ix * p.x.sw + c0, v);
+        const float* wp = p.w + ((int64_t)c0 * K + ky) * K + kx;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) acc[j] = fmaf(v[j], __ldg(wp + (int64_t)j * K * K), acc[j]);
+      }
+    }
+    Vec<T, VEC>::store(yg + (int64_t)b * p.y.sb + (int64_t)oy * p.y.sh + (int64_t)ox * p.y.sw + c0, acc);
+  }
+}
+
+// any strides / channel counts: one thread per output element
+template <typename T>
+__global__ void __launch_bounds__(256) upsample_generic_kernel(UpParams p) {
+  const int64_t total = (int64_t)p.B * p.C * p.Ho * p.Wo;
+  const int K = 2 * p.f, pad = p.f / 2;
+  const T* xg = reinterpret_cast<const T*>(p.x.ptr);
+  const T* sg = reinterpret_cast<const T*>(p.skip.ptr);
+  T* yg = reinterpret_cast<T*>(p.y.ptr);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t t = i;
+    const int ox = (int)(t % p.Wo); t /= p.Wo;
+    const int oy = (int)(t % p.Ho); t /= p.Ho;
+    const int c = (int)(t % p.C);
+    const int b = (int)(t / p.C);
+    const int iy1 = (oy + pad) / p.f, ky1 = (oy + pad) - iy1 * p.f;
+    const int ix1 = (ox + pad) / p.f, kx1 = (ox + pad) - ix1 * p.f;
+    float acc = sg ? ld_as_float(sg + (int64_t)b * p.skip.sb + (int64_t)c * p.skip.sc + (int64_t)oy * p.skip.sh + (int64_t)ox * p.skip.sw) : 0.f;
+    for (int dy = 0; dy < 2; ++dy) {
+      const int iy = iy1 - dy, ky = ky1 + dy * p.f;
+      if (iy < 0 || iy >= p.H) continue;
+      for (int dx = 0; dx < 2; ++dx) {
+        const int ix = ix1 - dx, kx = kx1 + dx * p.f;
+        if (ix < 0 || ix >= p.W) continue;
+        acc = fmaf(ld_as_float(xg + (int64_t)b * p.x.sb + (int64_t)c * p.x.sc + (int64_t)iy * p.x.sh + (int64_t)ix * p.x.sw),
+                   __ldg(p.w + ((int64_t)c * K + ky) * K + kx), acc);
+      }
+    }
+    st_from_float(yg + (int64_t)b * p.y.sb + (int64_t)c * p.y.sc + (int64_t)oy * p.y.sh + (int64_t)ox * p.y.sw, acc);
+  }
+}
+
+bool vec_ok(const cpoly_tensor4& t, int vec_bytes_elems) {
+  return t.ptr == nullptr || (t.sc == 1 && (reinterpret_cast<uintptr_t>(t.ptr) & 15) == 0 && t.sw % vec_bytes_elems == 0 &&
+                              t.sh % vec_bytes_elems == 0 && t.sb % vec_bytes_elems == 0);
+}
+
+}  // namespace
+
+int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream) {
+  UpParams p;
+  p.B = a.B; p.C = a.C; p.H = a.H; p.W = a.W; p.f = a.f; p.Ho = a.H * a.f; p.Wo = a.W * a.f;
+  p.x = a.x; p.skip = a.skip; p.y = a.y; p.w = a.weight;
+  const bool bf = a.dtype == CPOLY_BF16;
+  const int vec = bf ? 8 : 4;
+  const bool fast = a.C % vec == 0 && vec_ok(a.x, vec) && vec_ok(a.skip, vec) && vec_ok(a.y, vec);
+  const int64_t total = (int64_t)a.B * p.Ho * p.Wo * (fast ? a.C / vec : a.C);
+  const unsigned blocks = (unsigned)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
+  if (fast) {
+    if (bf) upsample_nhwc_kernel<__nv_bfloat16, 8><<<blocks, 256, 0, stream>>>(p);
+    else upsample_nhwc_kernel<float, 4><<<blocks, 256, 0, stream>>>(p);
+  } else {
+    if (bf) upsample_generic_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(p);
+    else upsample_generic_kernel<float><<<blocks, 256, 0, stream>>>(p);
+  }
+  return check_launch("idaup_upsample_kernel");
+}
+
+}  // namespace cpoly

@@ -40,10 +40,10 @@ def _out_hw(H, W, k, s, p, d):
 
 
 class _PackedWeights:
-    """Derived, non-persistent cache of the tap-major / swizzled weight image (never in state_dict)."""
-
-    def __init__(self):
-        self._entries = {}
+    """Derived, non-persistent cache of the tap-major / swizzled weight images (never in state_dict).
+    The image hangs off the weight tensor OBJECT (a plain Python attribute, so it dies with the parameter and can
+    never be confused with another tensor that later reuses the same address); it is rebuilt when the parameter's
+    version counter, storage address, device or shape moves (optimizer step, load_state_dict, .to(), .bfloat16())."""
 
     def get(self, weight: torch.Tensor, dtype_code: int):
         Cout, Cin, kh, kw = weight.shape
@@ -51,9 +51,15 @@ class _PackedWeights:
         nbytes = L.cpoly_dcn_packed_weight_bytes(Cin, Cout, kh, kw, dtype_code)
         if nbytes == 0:
             return None
-        key = (weight.device, dtype_code)
-        tag = (weight.data_ptr(), weight._version, tuple(weight.shape))
-        hit = self._entries.get(key)
+        tag = (weight._version, weight.data_ptr(), weight.device, tuple(weight.shape), weight.dtype)
+        cache = getattr(weight, "_cpoly_packed", None)
+        if cache is None:
+            cache = {}
+            try:
+                weight._cpoly_packed = cache
+            except Exception:      # tensor subclass without a __dict__: pack every call
+                pass
+        hit = cache.get(dtype_code)
         if hit is not None and hit[0] == tag:
             return hit[1]
         w32 = weight.detach()
@@ -62,17 +68,18 @@ class _PackedWeights:
         packed = torch.empty(nbytes, dtype=torch.uint8, device=weight.device)
         _lib.check(L.cpoly_dcn_pack_weights(w32.data_ptr(), packed.data_ptr(), Cin, Cout, kh, kw, dtype_code,
                                             _lib.stream_ptr(weight.device)), "cpoly_dcn_pack_weights")
-        self._entries[key] = (tag, packed)
+        cache[dtype_code] = (tag, packed)
         return packed
 
 
 _GLOBAL_PACK_CACHE = _PackedWeights()
 
 
-def _fwd_args(x, offset, mask, weight32, bias32, stride, padding, dilation, dg, mask_is_logit, packed, y):
+def _fwd_args(x, offset, mask, weight32, bias32, stride, padding, dilation, dg, mask_is_logit, packed, y,
+              wshape=None, out_scale=None, relu=False):
     a = _lib.DcnFwdArgs()
     a.B, a.Cin, a.H, a.W = x.shape
-    a.Cout, _, a.kh, a.kw = weight32.shape
+    a.Cout, _, a.kh, a.kw = wshape if wshape is not None else weight32.shape
     a.stride_h, a.stride_w = stride
     a.pad_h, a.pad_w = padding
     a.dil_h, a.dil_w = dilation
@@ -82,10 +89,12 @@ def _fwd_args(x, offset, mask, weight32, bias32, stride, padding, dilation, dg, 
     a.mask_is_logit = int(mask_is_logit)
     a.path = _FORCED_PATH
     a.x, a.offset, a.mask = _lib.t4(x), _lib.t4(offset), _lib.t4(mask)
-    a.weight = weight32.data_ptr()
+    a.weight = weight32.data_ptr() if weight32 is not None else None
     a.bias = bias32.data_ptr() if bias32 is not None else None
     a.weight_packed = packed.data_ptr() if packed is not None else None
     a.y = _lib.t4(y)
+    a.out_scale = out_scale.data_ptr() if out_scale is not None else None
+    a.relu = int(bool(relu))
     return a
 
 
@@ -113,11 +122,11 @@ def _check_shapes(x, offset, mask, weight, stride, padding, dilation, dg):
     return Ho, Wo
 
 
-def _forward_impl(x, offset, mask, weight, bias, stride, padding, dilation, dg, mask_is_logit):
+def _forward_impl(x, offset, mask, weight, bias, stride, padding, dilation, dg, mask_is_logit, out_scale=None, relu=False):
+    """y = act(out_scale * dcn(x) + bias); out_scale/relu are the optional fused DeformConv epilogue."""
     dev = _lib.require_cuda(x, offset, mask, weight, bias)
     Ho, Wo = _check_shapes(x, offset, mask, weight, stride, padding, dilation, dg)
     L = _lib.lib()
-    w32, b32 = _as_f32_contig(weight), _as_f32_contig(bias)
     with torch.cuda.device(dev):
         packed = _GLOBAL_PACK_CACHE.get(weight, _lib.dtype_code(x)) if _FORCED_PATH != _lib.PATH_SIMT else None
         if packed is not None and not x.is_contiguous(memory_format=torch.channels_last):
@@ -125,7 +134,19 @@ def _forward_impl(x, offset, mask, weight, bias, stride, padding, dilation, dg, 
             x = x.contiguous(memory_format=torch.channels_last)
         y = torch.empty((x.shape[0], weight.shape[0], Ho, Wo), dtype=x.dtype, device=dev,
                         memory_format=torch.channels_last)
-        a = _fwd_args(x, offset, mask, w32, b32, stride, padding, dilation, dg, mask_is_logit, packed, y)
+        b32 = _as_f32_contig(bias)
+        s32 = _as_f32_contig(out_scale)
+        a = _fwd_args(x, offset, mask, None, b32, stride, padding, dilation, dg, mask_is_logit, packed, y,
+                      wshape=weight.shape, out_scale=s32, relu=relu)
+        use_tc = packed is not None and L.cpoly_dcn_tcgen05_eligible(byref(a))
+        if use_tc:
+            nbytes = L.cpoly_dcn_forward_workspace_bytes(byref(a))
+            if nbytes > 256:
+                ws = _lib.workspace(nbytes, dev)
+                a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+        else:
+            w32 = _as_f32_contig(weight)      # the generic SIMT path reads the dense fp32 master weights
+            a.weight = w32.data_ptr()
         _lib.check(L.cpoly_dcn_forward(byref(a), _lib.stream_ptr(dev)), "cpoly_dcn_forward")
     return y, x
 
@@ -278,5 +299,15 @@ class DCN(DCNv2):
 
     def forward(self, input):
         om = self.conv_offset_mask(input)
+        fused = getattr(self, "_fused_epilogue", None)
+        if fused is not None:
+            # inference-only DeformConv fusion installed by centerpoly_b200.fuse (eval-mode BN + ReLU in the epilogue)
+            if torch.is_grad_enabled() and (input.requires_grad or self.weight.requires_grad):
+                raise RuntimeError("the fused DeformConv epilogue is inference-only; call fuse.unfuse(model) before training")
+            scale, shift, relu = fused
+            n_off = om.shape[1] // 3 * 2
+            y, _ = _forward_impl(input, om[:, :n_off], om[:, n_off:], self.weight, shift, self.stride, self.padding,
+                                 self.dilation, self.deformable_groups, True, out_scale=scale, relu=relu)
+            return y
         return _DCNFused.apply(input, om, self.weight, self.bias, self.stride, self.padding, self.dilation,
                                self.deformable_groups)

@@ -21,7 +21,7 @@ HEADS = {"hm": 8, "poly": 64, "pseudo_depth": 1, "reg": 2}
 
 class PolydetEngine:
     def __init__(self, height=1024, width=2048, batch=1, dtype="bf16", K=100, rep="cartesian", heads=None,
-                 device="cuda:0", seed=317, calibrate=True, use_graph=True, n_slots=2):
+                 device="cuda:0", seed=317, calibrate=True, use_graph=True, n_slots=2, optimize=True):
         self.device = torch.device(device)
         self.dtype = dtype
         self.K, self.rep = K, rep
@@ -31,7 +31,15 @@ class PolydetEngine:
         net = PolydetDLA34(self.heads).to(self.device).to(memory_format=torch.channels_last)
         if calibrate:
             calibrate_random_init(net, height, width, seed=seed)
-        self.net = net.eval()
+        net = net.eval()
+        self.fusion = None
+        if optimize:
+            from .. import fuse
+            self.fusion = fuse.optimize_for_inference(net)   # module rewrite, SURVEY 8(f)-2
+            if dtype == "bf16":
+                net = net.bfloat16()                           # bf16 weights: no per-call autocast casts
+        self.optimize = optimize
+        self.net = net
         self.n_dcn_per_frame = sum(1 for m in net.modules() if hasattr(m, "conv_offset_mask"))
         self.stream = torch.cuda.Stream(self.device)
         self.copy_stream = torch.cuda.Stream(self.device)   # H2D
@@ -49,14 +57,19 @@ class PolydetEngine:
 
     # ------------------------------------------------------------------------------------------
     def _autocast(self):
-        if self.dtype == "bf16":
+        if self.dtype == "bf16" and not self.optimize:
             return torch.autocast("cuda", dtype=torch.bfloat16)
         return contextlib.nullcontext()
 
     def _step(self, x):
         """One frame: network -> sigmoid -> decode (the body of PolydetDetector.process)."""
         with torch.no_grad(), self._autocast():
+            if self.dtype == "bf16" and self.optimize:
+                x = x.to(torch.bfloat16)
             out = self.net(x)[-1]
+            if self.optimize:   # the sigmoid of detectors/polydet.py:28 is fused into the decode kernel
+                return cdecode.polydet_decode_from_logits(out["hm"], out["poly"], out["pseudo_depth"], reg=out.get("reg"),
+                                                          K=self.K, rep=self.rep)
             hm = out["hm"].sigmoid_()
             return cdecode.polydet_decode(hm, out["poly"], out["pseudo_depth"], reg=out.get("reg"), K=self.K, rep=self.rep)
 

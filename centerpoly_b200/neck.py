@@ -1,0 +1,65 @@
+"""The ``up_i`` of the reference's IDAUp — depthwise ``nn.ConvTranspose2d(o, o, 2f, stride=f, padding=f//2,
+groups=o, bias=False)`` (src/lib/models/networks/pose_dla_dcn.py:372-375, applied at :385) — as one streaming
+CUDA kernel, optionally fused with the skip add ``layers[i] + layers[i-1]`` of :387.
+
+``IDAUpsample`` keeps the parameter name and shape of the module it replaces (``weight`` (C,1,2f,2f)), so
+``state_dict`` keys do not change.  Inference only (no autograd): training keeps the reference's ConvTranspose2d.
+"""
+from __future__ import annotations
+
+from ctypes import byref
+
+import torch
+from torch import nn
+
+from . import _lib
+
+__all__ = ["idaup_upsample", "IDAUpsample"]
+
+
+def idaup_upsample(x: torch.Tensor, weight: torch.Tensor, f: int, skip: torch.Tensor | None = None) -> torch.Tensor:
+    """conv_transpose2d(x, weight, stride=f, padding=f//2, groups=C) [+ skip]; x (B,C,H,W) -> (B,C,H*f,W*f)."""
+    dev = _lib.require_cuda(x, weight, skip)
+    if x.dim() != 4 or tuple(weight.shape) != (x.shape[1], 1, 2 * f, 2 * f):
+        raise RuntimeError(f"idaup_upsample: weight {tuple(weight.shape)} does not match C={x.shape[1]}, f={f}")
+    B, C, H, W = x.shape
+    if skip is not None and (tuple(skip.shape) != (B, C, H * f, W * f) or skip.dtype != x.dtype):
+        raise RuntimeError("idaup_upsample: skip must be (B,C,H*f,W*f) with the dtype of x")
+    w32 = weight.detach()
+    if w32.dtype != torch.float32 or not w32.is_contiguous():
+        w32 = w32.float().contiguous()
+    with torch.cuda.device(dev):
+        cl = x.is_contiguous(memory_format=torch.channels_last)
+        y = torch.empty((B, C, H * f, W * f), dtype=x.dtype, device=dev,
+                        memory_format=torch.channels_last if cl else torch.contiguous_format)
+        a = _lib.UpsampleArgs()
+        a.B, a.C, a.H, a.W, a.f = B, C, H, W, f
+        a.dtype = _lib.dtype_code(x)
+        a.x, a.skip, a.y = _lib.t4(x), _lib.t4(skip), _lib.t4(y)
+        a.weight = w32.data_ptr()
+        _lib.check(_lib.lib().cpoly_idaup_upsample_forward(byref(a), _lib.stream_ptr(dev)), "cpoly_idaup_upsample_forward")
+    return y
+
+
+class IDAUpsample(nn.Module):
+    """Drop-in for IDAUp's ``up_i`` (same ``weight`` parameter), forward(x, skip=None)."""
+
+    def __init__(self, deconv: nn.ConvTranspose2d):
+        super().__init__()
+        k, s = deconv.kernel_size[0], deconv.stride[0]
+        ok = (deconv.groups == deconv.in_channels == deconv.out_channels and deconv.bias is None and
+              deconv.kernel_size == (2 * s, 2 * s) and deconv.stride == (s, s) and deconv.padding == (s // 2, s // 2) and
+              deconv.output_padding == (0, 0) and deconv.dilation == (1, 1) and s >= 2 and s % 2 == 0)
+        if not ok:
+            raise RuntimeError(f"IDAUpsample: {deconv} is not the depthwise 2f/f/f//2 deconvolution of IDAUp")
+        self.f = s
+        self.weight = deconv.weight
+        self._w32 = None
+
+    def forward(self, x, skip=None):
+        w = self.weight
+        if w.dtype != torch.float32:   # bf16 model: keep one fp32 copy of the (tiny) weights
+            if self._w32 is None or self._w32[0] != (w.data_ptr(), w._version):
+                self._w32 = ((w.data_ptr(), w._version), w.detach().float().contiguous())
+            w = self._w32[1]
+        return idaup_upsample(x, w, self.f, skip)

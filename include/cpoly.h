@@ -14,6 +14,8 @@
  *                           src/lib/trains/base_trainer.py:97-98 `loss.backward()`).
  *   cpoly_dcn_pack_weights  (new) derived tap-major / MMA-swizzled weight cache; the stored parameter stays
  *                           (Cout,Cin,kh,kw) so checkpoints (src/lib/models/model.py:31-130) are unaffected.
+ *   cpoly_idaup_upsample_forward <- the depthwise `nn.ConvTranspose2d` `up_i` of IDAUp
+ *                           (src/lib/models/networks/pose_dla_dcn.py:372-375,385) fused with the skip add of :387.
  *   cpoly_decode         <- `polydet_decode(heat, polys, depth, reg, cat_spec_poly, K, rep)`
  *                           src/lib/models/decode.py:512-670, i.e. `_nms` :13-19, `_topk` :117-133,
  *                           `_transpose_and_gather_feat` src/lib/models/utils.py:22-26, and (optionally, with
@@ -41,7 +43,7 @@
 extern "C" {
 #endif
 
-#define CPOLY_ABI_VERSION 1
+#define CPOLY_ABI_VERSION 2
 
 /* element types */
 #define CPOLY_F32 0
@@ -84,10 +86,20 @@ typedef struct {
   cpoly_tensor4 x;       /* (B,Cin,H,W)                       */
   cpoly_tensor4 offset;  /* (B,dg*2*kh*kw,Ho,Wo): channel 2k = dy, 2k+1 = dx of tap k = i*kw+j */
   cpoly_tensor4 mask;    /* (B,dg*kh*kw,Ho,Wo)                */
-  const float* weight;   /* (Cout,Cin,kh,kw) dense fp32 master weights (always required)        */
+  const float* weight;   /* (Cout,Cin,kh,kw) dense fp32 master weights (generic path and backward) */
   const float* bias;     /* (Cout) fp32 or NULL                                                 */
   const void* weight_packed; /* output of cpoly_dcn_pack_weights for `dtype`, or NULL (=> SIMT)  */
   cpoly_tensor4 y;       /* (B,Cout,Ho,Wo), element type `dtype`                                */
+  /* Fused epilogue (all optional): y = act(out_scale[o] * conv + bias[o]).  With out_scale = gamma/sqrt(var+eps)
+   * and bias = out_scale*dcn_bias + beta - out_scale*mean this is the eval-mode DeformConv of
+   * pose_dla_dcn.py:347-359 (DCN -> BatchNorm2d -> ReLU) in one pass.  NULL / 0 => plain DCN. */
+  const float* out_scale; /* (Cout) fp32 or NULL */
+  int32_t relu;          /* 1: clamp at zero */
+  int32_t reserved0;
+  /* Scratch for the tap-split schedule of small feature maps (cpoly_dcn_forward_workspace_bytes); may be
+   * NULL, in which case the unsplit schedule is used. */
+  void* workspace;
+  size_t workspace_bytes;
 } cpoly_dcn_fwd_args;
 
 typedef struct {
@@ -118,10 +130,28 @@ size_t cpoly_dcn_packed_weight_bytes(int32_t Cin, int32_t Cout, int32_t kh, int3
 int cpoly_dcn_pack_weights(const float* weight, void* packed, int32_t Cin, int32_t Cout, int32_t kh,
                            int32_t kw, int32_t dtype, cpoly_stream_t stream);
 
+size_t cpoly_dcn_forward_workspace_bytes(const cpoly_dcn_fwd_args* args);
 int cpoly_dcn_forward(const cpoly_dcn_fwd_args* args, cpoly_stream_t stream);
 
 size_t cpoly_dcn_backward_workspace_bytes(const cpoly_dcn_bwd_args* args);
 int cpoly_dcn_backward(const cpoly_dcn_bwd_args* args, cpoly_stream_t stream);
+
+/* ------------------------------------------------------------------------------ IDAUp upsampling */
+
+/* The `up_i` of IDAUp (src/lib/models/networks/pose_dla_dcn.py:372-375, applied at :385): depthwise
+ * ConvTranspose2d(C, C, 2f, stride=f, padding=f/2, groups=C, bias=False), optionally fused with the
+ * `layers[i] + layers[i-1]` of :387:   y = conv_transpose(x, weight) [+ skip].   y and skip are (B,C,H*f,W*f). */
+typedef struct {
+  int32_t B, C, H, W;   /* input (B,C,H,W) */
+  int32_t f;            /* up-sampling factor: kernel 2f, stride f, padding f/2 */
+  int32_t dtype;        /* element type of x, skip and y */
+  cpoly_tensor4 x;
+  const float* weight;  /* (C,1,2f,2f) dense fp32 */
+  cpoly_tensor4 skip;   /* ptr == NULL => no addend */
+  cpoly_tensor4 y;
+} cpoly_upsample_args;
+
+int cpoly_idaup_upsample_forward(const cpoly_upsample_args* args, cpoly_stream_t stream);
 
 /* --------------------------------------------------------------------------------------- decode */
 

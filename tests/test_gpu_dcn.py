@@ -72,6 +72,8 @@ def test_simt_vs_golden_all_geometries(path):
 TC_SHAPES = [  # (B, Cin, Cout, H, W) — reduced-resolution versions of the 7 IDAUp shape classes + ragged sizes
     (1, 64, 64, 16, 32), (2, 128, 64, 24, 40), (1, 128, 128, 16, 16), (1, 256, 64, 8, 16),
     (1, 256, 128, 9, 21), (1, 256, 256, 8, 16), (1, 512, 256, 8, 16), (3, 64, 64, 5, 7),
+    (1, 128, 64, 72, 100),    # 63 tiles  -> tap split 3
+    (1, 64, 64, 100, 200),    # 169 tiles -> unsplit persistent schedule, ragged right/bottom tiles
 ]
 
 
@@ -189,3 +191,26 @@ def test_errors_are_runtime_errors():
         cp.dcn_v2_conv(x, torch.zeros(1, 17, 8, 8, device="cuda"), torch.zeros(1, 9, 8, 8, device="cuda"), w, None, 1, 1, 1, 1)
     with pytest.raises(RuntimeError):
         cp.dcn_v2_conv(x.cpu(), torch.zeros(1, 18, 8, 8), torch.zeros(1, 9, 8, 8), w.cpu(), None, 1, 1, 1, 1)
+
+
+def test_pack_cache_is_not_confused_by_recycled_addresses():
+    """A freed weight tensor's address is routinely recycled by the caching allocator for the next weight of the
+    same shape: the packed-weight cache must follow the tensor object, not the address."""
+    import centerpoly_b200 as cp
+    case = make_dcn_case(3, 1, 64, 64, 16, 32)
+    x = case["x"].cuda().contiguous(memory_format=torch.channels_last)
+    off, msk = case["offset"].cuda(), case["mask"].cuda()
+    outs, ptrs = [], []
+    for scale in (1.0, -2.0, 0.5):
+        w = (case["weight"] * scale).cuda()
+        ptrs.append(w.data_ptr())
+        outs.append(cp.dcn_v2_conv(x, off, msk, w, None, 1, 1, 1, 1).float().cpu())
+        del w
+    gate(outs[1].numpy(), (-2.0 * outs[0]).numpy(), 2e-3, "recycled weight 1")
+    gate(outs[2].numpy(), (0.5 * outs[0]).numpy(), 2e-3, "recycled weight 2")
+    # in-place update of the same tensor (optimizer step) must also be seen
+    w = case["weight"].cuda()
+    y0 = cp.dcn_v2_conv(x, off, msk, w, None, 1, 1, 1, 1).float().cpu()
+    w.mul_(3.0)
+    y1 = cp.dcn_v2_conv(x, off, msk, w, None, 1, 1, 1, 1).float().cpu()
+    gate(y1.numpy(), (3.0 * y0).numpy(), 2e-3, "in-place update")
