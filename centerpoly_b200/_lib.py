@@ -37,6 +37,7 @@ class DcnFwdArgs(Structure):
         ("x", Tensor4), ("offset", Tensor4), ("mask", Tensor4),
         ("weight", c_void_p), ("bias", c_void_p), ("weight_packed", c_void_p), ("y", Tensor4),
         ("out_scale", c_void_p), ("relu", c_int32), ("reserved0", c_int32),
+        ("offset_bias", c_void_p), ("mask_bias", c_void_p),
         ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
 
 
@@ -46,7 +47,7 @@ class DcnBwdArgs(Structure):
 
 
 class UpsampleArgs(Structure):
-    _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "f", "dtype")] + [
+    _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "f", "dtype", "weight_tap_major", "reserved0")] + [
         ("x", Tensor4), ("weight", c_void_p), ("skip", Tensor4), ("y", Tensor4)]
 
 

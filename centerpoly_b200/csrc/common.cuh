@@ -64,6 +64,8 @@ struct DcnGeom {
   int B, Cin, Cout, H, W, Ho, Wo;
   int kh, kw, sh, sw, ph, pw, dh, dw, dg;
   int om_dtype, mask_is_logit;
+  const float* offset_bias;
+  const float* mask_bias;
 };
 
 inline DcnGeom make_geom(const cpoly_dcn_fwd_args& a) {
@@ -74,6 +76,7 @@ inline DcnGeom make_geom(const cpoly_dcn_fwd_args& a) {
   g.Ho = (a.H + 2 * a.pad_h - (a.dil_h * (a.kh - 1) + 1)) / a.stride_h + 1;
   g.Wo = (a.W + 2 * a.pad_w - (a.dil_w * (a.kw - 1) + 1)) / a.stride_w + 1;
   g.om_dtype = a.om_dtype; g.mask_is_logit = a.mask_is_logit;
+  g.offset_bias = a.offset_bias; g.mask_bias = a.mask_bias;
   return g;
 }
 

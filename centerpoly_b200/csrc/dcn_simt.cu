@@ -48,10 +48,12 @@ __device__ __forceinline__ void fill_pixel_tap(PixelTap& pt, int64_t p, int64_t 
   const int T = g.kh * g.kw;
   const int i = tap / g.kw, j = tap - i * g.kw;
   const int64_t opix = (int64_t)b * offset.sb + (int64_t)ho * offset.sh + (int64_t)wo * offset.sw;
-  const float dy = ld_dyn(offset.ptr, opix + (int64_t)(grp * 2 * T + 2 * tap) * offset.sc, g.om_dtype);
-  const float dx = ld_dyn(offset.ptr, opix + (int64_t)(grp * 2 * T + 2 * tap + 1) * offset.sc, g.om_dtype);
+  float dy = ld_dyn(offset.ptr, opix + (int64_t)(grp * 2 * T + 2 * tap) * offset.sc, g.om_dtype);
+  float dx = ld_dyn(offset.ptr, opix + (int64_t)(grp * 2 * T + 2 * tap + 1) * offset.sc, g.om_dtype);
   float m = ld_dyn(mask.ptr, (int64_t)b * mask.sb + (int64_t)(grp * T + tap) * mask.sc +
                                  (int64_t)ho * mask.sh + (int64_t)wo * mask.sw, g.om_dtype);
+  if (g.offset_bias) { dy += __ldg(g.offset_bias + grp * 2 * T + 2 * tap); dx += __ldg(g.offset_bias + grp * 2 * T + 2 * tap + 1); }
+  if (g.mask_bias) m += __ldg(g.mask_bias + grp * T + tap);
   if (g.mask_is_logit) m = sigmoidf_accurate(m);
   const float py = (float)(ho * g.sh - g.ph + i * g.dh) + dy;
   const float px = (float)(wo * g.sw - g.pw + j * g.dw) + dx;

@@ -60,6 +60,8 @@ struct TcParams {
   const void* wpacked;
   const float* bias;
   const float* scale;
+  const float* offset_bias;
+  const float* mask_bias;
   void* y;
   float* partial;  // [split][B*H*W][Cout] fp32 when split > 1
   int B, Cin, Cout, H, W;
@@ -197,6 +199,8 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
           raw_dy[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k) * p.offset.sc, p.om_dtype);
           raw_dx[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k + 1) * p.offset.sc, p.om_dtype);
           raw_m[i] = ld_dyn(p.mask.ptr, (int64_t)b * p.mask.sb + (int64_t)k * p.mask.sc + (int64_t)y * p.mask.sh + (int64_t)x * p.mask.sw, p.om_dtype);
+          if (p.offset_bias) { raw_dy[i] += __ldg(p.offset_bias + 2 * k); raw_dx[i] += __ldg(p.offset_bias + 2 * k + 1); }
+          if (p.mask_bias) raw_m[i] += __ldg(p.mask_bias + k);
         }
       }
     };
@@ -287,7 +291,7 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
         const int q0 = (item % p.split) * chunks_per_item;
         for (int q = 0; q < chunks_per_item; ++q) {
-          mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u);
+          mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u, 500);
           mbar_arrive_expect_tx(bar_fullB + 8 * rc.s, (uint32_t)p.b_stage_bytes);
           bulk_copy_g2s(smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes + A_STAGE_BYTES,
                         wsrc + (size_t)(q0 + q) * p.b_stage_bytes, (uint32_t)p.b_stage_bytes, bar_fullB + 8 * rc.s);
@@ -303,12 +307,12 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       uint32_t tcount = 0;
       for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++tcount) {
         const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
-        mbar_wait(bar_tempty + 8 * acc, accph ^ 1u);  // epilogue drained this accumulator
+        mbar_wait(bar_tempty + 8 * acc, accph ^ 1u, 200);  // epilogue drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.acc_cols;
         for (int q = 0; q < chunks_per_item; ++q) {
-          mbar_wait(bar_fullA + 8 * rc.s, rc.ph);
-          mbar_wait(bar_fullB + 8 * rc.s, rc.ph);
+          mbar_wait(bar_fullA + 8 * rc.s, rc.ph, 100);
+          mbar_wait(bar_fullB + 8 * rc.s, rc.ph, 100);
           tc_fence_after();
           const uint32_t a_addr = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
           const uint64_t adesc = umma_desc_sw128(a_addr);
@@ -335,7 +339,7 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
       const bool valid = (y < p.H) && (x < p.W);
       const int64_t pix = ((int64_t)b * p.H + y) * p.W + x;
-      mbar_wait(bar_tfull + 8 * acc, accph);
+      mbar_wait(bar_tfull + 8 * acc, accph, 1000);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + acc * (uint32_t)p.acc_cols;
       if (p.split == 1) {
@@ -504,7 +508,7 @@ int dcn_tc_pack_weights(const float* weight, void* packed, int Cin, int Cout, in
 int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   TcParams p;
   const int esize = a.dtype == CPOLY_BF16 ? 2 : 4;
-  p.x = a.x.ptr; p.offset = a.offset; p.mask = a.mask; p.wpacked = a.weight_packed; p.bias = a.bias; p.scale = a.out_scale;
+  p.x = a.x.ptr; p.offset = a.offset; p.mask = a.mask; p.wpacked = a.weight_packed; p.bias = a.bias; p.scale = a.out_scale; p.offset_bias = a.offset_bias; p.mask_bias = a.mask_bias;
   p.y = a.y.ptr;
   p.B = a.B; p.Cin = a.Cin; p.Cout = a.Cout; p.H = a.H; p.W = a.W;
   p.om_dtype = a.om_dtype; p.mask_is_logit = a.mask_is_logit; p.relu = a.relu;

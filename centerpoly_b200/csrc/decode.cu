@@ -1,22 +1,27 @@
 // Fused polydet decode: [sigmoid] -> 3x3 max-pool NMS -> per-image top-K -> gather of the reg /
-// poly / pseudo-depth heads -> [polar -> cartesian] -> centre add -> bbox -> (B,K,2N+7), ONE launch.
+// poly / pseudo-depth heads -> [polar -> cartesian] -> centre add -> bbox -> (B,K,2N+7).
 //
 // Replaces (reference paths): _nms decode.py:13-19, _topk decode.py:117-133,
 // _transpose_and_gather_feat models/utils.py:22-26, polydet_decode decode.py:512-670 and optionally
 // hm.sigmoid_() detectors/polydet.py:28.  The reference runs ~25 ATen kernels and transposes the whole
-// 64-channel poly map (33.5 MB at 2048x1024) to fetch K x 64 values; here the heat map is read once
-// and only K x (2N+3) head values are gathered.
+// 64-channel poly map (33.5 MB at 2048x1024) to fetch K x 64 values; here the heat map is read from HBM once
+// (a second time from L2) and only K x (2N+3) head values are gathered.
 //
-// Structure (no inter-CTA waiting, so a single ordinary launch is safe):
-//   scan phase   every warp owns a 128-column band x RH rows of one (image, class) plane; rows roll
-//                through registers (vertical 3-max), the horizontal 3-max uses warp shuffles; a pixel is
-//                a peak iff it equals its 3x3 max (plateaus keep every member, like `hmax == heat`).
-//                Peaks are pushed as 64-bit keys (ordered score << 32 | ~flat_index) into a shared-memory
-//                list that is pruned by a block-level radix select whenever it could overflow; after the
-//                first prune the running K-th best key is a threshold that rejects most peaks at once.
-//   merge phase  each CTA publishes <= K keys; the last CTA of an image to finish (atomic ticket)
-//                radix-selects the global top-K, bitonic-sorts them (score desc, flat index asc — the
-//                oracle's tie rule), and runs the gather epilogue.
+// Exact top-K by histogram threshold, three small launches per image group (groups are sized so that a group's
+// heat maps stay L2 resident between the first two):
+//   1 scan + histogram   every warp owns a 128-column band x RH rows of one (image, class) plane; rows roll
+//                        through registers (vertical 3-max), the horizontal 3-max uses warp shuffles; a pixel is
+//                        a peak iff it equals its 3x3 max (plateaus keep every member, like `hmax == heat`).
+//                        Peaks are counted in a shared-memory histogram over the top 13 bits of the score
+//                        (32 bins per octave), flushed to the image's global histogram once per CTA.
+//   2 threshold + collect each CTA finds the bin holding the K-th best peak of its image and re-scans its items
+//                        (now L2 hits), appending the peaks at or above that bin — about K + one bin's
+//                        population — to the image's candidate list as 64-bit keys (score << 32 | ~flat index).
+//   3 select + gather    one CTA per image: radix-select the top K candidates, bitonic-sort them (score desc,
+//                        flat index asc — the oracle's tie rule), gather reg / poly / depth at the K centres,
+//                        polar -> cartesian, centre add, bbox, write (K, 2N+7).
+// Degenerate maps whose boundary bin overflows the candidate list (e.g. a constant map) take a slow exact path in
+// launch 3 (the CTA re-scans the image itself).
 //
 // The two-stage top-K of the reference (per class, then over C*K) equals the global top-K over
 // (class, y, x) whenever scores are tie-free; heat must be non-negative (it is post-sigmoid).
@@ -31,21 +36,26 @@ constexpr int DNT = 256;           // threads per CTA
 constexpr int DWARPS = DNT / 32;
 constexpr int KMAX = 1024;         // largest supported K
 constexpr int BAND = 128;          // columns per warp (4 per lane)
-constexpr int ROUND_ROWS = 2;      // rows every warp scans between two block-level checks
-constexpr int ROUND_MAX = DWARPS * BAND * ROUND_ROWS;  // most keys a round can add
-constexpr int CAP = KMAX + ROUND_MAX;                  // shared list capacity
+constexpr int CAP = 4096;          // shared key list capacity of the select kernel
+constexpr int HBITS = 13;          // histogram over score bits [30:18]: exponent + 5 mantissa bits
+constexpr int HBINS = 1 << HBITS;
+constexpr int HSHIFT = 31 - HBITS;
+constexpr int CAND_CAP = 32768;    // candidate keys per image (global)
 
 struct DecodeParams {
   int B, C, H, W, n_poly, K, rep, heat_is_logit, dtype;
   cpoly_tensor4 heat, polys, depth, reg;
   float* out;
   int64_t* out_inds;
-  unsigned long long* cand;  // [B][ctas_per_image][K]
-  int* cand_count;           // [B][ctas_per_image]
-  unsigned int* done;        // [B]
-  int rh;                    // rows per warp work item
-  int nbands, nrowchunks, items_per_image, ctas_per_image;
+  unsigned int* hist;          // [B][HBINS]
+  unsigned long long* cand;    // [B][CAND_CAP]
+  unsigned int* cand_count;    // [B]
+  int rh;                      // rows per warp work item
+  int nbands, nrowchunks, items_per_image;
+  int b0, nb;                  // image group handled by this launch (kernels 1 and 2)
 };
+
+__device__ __forceinline__ int score_bin(float v) { return (int)(__float_as_uint(v) >> HSHIFT) & (HBINS - 1); }
 
 __device__ __forceinline__ unsigned int float_to_ordered(float f) {
   const unsigned int u = __float_as_uint(f);
@@ -191,118 +201,217 @@ __device__ __forceinline__ float head_value(const cpoly_tensor4& t, int b, int c
                      (int64_t)x * t.sw);
 }
 
+
+// One warp scans its item (a 128-column band x rh rows of one class plane) and calls f(score, flat index) for
+// every NMS peak with a positive score, flat = c*H*W + y*W + x.
+template <typename T, typename F>
+__device__ __forceinline__ void scan_item(const DecodeParams& p, int b, int item, int lane, F&& f) {
+  int t = item;
+  const int band = t % p.nbands; t /= p.nbands;
+  const int rc = t % p.nrowchunks;
+  const int c = t / p.nrowchunks;
+  const int r0 = rc * p.rh, x0 = band * BAND;
+  const int HW = p.H * p.W;
+  const bool logit = p.heat_is_logit != 0;
+  const T* plane = reinterpret_cast<const T*>(p.heat.ptr) + (int64_t)b * p.heat.sb + (int64_t)c * p.heat.sc;
+  float v_cur[4], h_prev[4], h_cur[4], l, r, v[4];
+  load_row(plane, p.heat.sh, p.heat.sw, r0 - 1, p.H, p.W, x0, lane, logit, v, l, r);
+  hmax3(v, l, r, h_prev);
+  load_row(plane, p.heat.sh, p.heat.sw, r0, p.H, p.W, x0, lane, logit, v_cur, l, r);
+  hmax3(v_cur, l, r, h_cur);
+  for (int rr = 0; rr < p.rh; ++rr) {
+    const int y = r0 + rr;
+    if (y >= p.H) break;   // warp-uniform
+    float v_next[4], h_next[4];
+    load_row(plane, p.heat.sh, p.heat.sw, y + 1, p.H, p.W, x0, lane, logit, v_next, l, r);
+    hmax3(v_next, l, r, h_next);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float m = fmaxf(fmaxf(h_prev[j], h_cur[j]), h_next[j]);
+      const int x = x0 + lane * 4 + j;
+      if (x < p.W && v_cur[j] == m && v_cur[j] > 0.f) f(v_cur[j], (unsigned int)(c * HW + y * p.W + x));
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { h_prev[j] = h_cur[j]; h_cur[j] = h_next[j]; v_cur[j] = v_next[j]; }
+  }
+}
+
+// Work items of the image group [b0, b0+nb) are dealt to warps in CTA-contiguous blocks, so one CTA touches one
+// image (or two at a boundary) and flushes / thresholds once per image.
+__device__ __forceinline__ void cta_item_range(const DecodeParams& p, int64_t& beg, int64_t& end) {
+  const int64_t total = (int64_t)p.nb * p.items_per_image;
+  const int64_t per = (total + gridDim.x - 1) / gridDim.x;
+  beg = (int64_t)blockIdx.x * per;
+  end = beg + per < total ? beg + per : total;
+}
+
+// ------------------------------------------------------------------ launch 1: NMS scan + score histogram
 template <typename T>
-__global__ void __launch_bounds__(DNT) decode_kernel(DecodeParams p) {
+__global__ void __launch_bounds__(DNT) decode_hist_kernel(DecodeParams p) {
+  __shared__ unsigned int hist[HBINS];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int64_t beg, end;
+  cta_item_range(p, beg, end);
+  if (beg >= end) return;
+  int cur_b = (int)(beg / p.items_per_image);
+  for (int i = tid; i < HBINS; i += DNT) hist[i] = 0u;
+  __syncthreads();
+  for (int64_t base = beg; base < end; base += DWARPS) {
+    // all warps of an iteration work on the same image: stop the batch at the image boundary
+    const int64_t img_end = (int64_t)(cur_b + 1) * p.items_per_image;
+    const int64_t lim = end < img_end ? end : img_end;
+    const int64_t it = base + warp;
+    if (it < lim) {
+      scan_item<T>(p, p.b0 + cur_b, (int)(it - (int64_t)cur_b * p.items_per_image), lane,
+                   [&](float s, unsigned int) { atomicAdd(&hist[score_bin(s)], 1u); });
+    }
+    if (base + DWARPS >= lim) {   // uniform: image (or range) finished -> flush
+      __syncthreads();
+      unsigned int* gh = p.hist + (int64_t)(p.b0 + cur_b) * HBINS;
+      for (int i = tid; i < HBINS; i += DNT) {
+        const unsigned int n = hist[i];
+        if (n) { atomicAdd(gh + i, n); hist[i] = 0u; }
+      }
+      __syncthreads();
+      if (lim < end) {            // continue with the next image; re-align the batch start
+        cur_b += 1;
+        base = lim - DWARPS;      // loop increment brings it to `lim`
+      }
+    }
+  }
+}
+
+// Bin holding the K-th best peak of the image: smallest tb with count(bins >= tb) >= K (0 if there are fewer
+// than K peaks).  All DNT threads call it; `sh` is HBINS ints of shared scratch.
+__device__ int threshold_bin(const unsigned int* __restrict__ gh, int K, unsigned int* sh, int* s_result) {
+  const int tid = threadIdx.x;
+  constexpr int PER = HBINS / DNT;   // bins per thread, thread t owns the descending range starting at HBINS-1-t*PER
+  unsigned int mine = 0;
+#pragma unroll 4
+  for (int q = 0; q < PER; ++q) {
+    const unsigned int n = __ldcg(gh + (HBINS - 1 - tid * PER - q));
+    sh[HBINS - 1 - tid * PER - q] = n;
+    mine += n;
+  }
+  // inclusive scan of per-thread sums over the block (descending bin order)
+  __shared__ unsigned int warp_tot[DWARPS];
+  unsigned int incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if ((tid & 31) >= d) incl += t;
+  }
+  if ((tid & 31) == 31) warp_tot[tid >> 5] = incl;
+  if (tid == 0) *s_result = 0;
+  __syncthreads();
+  unsigned int before = 0;
+  for (int w = 0; w < (tid >> 5); ++w) before += warp_tot[w];
+  incl += before;
+  const unsigned int excl = incl - mine;
+  if (excl < (unsigned)K && incl >= (unsigned)K) {
+    unsigned int run = excl;
+    for (int q = 0; q < PER; ++q) {
+      run += sh[HBINS - 1 - tid * PER - q];
+      if (run >= (unsigned)K) { *s_result = HBINS - 1 - tid * PER - q; break; }
+    }
+  }
+  __syncthreads();
+  return *s_result;
+}
+
+// ------------------------------------------------------------------ launch 2: threshold + candidate collection
+template <typename T>
+__global__ void __launch_bounds__(DNT) decode_collect_kernel(DecodeParams p) {
+  __shared__ unsigned int sh[HBINS];
+  __shared__ int s_tb;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int64_t beg, end;
+  cta_item_range(p, beg, end);
+  if (beg >= end) return;
+  int cur_b = (int)(beg / p.items_per_image);
+  int tb = threshold_bin(p.hist + (int64_t)(p.b0 + cur_b) * HBINS, p.K, sh, &s_tb);
+  for (int64_t base = beg; base < end; base += DWARPS) {
+    const int64_t img_end = (int64_t)(cur_b + 1) * p.items_per_image;
+    const int64_t lim = end < img_end ? end : img_end;
+    const int64_t it = base + warp;
+    if (it < lim) {
+      const int b = p.b0 + cur_b;
+      unsigned long long* cand = p.cand + (int64_t)b * CAND_CAP;
+      unsigned int* cnt = p.cand_count + b;
+      scan_item<T>(p, b, (int)(it - (int64_t)cur_b * p.items_per_image), lane, [&](float s, unsigned int flat) {
+        if (score_bin(s) >= tb) {
+          const unsigned int pos = atomicAdd(cnt, 1u);   // the compiler aggregates same-address atomics per warp
+          if (pos < (unsigned)CAND_CAP) cand[pos] = make_key(s, flat);
+        }
+      });
+    }
+    if (base + DWARPS >= lim && lim < end) {   // uniform: next image
+      cur_b += 1;
+      base = lim - DWARPS;
+      tb = threshold_bin(p.hist + (int64_t)(p.b0 + cur_b) * HBINS, p.K, sh, &s_tb);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ launch 3: select + sort + gather (one CTA per image)
+template <typename T>
+__global__ void __launch_bounds__(DNT) decode_select_kernel(DecodeParams p) {
   __shared__ unsigned long long list[CAP];
   __shared__ SelectScratch scratch;
   __shared__ int s_count;
-  __shared__ int s_is_last;
   __shared__ unsigned char s_taken[KMAX];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int b = blockIdx.y;
+  const int b = blockIdx.x;
   const int K = p.K;
   const int HW = p.H * p.W;
-  const bool logit = p.heat_is_logit != 0;
-
-  if (tid == 0) s_count = 0;
-  __syncthreads();
-
-  // ------------------------------------------------------------------ scan phase
-  const int item = blockIdx.x * DWARPS + warp;
-  const bool active = item < p.items_per_image;
-  int c = 0, r0 = 0, x0 = 0;
-  if (active) {
-    int t = item;
-    const int band = t % p.nbands; t /= p.nbands;
-    const int rc = t % p.nrowchunks;
-    c = t / p.nrowchunks;
-    r0 = rc * p.rh;
-    x0 = band * BAND;
-  }
-  const T* plane = reinterpret_cast<const T*>(p.heat.ptr) + (int64_t)b * p.heat.sb + (int64_t)c * p.heat.sc;
-  unsigned long long threshold = 0ull;  // keys <= threshold cannot enter the top-K any more
-
-  float v_cur[4], h_prev[4], h_cur[4];
-  {
-    float l, r, v[4];
-    if (active) {
-      load_row(plane, p.heat.sh, p.heat.sw, r0 - 1, p.H, p.W, x0, lane, logit, v, l, r);
-      hmax3(v, l, r, h_prev);
-      load_row(plane, p.heat.sh, p.heat.sw, r0, p.H, p.W, x0, lane, logit, v_cur, l, r);
-      hmax3(v_cur, l, r, h_cur);
+  const unsigned int total = __ldcg(p.cand_count + b);
+  int n = 0;
+  if (total <= (unsigned)CAND_CAP) {
+    // ---- normal path: the candidate list holds every peak at or above the threshold bin
+    const unsigned long long* src = p.cand + (int64_t)b * CAND_CAP;
+    for (unsigned int off = 0; off < total;) {
+      if (n == CAP) {  // uniform
+        block_select_topk(list, n, K, scratch);
+        n = K;
+      }
+      const unsigned int take = min((unsigned)(CAP - n), total - off);
+      for (unsigned int i = tid; i < take; i += DNT) list[n + i] = __ldcg(src + off + i);
+      n += (int)take;
+      off += take;
+      __syncthreads();
     }
-  }
-  for (int rr = 0; rr < p.rh; rr += ROUND_ROWS) {
-    if (active) {
-#pragma unroll
-      for (int q = 0; q < ROUND_ROWS; ++q) {
-        const int y = r0 + rr + q;
-        float v_next[4], h_next[4], l, r;
-        load_row(plane, p.heat.sh, p.heat.sw, y + 1, p.H, p.W, x0, lane, logit, v_next, l, r);
-        hmax3(v_next, l, r, h_next);
-        if (y < p.H) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float m = fmaxf(fmaxf(h_prev[j], h_cur[j]), h_next[j]);
-            const int x = x0 + lane * 4 + j;
-            if (x < p.W && v_cur[j] == m && v_cur[j] > 0.f) {
-              const unsigned long long key = make_key(v_cur[j], (unsigned int)(c * HW + y * p.W + x));
-              if (key > threshold) {
-                const int pos = atomicAdd(&s_count, 1);
-                if (pos < CAP) list[pos] = key;  // cannot overflow: a prune precedes any round that could
-              }
-            }
+  } else {
+    // ---- slow exact path (degenerate map: the boundary bin alone overflows the candidate list): this CTA re-scans
+    // the image two rows per warp and round, pruning the shared list with a block radix select whenever it could
+    // overflow; after the first prune the K-th best key is a threshold that rejects most peaks at once.
+    DecodeParams q = p;
+    q.rh = 2;
+    q.nrowchunks = (p.H + 1) / 2;
+    q.items_per_image = p.C * q.nrowchunks * q.nbands;
+    constexpr int ROUND_MAX = DWARPS * BAND * 2;
+    unsigned long long threshold = 0ull;
+    if (tid == 0) s_count = 0;
+    __syncthreads();
+    for (int base = 0; base < q.items_per_image; base += DWARPS) {
+      const int it = base + warp;
+      if (it < q.items_per_image) {
+        scan_item<T>(q, b, it, lane, [&](float s, unsigned int flat) {
+          const unsigned long long key = make_key(s, flat);
+          if (key > threshold) {
+            const int pos = atomicAdd(&s_count, 1);
+            if (pos < CAP) list[pos] = key;  // cannot overflow: a prune precedes any round that could
           }
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { h_prev[j] = h_cur[j]; h_cur[j] = h_next[j]; v_cur[j] = v_next[j]; }
+        });
+      }
+      __syncthreads();
+      if (s_count > CAP - ROUND_MAX) {  // uniform
+        threshold = block_select_topk(list, s_count, K, scratch);
+        if (tid == 0) s_count = K;
+        __syncthreads();
       }
     }
-    __syncthreads();
-    const int n = s_count;
-    if (n > CAP - ROUND_MAX) {  // uniform branch
-      threshold = block_select_topk(list, n, K, scratch);
-      if (tid == 0) s_count = K;
-      __syncthreads();
-    }
-  }
-  {
-    const int n = s_count;
-    if (n > K) {
-      block_select_topk(list, n, K, scratch);
-      if (tid == 0) s_count = K;
-      __syncthreads();
-    }
-  }
-  // ------------------------------------------------------------------ publish + ticket
-  const int my_count = s_count;
-  unsigned long long* my_cand = p.cand + ((int64_t)b * p.ctas_per_image + blockIdx.x) * K;
-  for (int i = tid; i < my_count; i += DNT) my_cand[i] = list[i];
-  if (tid == 0) p.cand_count[b * p.ctas_per_image + blockIdx.x] = my_count;
-  __threadfence();
-  __syncthreads();
-  if (tid == 0) {
-    const unsigned int ticket = atomicAdd(&p.done[b], 1u);
-    s_is_last = (ticket == (unsigned int)p.ctas_per_image - 1u);
-  }
-  __syncthreads();
-  if (!s_is_last) return;
-  __threadfence();
-
-  // ------------------------------------------------------------------ merge phase (one CTA per image)
-  if (tid == 0) s_count = 0;
-  __syncthreads();
-  int n = 0;
-  for (int j = 0; j < p.ctas_per_image; ++j) {
-    const int cnt = __ldcg(p.cand_count + b * p.ctas_per_image + j);
-    const unsigned long long* src = p.cand + ((int64_t)b * p.ctas_per_image + j) * K;
-    if (n + cnt > CAP) {  // uniform
-      block_select_topk(list, n, K, scratch);
-      n = K;
-    }
-    for (int i = tid; i < cnt; i += DNT) list[n + i] = __ldcg(src + i);
-    n += cnt;
+    n = s_count;
     __syncthreads();
   }
   if (n > K) {
@@ -347,7 +456,7 @@ __global__ void __launch_bounds__(DNT) decode_kernel(DecodeParams p) {
       __syncthreads();
     }
 
-  // ------------------------------------------------------------------ gather epilogue: one warp per detection
+  // ---- gather epilogue: one warp per detection
   const int N = p.n_poly / 2;
   const int row_len = p.n_poly + 7;
   for (int k = warp; k < K; k += DWARPS) {
@@ -403,19 +512,11 @@ __global__ void __launch_bounds__(DNT) decode_kernel(DecodeParams p) {
 }
 
 void plan(int B, int C, int H, int W, DecodeParams& p) {
+  (void)B;
   p.nbands = (W + BAND - 1) / BAND;
-  int rh = 32;
-  // enough CTAs to cover the machine a couple of times when the problem allows it
-  while (rh > ROUND_ROWS) {
-    const int64_t items = (int64_t)C * ((H + rh - 1) / rh) * p.nbands;
-    const int64_t ctas = (items + DWARPS - 1) / DWARPS * B;
-    if (ctas >= 2 * 148) break;
-    rh >>= 1;
-  }
-  p.rh = rh;
-  p.nrowchunks = (H + rh - 1) / rh;
+  p.rh = 8;
+  p.nrowchunks = (H + p.rh - 1) / p.rh;
   p.items_per_image = C * p.nrowchunks * p.nbands;
-  p.ctas_per_image = (p.items_per_image + DWARPS - 1) / DWARPS;
 }
 
 size_t align256(size_t v) { return (v + 255) / 256 * 256; }
@@ -423,10 +524,9 @@ size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 }  // namespace
 
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K) {
-  DecodeParams p;
-  plan(B, C, H, W, p);
-  return align256((size_t)B * p.ctas_per_image * K * sizeof(unsigned long long)) +
-         align256((size_t)B * p.ctas_per_image * sizeof(int)) + align256((size_t)B * sizeof(unsigned int)) + 256;
+  (void)C; (void)H; (void)W; (void)K;
+  return align256((size_t)B * HBINS * sizeof(unsigned int) + (size_t)B * sizeof(unsigned int)) +
+         align256((size_t)B * CAND_CAP * sizeof(unsigned long long)) + 256;
 }
 
 int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
@@ -441,16 +541,36 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
                 "decode workspace too small: need %zu bytes, have %zu", need, a.workspace_bytes);
   CPOLY_REQUIRE((reinterpret_cast<uintptr_t>(a.workspace) & 255) == 0, CPOLY_EINVAL, "decode workspace must be 256-byte aligned");
   char* ws = reinterpret_cast<char*>(a.workspace);
+  const size_t zero_bytes = (size_t)a.B * HBINS * sizeof(unsigned int) + (size_t)a.B * sizeof(unsigned int);
+  p.hist = reinterpret_cast<unsigned int*>(ws);
+  p.cand_count = p.hist + (size_t)a.B * HBINS;
+  ws += align256(zero_bytes);
   p.cand = reinterpret_cast<unsigned long long*>(ws);
-  ws += align256((size_t)a.B * p.ctas_per_image * a.K * sizeof(unsigned long long));
-  p.cand_count = reinterpret_cast<int*>(ws);
-  ws += align256((size_t)a.B * p.ctas_per_image * sizeof(int));
-  p.done = reinterpret_cast<unsigned int*>(ws);
-  CPOLY_CUDA_OK(cudaMemsetAsync(p.done, 0, (size_t)a.B * sizeof(unsigned int), stream));
-  dim3 grid((unsigned)p.ctas_per_image, (unsigned)a.B);
-  if (a.dtype == CPOLY_BF16) decode_kernel<__nv_bfloat16><<<grid, DNT, 0, stream>>>(p);
-  else decode_kernel<float><<<grid, DNT, 0, stream>>>(p);
-  return check_launch("decode_kernel");
+  CPOLY_CUDA_OK(cudaMemsetAsync(p.hist, 0, zero_bytes, stream));
+  int dev = 0, sms = 0;
+  CPOLY_CUDA_OK(cudaGetDevice(&dev));
+  CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  // image groups whose heat maps (<= 48 MB) stay L2 resident between the histogram and the collection pass
+  const size_t img_bytes = (size_t)a.C * a.H * a.W * (a.dtype == CPOLY_BF16 ? 2 : 4);
+  int group = (int)((48u << 20) / (img_bytes ? img_bytes : 1));
+  if (group < 1) group = 1;
+  const bool bf = a.dtype == CPOLY_BF16;
+  for (int b0 = 0; b0 < a.B; b0 += group) {
+    p.b0 = b0;
+    p.nb = a.B - b0 < group ? a.B - b0 : group;
+    const int64_t items = (int64_t)p.nb * p.items_per_image;
+    int64_t ctas = (items + DWARPS - 1) / DWARPS;
+    if (ctas > 2 * sms) ctas = 2 * sms;
+    if (bf) decode_hist_kernel<__nv_bfloat16><<<(unsigned)ctas, DNT, 0, stream>>>(p);
+    else decode_hist_kernel<float><<<(unsigned)ctas, DNT, 0, stream>>>(p);
+    if (int rc = check_launch("decode_hist_kernel")) return rc;
+    if (bf) decode_collect_kernel<__nv_bfloat16><<<(unsigned)ctas, DNT, 0, stream>>>(p);
+    else decode_collect_kernel<float><<<(unsigned)ctas, DNT, 0, stream>>>(p);
+    if (int rc = check_launch("decode_collect_kernel")) return rc;
+  }
+  if (bf) decode_select_kernel<__nv_bfloat16><<<(unsigned)a.B, DNT, 0, stream>>>(p);
+  else decode_select_kernel<float><<<(unsigned)a.B, DNT, 0, stream>>>(p);
+  return check_launch("decode_select_kernel");
 }
 
 }  // namespace cpoly

@@ -16,6 +16,7 @@ struct UpParams {
   int B, C, H, W, f, Ho, Wo;
   cpoly_tensor4 x, skip, y;
   const float* w;
+  int w_tapmajor;
 };
 
 template <typename T, int VEC>
@@ -86,9 +87,21 @@ __global__ void __launch_bounds__(256) upsample_nhwc_kernel(UpParams p) {
         if (ix < 0 || ix >= p.W) continue;
         float v[VEC];
         Vec<T, VEC>::load(xg + (int64_t)b * p.x.sb + (int64_t)iy * p.x.sh + (int64_t)ix * p.x.sw + c0, v);
-        const float* wp = p.w + ((int64_t)c0 * K + ky) * K + kx;
+        if (p.w_tapmajor) {   // (2f*2f, C): the piece's channels are contiguous
+          const float4* wp = reinterpret_cast<const float4*>(p.w + (int64_t)(ky * K + kx) * p.C + c0);
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) acc[j] = fmaf(v[j], __ldg(wp + (int64_t)j * K * K), acc[j]);
+          for (int j = 0; j < VEC / 4; ++j) {
+            const float4 w4 = __ldg(wp + j);
+            acc[4 * j] = fmaf(v[4 * j], w4.x, acc[4 * j]);
+            acc[4 * j + 1] = fmaf(v[4 * j + 1], w4.y, acc[4 * j + 1]);
+            acc[4 * j + 2] = fmaf(v[4 * j + 2], w4.z, acc[4 * j + 2]);
+            acc[4 * j + 3] = fmaf(v[4 * j + 3], w4.w, acc[4 * j + 3]);
+          }
+        } else {
+          const float* wp = p.w + ((int64_t)c0 * K + ky) * K + kx;
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) acc[j] = fmaf(v[j], __ldg(wp + (int64_t)j * K * K), acc[j]);
+        }
       }
     }
     Vec<T, VEC>::store(yg + (int64_t)b * p.y.sb + (int64_t)oy * p.y.sh + (int64_t)ox * p.y.sw + c0, acc);
@@ -119,7 +132,7 @@ __global__ void __launch_bounds__(256) upsample_generic_kernel(UpParams p) {
         const int ix = ix1 - dx, kx = kx1 + dx * p.f;
         if (ix < 0 || ix >= p.W) continue;
         acc = fmaf(ld_as_float(xg + (int64_t)b * p.x.sb + (int64_t)c * p.x.sc + (int64_t)iy * p.x.sh + (int64_t)ix * p.x.sw),
-                   __ldg(p.w + ((int64_t)c * K + ky) * K + kx), acc);
+                   __ldg(p.w_tapmajor ? p.w + (int64_t)(ky * K + kx) * p.C + c : p.w + ((int64_t)c * K + ky) * K + kx), acc);
       }
     }
     st_from_float(yg + (int64_t)b * p.y.sb + (int64_t)c * p.y.sc + (int64_t)oy * p.y.sh + (int64_t)ox * p.y.sw, acc);
@@ -136,7 +149,7 @@ bool vec_ok(const cpoly_tensor4& t, int vec_bytes_elems) {
 int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream) {
   UpParams p;
   p.B = a.B; p.C = a.C; p.H = a.H; p.W = a.W; p.f = a.f; p.Ho = a.H * a.f; p.Wo = a.W * a.f;
-  p.x = a.x; p.skip = a.skip; p.y = a.y; p.w = a.weight;
+  p.x = a.x; p.skip = a.skip; p.y = a.y; p.w = a.weight; p.w_tapmajor = a.weight_tap_major;
   const bool bf = a.dtype == CPOLY_BF16;
   const int vec = bf ? 8 : 4;
   const bool fast = a.C % vec == 0 && vec_ok(a.x, vec) && vec_ok(a.skip, vec) && vec_ok(a.y, vec);

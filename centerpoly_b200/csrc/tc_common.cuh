@@ -39,12 +39,14 @@ __device__ __noinline__ void mbar_timeout(uint32_t bar, uint32_t parity) {
          threadIdx.x, bar, parity);
   __trap();
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+// `sleep_ns`: back-off between polls.  Roles that wait for most of a tile (weight loader, epilogue, MMA issuer
+// behind slow producers) pass a long sleep so that their polling does not take issue slots from the samplers.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, uint32_t sleep_ns = 32) {
   if (mbar_try_wait(bar, parity, 2000u)) return;
   const long long t0 = clock64();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity, 20000u)) {
-    __nanosleep(40);  // the hardware suspend of try_wait is short: do not burn issue slots the samplers need
+    __nanosleep(sleep_ns);
     if ((++spins & 63u) == 0u && clock64() - t0 > WAIT_TIMEOUT_CYCLES) mbar_timeout(bar, parity);
   }
 }

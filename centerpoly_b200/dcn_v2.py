@@ -76,7 +76,7 @@ _GLOBAL_PACK_CACHE = _PackedWeights()
 
 
 def _fwd_args(x, offset, mask, weight32, bias32, stride, padding, dilation, dg, mask_is_logit, packed, y,
-              wshape=None, out_scale=None, relu=False):
+              wshape=None, out_scale=None, relu=False, om_bias=None):
     a = _lib.DcnFwdArgs()
     a.B, a.Cin, a.H, a.W = x.shape
     a.Cout, _, a.kh, a.kw = wshape if wshape is not None else weight32.shape
@@ -95,6 +95,10 @@ def _fwd_args(x, offset, mask, weight32, bias32, stride, padding, dilation, dg, 
     a.y = _lib.t4(y)
     a.out_scale = out_scale.data_ptr() if out_scale is not None else None
     a.relu = int(bool(relu))
+    if om_bias is not None:   # fp32 (3*dg*kh*kw): offsets first, then mask logits
+        n_off = a.deformable_groups * 2 * a.kh * a.kw
+        a.offset_bias = om_bias.data_ptr()
+        a.mask_bias = om_bias.data_ptr() + 4 * n_off
     return a
 
 
@@ -122,7 +126,8 @@ def _check_shapes(x, offset, mask, weight, stride, padding, dilation, dg):
     return Ho, Wo
 
 
-def _forward_impl(x, offset, mask, weight, bias, stride, padding, dilation, dg, mask_is_logit, out_scale=None, relu=False):
+def _forward_impl(x, offset, mask, weight, bias, stride, padding, dilation, dg, mask_is_logit, out_scale=None, relu=False,
+                  om_bias=None):
     """y = act(out_scale * dcn(x) + bias); out_scale/relu are the optional fused DeformConv epilogue."""
     dev = _lib.require_cuda(x, offset, mask, weight, bias)
     Ho, Wo = _check_shapes(x, offset, mask, weight, stride, padding, dilation, dg)
@@ -137,7 +142,7 @@ def _forward_impl(x, offset, mask, weight, bias, stride, padding, dilation, dg, 
         b32 = _as_f32_contig(bias)
         s32 = _as_f32_contig(out_scale)
         a = _fwd_args(x, offset, mask, None, b32, stride, padding, dilation, dg, mask_is_logit, packed, y,
-                      wshape=weight.shape, out_scale=s32, relu=relu)
+                      wshape=weight.shape, out_scale=s32, relu=relu, om_bias=om_bias)
         use_tc = packed is not None and L.cpoly_dcn_tcgen05_eligible(byref(a))
         if use_tc:
             nbytes = L.cpoly_dcn_forward_workspace_bytes(byref(a))
@@ -297,17 +302,37 @@ class DCN(DCNv2):
             self.conv_offset_mask.weight.zero_()
             self.conv_offset_mask.bias.zero_()
 
+    def _padded_offset_conv(self):
+        """(weight padded to a multiple of 8 output channels, fp32 bias): derived cache, never in state_dict."""
+        w, b = self.conv_offset_mask.weight, self.conv_offset_mask.bias
+        tag = (w._version, w.data_ptr(), w.dtype, w.device, b._version, b.data_ptr())
+        hit = getattr(self, "_om_cache", None)
+        if hit is None or hit[0] != tag:
+            n = w.shape[0]
+            npad = (n + 7) // 8 * 8
+            wp = torch.zeros((npad,) + tuple(w.shape[1:]), dtype=w.dtype, device=w.device)
+            wp[:n] = w.detach()
+            wp = wp.contiguous(memory_format=torch.channels_last)
+            hit = (tag, wp, b.detach().float().contiguous())
+            self._om_cache = hit
+        return hit[1], hit[2]
+
     def forward(self, input):
-        om = self.conv_offset_mask(input)
         fused = getattr(self, "_fused_epilogue", None)
         if fused is not None:
-            # inference-only DeformConv fusion installed by centerpoly_b200.fuse (eval-mode BN + ReLU in the epilogue)
+            # inference-only DeformConv fusion installed by centerpoly_b200.fuse: eval-mode BN + ReLU in the epilogue,
+            # the offset conv runs bias-free with its 27 output channels padded to 32 (no cuDNN padding kernels, no
+            # separate bias add) and the kernel adds conv_offset_mask.bias itself.
             if torch.is_grad_enabled() and (input.requires_grad or self.weight.requires_grad):
-                raise RuntimeError("the fused DeformConv epilogue is inference-only; call fuse.unfuse(model) before training")
+                raise RuntimeError("the fused DeformConv epilogue is inference-only; rebuild the model for training")
             scale, shift, relu = fused
-            n_off = om.shape[1] // 3 * 2
-            y, _ = _forward_impl(input, om[:, :n_off], om[:, n_off:], self.weight, shift, self.stride, self.padding,
-                                 self.dilation, self.deformable_groups, True, out_scale=scale, relu=relu)
+            w_om, b_om = self._padded_offset_conv()
+            om = torch.nn.functional.conv2d(input, w_om, None, self.stride, self.padding)
+            n_off = self.deformable_groups * 2 * self.kernel_size[0] * self.kernel_size[1]
+            n_all = n_off // 2 * 3
+            y, _ = _forward_impl(input, om[:, :n_off], om[:, n_off:n_all], self.weight, shift, self.stride, self.padding,
+                                 self.dilation, self.deformable_groups, True, out_scale=scale, relu=relu, om_bias=b_om)
             return y
+        om = self.conv_offset_mask(input)
         return _DCNFused.apply(input, om, self.weight, self.bias, self.stride, self.padding, self.dilation,
                                self.deformable_groups)

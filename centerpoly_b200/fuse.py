@@ -3,14 +3,17 @@
     model = create_model(...).eval().cuda()
     centerpoly_b200.fuse.optimize_for_inference(model)
 
-No file of the reference is edited; every rewrite is on the live module tree and keeps ``state_dict`` keys:
+No file of the reference is edited; every rewrite is on the live module tree.  Load the checkpoint FIRST: the DCN,
+deconvolution and convolution parameters keep their names, but the folded BatchNorm tensors leave ``state_dict``.
 
 * ``DeformConv`` (pose_dla_dcn.py:347-359: DCN -> BatchNorm2d -> ReLU): the eval-mode BN affine and the ReLU move
   into the DCN kernel's epilogue (``y = relu(scale * conv + shift)``), removing two elementwise passes per layer.
 * ``IDAUp`` (pose_dla_dcn.py:362-387): ``up_i`` (depthwise ConvTranspose2d) becomes one streaming kernel that also
   performs the ``layers[i] + layers[i-1]`` of :387.
 * plain ``Conv2d -> BatchNorm2d`` pairs of the DLA backbone (BasicBlock :42-69, Root :167-185, Tree.project,
-  base_layer / level0 / level1) are folded into the convolution weights (exact in eval mode).
+  base_layer / level0 / level1) are folded into the convolution weights (exact in eval mode), and the resulting
+  conv+bias+ReLU / conv+bias+residual+ReLU sites run as single cuDNN fused calls (backbone and heads are not the
+  hot path and stay in cuDNN).
 
 Inference only: the rewritten model raises if asked for gradients.
 """
@@ -25,7 +28,7 @@ from torch.nn.utils.fusion import fuse_conv_bn_eval
 from .dcn_v2 import DCN
 from .neck import IDAUpsample
 
-__all__ = ["optimize_for_inference", "fuse_deform_convs", "fuse_idaup", "fold_conv_bn"]
+__all__ = ["optimize_for_inference", "fuse_deform_convs", "fuse_idaup", "fold_conv_bn", "fuse_backbone_cudnn"]
 
 
 def _bn_affine(bn: nn.BatchNorm2d):
@@ -106,10 +109,128 @@ def fold_conv_bn(model: nn.Module) -> int:
     return n
 
 
-def optimize_for_inference(model: nn.Module) -> dict:
-    """Apply every rewrite; the model must be in eval mode and on its CUDA device.  Returns counts."""
+# ---- backbone (NOT the hot path; stays in cuDNN): conv+bias+ReLU and conv+bias+residual+ReLU as single cuDNN calls
+def _conv_args(c: nn.Conv2d):
+    return c.stride, c.padding, c.dilation, c.groups
+
+
+def _conv_relu(c: nn.Conv2d, x):
+    return torch.cudnn_convolution_relu(x, c.weight, c.bias, *_conv_args(c))
+
+
+def _conv_add_relu(c: nn.Conv2d, x, z):
+    return torch.cudnn_convolution_add_relu(x, c.weight, z, 1.0, c.bias, *_conv_args(c))
+
+
+class _ConvReLU(nn.Module):
+    """Conv2d (BN already folded) + ReLU as one cuDNN call; keeps the conv as a sub-module (same state_dict keys)."""
+
+    def __init__(self, conv):
+        super().__init__()
+        self.conv = conv
+
+    def forward(self, x):
+        return _conv_relu(self.conv, x)
+
+
+def _basic_block_forward(self, x, residual=None):
+    """BasicBlock.forward (pose_dla_dcn.py:55-69) after BN folding: two fused cuDNN calls."""
+    if residual is None:
+        residual = x
+    return _conv_add_relu(self.conv2, _conv_relu(self.conv1, x), residual)
+
+
+def _root_forward(self, *x):
+    """Root.forward (pose_dla_dcn.py:176-185) after BN folding."""
+    children = x
+    cat = torch.cat(x, 1)
+    if getattr(self, "residual", False):
+        return _conv_add_relu(self.conv, cat, children[0])
+    return _conv_relu(self.conv, cat)
+
+
+def _cudnn_fused_ops_work(device, dtype) -> bool:
+    try:
+        x = torch.randn(1, 16, 8, 8, device=device, dtype=dtype).contiguous(memory_format=torch.channels_last)
+        w = torch.randn(16, 16, 3, 3, device=device, dtype=dtype).contiguous(memory_format=torch.channels_last)
+        b = torch.zeros(16, device=device, dtype=dtype)
+        y = torch.cudnn_convolution_relu(x, w, b, (1, 1), (1, 1), (1, 1), 1)
+        torch.cudnn_convolution_add_relu(x, w, y, 1.0, b, (1, 1), (1, 1), (1, 1), 1)
+        return True
+    except Exception:
+        return False
+
+
+def _plain_conv(c):
+    return type(c) is nn.Conv2d and c.bias is not None and c.padding_mode == "zeros" and isinstance(c.padding, tuple)
+
+
+def fuse_backbone_cudnn(model: nn.Module) -> int:
+    """After fold_conv_bn: route Conv+ReLU / Conv+residual+ReLU of the DLA backbone and heads through cuDNN's fused
+    conv-bias-activation engines (removes the separate bias-add, residual-add and ReLU kernels).  Call it AFTER the
+    model has its final dtype.  Returns the number of rewritten sites (0 if cuDNN lacks the fused engines here)."""
+    p = next(model.parameters())
+    if not p.is_cuda or not _cudnn_fused_ops_work(p.device, p.dtype):
+        return 0
+    n = 0
+    for m in model.modules():
+        if isinstance(m, nn.Sequential):
+            keys = list(m._modules.keys())
+            for i, a in enumerate(keys):
+                ca = m._modules[a]
+                if not _plain_conv(ca):
+                    continue
+                j = i + 1
+                while j < len(keys) and isinstance(m._modules[keys[j]], nn.Identity):
+                    j += 1
+                if j < len(keys) and isinstance(m._modules[keys[j]], nn.ReLU):
+                    m._modules[a] = _ConvReLU(ca)
+                    m._modules[keys[j]] = nn.Identity()
+                    n += 1
+            continue
+        ident = lambda name: isinstance(getattr(m, name, None), nn.Identity)
+        if (_plain_conv(getattr(m, "conv1", None)) and _plain_conv(getattr(m, "conv2", None)) and ident("bn1") and
+                ident("bn2") and not hasattr(m, "conv3") and isinstance(getattr(m, "relu", None), nn.ReLU)):
+            m.forward = types.MethodType(_basic_block_forward, m)
+            n += 2
+        elif (_plain_conv(getattr(m, "conv", None)) and ident("bn") and isinstance(getattr(m, "relu", None), nn.ReLU) and
+              not hasattr(m, "actf")):
+            m.forward = types.MethodType(_root_forward, m)
+            n += 1
+    return n
+
+
+def pad_stem_input_channels(model: nn.Module, multiple: int = 8) -> int:
+    """Zero-pad the input channels of the stem convolution (3 -> 8) so cuDNN can use its NHWC tensor-core kernels
+    for it (with 3 input channels it converts the frame to fp32 and runs a generic kernel: 12 % of a bf16 frame).
+    Exact: the extra weights are zero.  The caller must feed inputs with the returned channel count (extra channels
+    zero).  Returns the new channel count (unchanged if no stem was found)."""
+    for parent in model.modules():
+        for name, c in list(parent._modules.items()):
+            if type(c) is nn.Conv2d and c.in_channels == 3 and c.groups == 1:
+                cin = (3 + multiple - 1) // multiple * multiple
+                new = nn.Conv2d(cin, c.out_channels, c.kernel_size, c.stride, c.padding, c.dilation, 1, c.bias is not None)
+                new = new.to(device=c.weight.device, dtype=c.weight.dtype)
+                with torch.no_grad():
+                    new.weight.zero_()
+                    new.weight[:, :3] = c.weight
+                    if c.bias is not None:
+                        new.bias.copy_(c.bias)
+                new = new.to(memory_format=torch.channels_last)
+                parent._modules[name] = new
+                return cin
+    return 3
+
+
+def optimize_for_inference(model: nn.Module, dtype: torch.dtype | None = None) -> dict:
+    """Apply every rewrite; the model must be in eval mode and on its CUDA device (load the checkpoint first: the
+    folded BatchNorm parameters leave the state_dict).  ``dtype`` (e.g. torch.bfloat16) casts the model after the
+    fp32 folding and before the cuDNN fused-op rewrite.  Returns counts."""
     if model.training:
         raise RuntimeError("optimize_for_inference needs model.eval()")
     with torch.no_grad():
         stats = dict(deform_convs=fuse_deform_convs(model), upsamplers=fuse_idaup(model), conv_bn=fold_conv_bn(model))
+        if dtype is not None:
+            model.to(dtype)
+        stats["cudnn_fused"] = fuse_backbone_cudnn(model)
     return stats

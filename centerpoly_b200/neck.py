@@ -17,10 +17,13 @@ from . import _lib
 __all__ = ["idaup_upsample", "IDAUpsample"]
 
 
-def idaup_upsample(x: torch.Tensor, weight: torch.Tensor, f: int, skip: torch.Tensor | None = None) -> torch.Tensor:
-    """conv_transpose2d(x, weight, stride=f, padding=f//2, groups=C) [+ skip]; x (B,C,H,W) -> (B,C,H*f,W*f)."""
+def idaup_upsample(x: torch.Tensor, weight: torch.Tensor, f: int, skip: torch.Tensor | None = None,
+                   tap_major: bool = False) -> torch.Tensor:
+    """conv_transpose2d(x, weight, stride=f, padding=f//2, groups=C) [+ skip]; x (B,C,H,W) -> (B,C,H*f,W*f).
+    ``weight`` is the parameter (C,1,2f,2f), or with ``tap_major`` its derived (2f*2f, C) fp32 transpose."""
     dev = _lib.require_cuda(x, weight, skip)
-    if x.dim() != 4 or tuple(weight.shape) != (x.shape[1], 1, 2 * f, 2 * f):
+    want = (4 * f * f, x.shape[1]) if tap_major else (x.shape[1], 1, 2 * f, 2 * f)
+    if x.dim() != 4 or tuple(weight.shape) != want:
         raise RuntimeError(f"idaup_upsample: weight {tuple(weight.shape)} does not match C={x.shape[1]}, f={f}")
     B, C, H, W = x.shape
     if skip is not None and (tuple(skip.shape) != (B, C, H * f, W * f) or skip.dtype != x.dtype):
@@ -35,6 +38,7 @@ def idaup_upsample(x: torch.Tensor, weight: torch.Tensor, f: int, skip: torch.Te
         a = _lib.UpsampleArgs()
         a.B, a.C, a.H, a.W, a.f = B, C, H, W, f
         a.dtype = _lib.dtype_code(x)
+        a.weight_tap_major = int(tap_major)
         a.x, a.skip, a.y = _lib.t4(x), _lib.t4(skip), _lib.t4(y)
         a.weight = w32.data_ptr()
         _lib.check(_lib.lib().cpoly_idaup_upsample_forward(byref(a), _lib.stream_ptr(dev)), "cpoly_idaup_upsample_forward")
@@ -54,12 +58,11 @@ class IDAUpsample(nn.Module):
             raise RuntimeError(f"IDAUpsample: {deconv} is not the depthwise 2f/f/f//2 deconvolution of IDAUp")
         self.f = s
         self.weight = deconv.weight
-        self._w32 = None
+        self._wt = None
 
     def forward(self, x, skip=None):
         w = self.weight
-        if w.dtype != torch.float32:   # bf16 model: keep one fp32 copy of the (tiny) weights
-            if self._w32 is None or self._w32[0] != (w.data_ptr(), w._version):
-                self._w32 = ((w.data_ptr(), w._version), w.detach().float().contiguous())
-            w = self._w32[1]
-        return idaup_upsample(x, w, self.f, skip)
+        tag = (w.data_ptr(), w._version, w.device)
+        if self._wt is None or self._wt[0] != tag:   # derived (2f*2f, C) fp32 copy of the (tiny) weights
+            self._wt = (tag, w.detach().float().reshape(w.shape[0], -1).t().contiguous())
+        return idaup_upsample(x, self._wt[1], self.f, skip, tap_major=True)

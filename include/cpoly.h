@@ -96,6 +96,11 @@ typedef struct {
   const float* out_scale; /* (Cout) fp32 or NULL */
   int32_t relu;          /* 1: clamp at zero */
   int32_t reserved0;
+  /* Optional bias of the offset-producing convolution (DCN.conv_offset_mask.bias, a2 in SURVEY 8), added to the
+   * raw offsets / mask logits inside the kernel so the producer conv can run bias-free: offset_bias has
+   * dg*2*kh*kw floats, mask_bias dg*kh*kw floats (added BEFORE the sigmoid when mask_is_logit). */
+  const float* offset_bias;
+  const float* mask_bias;
   /* Scratch for the tap-split schedule of small feature maps (cpoly_dcn_forward_workspace_bytes); may be
    * NULL, in which case the unsplit schedule is used. */
   void* workspace;
@@ -145,8 +150,10 @@ typedef struct {
   int32_t B, C, H, W;   /* input (B,C,H,W) */
   int32_t f;            /* up-sampling factor: kernel 2f, stride f, padding f/2 */
   int32_t dtype;        /* element type of x, skip and y */
+  int32_t weight_tap_major; /* 0: weight is the parameter layout (C,1,2f,2f); 1: derived (2f*2f, C) copy (vector loads) */
+  int32_t reserved0;
   cpoly_tensor4 x;
-  const float* weight;  /* (C,1,2f,2f) dense fp32 */
+  const float* weight;  /* dense fp32 */
   cpoly_tensor4 skip;   /* ptr == NULL => no addend */
   cpoly_tensor4 y;
 } cpoly_upsample_args;
