@@ -28,6 +28,7 @@ class PolydetEngine:
         self.heads = dict(heads or HEADS)
         self.shape = (batch, 3, height, width)
         torch.manual_seed(seed)
+        torch.backends.cudnn.benchmark = True     # as the reference does (src/main.py:32): let cuDNN time its algorithms
         net = PolydetDLA34(self.heads).to(self.device).to(memory_format=torch.channels_last)
         if calibrate:
             calibrate_random_init(net, height, width, seed=seed)
@@ -38,7 +39,8 @@ class PolydetEngine:
             from .. import fuse
             # module rewrite; bf16 weights instead of per-call autocast casts
             self.fusion = fuse.optimize_for_inference(net, torch.bfloat16 if dtype == "bf16" else None)
-            self.in_channels = fuse.pad_stem_input_channels(net, 8)   # exact; lets cuDNN use NHWC tensor-core kernels
+            # (fuse.pad_stem_input_channels exists, but on this cuDNN the 8-channel bf16 stem is 2x SLOWER than the
+            #  3-channel one - tools/stem_probe.py: 853 us vs 412 us - so the stem keeps its 3 input channels)
         self.optimize = optimize
         self.net = net
         self.n_dcn_per_frame = sum(1 for m in net.modules() if hasattr(m, "conv_offset_mask"))
