@@ -184,8 +184,13 @@ def dominant_kernel_roofline(torch, dtype, steps, peaks):
     alg_bytes = es * h * w * (Cin + 27 + Cout)          # s*B*H*W*(Cin+27+Cout)
     flops = 2.0 * Cout * Cin * 9 * h * w
     achieved = alg_bytes / ms / 1e6
+    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of this launch in the committed `ncu --set full` capture
+    # (profiles/r01d_dcn_fwd_tc_64x64_raw.txt; bf16 only).  Below the algorithmic bytes because the 16.8 MB output
+    # is still in the write-back L2 when the kernel ends.
+    traffic = 23.98e6 if dtype == "bf16" else None
     return dict(bound="hbm", kernel="dcn_fwd_tc_kernel", layer="64->64 @256x512 (5 of 16 DCN layers/frame)",
-                achieved=achieved, peak=peaks["hbm_gbs"], unit="GB/s", frac=achieved / peaks["hbm_gbs"], traffic=None,
+                achieved=achieved, peak=peaks["hbm_gbs"], unit="GB/s", frac=achieved / peaks["hbm_gbs"], traffic=traffic,
+                note="gather-bound: the sampler pulls 4*9*H*W*Cin*s = 604 MB through the L1 path per launch (DESIGN.md 3.1)",
                 peak_source=peaks["source"], us_per_launch=1000.0 * ms, algorithmic_bytes=alg_bytes,
                 tensor=dict(achieved=flops / ms / 1e9, peak=peaks["bf16_tflops"] * (1.0 if dtype == "bf16" else 0.5),
                             unit="TFLOP/s", frac=flops / ms / 1e9 / (peaks["bf16_tflops"] * (1.0 if dtype == "bf16" else 0.5))))
@@ -253,7 +258,9 @@ def run_ours(args):
             cpu = dict(value=1.0 / (4.0 * t_cpu), unit="frames/s", cores=threads, kind="port",
                        sample="one 1024x512 crop (1/4 of the 2048x1024 frame, cost linear in pixels) through the same DLA-34 "
                               "network with torchvision CPU deform_conv2d + numpy decode oracle; %.2f s" % t_cpu)
-        launches_per_step = eng.n_dcn_per_frame + 1      # 16 dcn_fwd_tc_kernel + 1 decode_kernel (weights pre-packed)
+        # our kernels per frame, counted by the shims on a warm eager frame: 16 dcn_fwd_tc_kernel (+ a combine kernel
+        # on the tap-split layers) + 8 upsample_nhwc_kernel + 3 decode kernels
+        launches_per_step = eng.launches_per_step
         line = dict(metric=METRIC, value=value, unit="frames/s", n_gpus=world, steps=args.steps, warmup=max(3, args.warmup),
                     ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype=("bf16" if args.dtype == "bf16" else "f32"), data="synthetic",

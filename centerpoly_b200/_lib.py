@@ -58,6 +58,8 @@ class DecodeArgs(Structure):
 
 
 _lib = None
+# kernels launched by the shims since import (our kernels only; bench.py reports it as gpu_launches)
+LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "decode": 0}
 
 
 def lib():

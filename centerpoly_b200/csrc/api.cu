@@ -83,16 +83,32 @@ int cpoly_dcn_forward(const cpoly_dcn_fwd_args* args, cpoly_stream_t stream) {
   return dcn_forward_simt(*args, s);
 }
 
+static bool use_tc_wgrad(const cpoly_dcn_bwd_args& a) {
+  return a.gweight && a.f.path != CPOLY_PATH_SIMT && dcn_tc_wgrad_eligible(a);
+}
+
 size_t cpoly_dcn_backward_workspace_bytes(const cpoly_dcn_bwd_args* args) {
   if (!args) return 0;
-  return dcn_backward_simt_workspace(*args);
+  const size_t simt = dcn_backward_simt_workspace(*args);
+  const size_t tc = use_tc_wgrad(*args) ? dcn_tc_wgrad_workspace(*args) : 0;
+  return simt > tc ? simt : tc;
 }
 
 int cpoly_dcn_backward(const cpoly_dcn_bwd_args* args, cpoly_stream_t stream) {
   CPOLY_REQUIRE(args, CPOLY_EINVAL, "NULL args");
   if (int rc = validate_dcn(args->f, false)) return rc;
   CPOLY_REQUIRE(args->gout.ptr && args->f.weight, CPOLY_EINVAL, "NULL grad_output / weight");
-  return dcn_backward_simt(*args, reinterpret_cast<cudaStream_t>(stream));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (use_tc_wgrad(*args)) {
+    // weight gradient on the tensor cores; the remaining gradients on the generic path
+    if (int rc = dcn_wgrad_tc(*args, args->workspace, args->workspace_bytes, s)) return rc;
+    cpoly_dcn_bwd_args rest = *args;
+    rest.gweight = nullptr;
+    return dcn_backward_simt(rest, s);
+  }
+  CPOLY_REQUIRE(args->f.path != CPOLY_PATH_TCGEN05 || !args->gweight, CPOLY_EUNSUPPORTED,
+                "tcgen05 path requested but the backward problem does not qualify");
+  return dcn_backward_simt(*args, s);
 }
 
 size_t cpoly_decode_workspace_bytes(int32_t B, int32_t C, int32_t H, int32_t W, int32_t K) {

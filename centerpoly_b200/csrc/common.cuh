@@ -121,6 +121,9 @@ size_t dcn_tc_packed_bytes(int Cin, int Cout, int kh, int kw, int dtype);
 int dcn_tc_pack_weights(const float* weight, void* packed, int Cin, int Cout, int kh, int kw, int dtype, cudaStream_t stream);
 int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream);
 size_t dcn_tc_forward_workspace(const cpoly_dcn_fwd_args& a);
+bool dcn_tc_wgrad_eligible(const cpoly_dcn_bwd_args& a);
+size_t dcn_tc_wgrad_workspace(const cpoly_dcn_bwd_args& a);
+int dcn_wgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream);
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K);
 int decode_launch(const cpoly_decode_args& a, cudaStream_t stream);

@@ -34,7 +34,7 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity,
       : "memory");
   return ok;
 }
-__device__ __noinline__ void mbar_timeout(uint32_t bar, uint32_t parity) {
+static __device__ __noinline__ void mbar_timeout(uint32_t bar, uint32_t parity) {
   printf("cpoly tcgen05 kernel: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", blockIdx.x,
          threadIdx.x, bar, parity);
   __trap();

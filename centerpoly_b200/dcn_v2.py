@@ -68,6 +68,7 @@ class _PackedWeights:
         packed = torch.empty(nbytes, dtype=torch.uint8, device=weight.device)
         _lib.check(L.cpoly_dcn_pack_weights(w32.data_ptr(), packed.data_ptr(), Cin, Cout, kh, kw, dtype_code,
                                             _lib.stream_ptr(weight.device)), "cpoly_dcn_pack_weights")
+        _lib.LAUNCHES["pack_weights"] += 1
         cache[dtype_code] = (tag, packed)
         return packed
 
@@ -153,6 +154,7 @@ def _forward_impl(x, offset, mask, weight, bias, stride, padding, dilation, dg, 
             w32 = _as_f32_contig(weight)      # the generic SIMT path reads the dense fp32 master weights
             a.weight = w32.data_ptr()
         _lib.check(L.cpoly_dcn_forward(byref(a), _lib.stream_ptr(dev)), "cpoly_dcn_forward")
+        _lib.LAUNCHES["dcn_forward"] += 2 if a.workspace else 1   # tap-split schedules add the combine kernel
     return y, x
 
 

@@ -83,10 +83,13 @@ class PolydetEngine:
             return cdecode.polydet_decode(hm, out["poly"], out["pseudo_depth"], reg=out.get("reg"), K=self.K, rep=self.rep)
 
     def _warm_and_capture(self):
+        from .. import _lib
         with torch.cuda.stream(self.stream):
             for slot in self.slots:
                 for _ in range(2):  # fills the packed-weight cache, cuDNN plans, allocator pools
+                    before = sum(_lib.LAUNCHES.values())
                     slot["dets"].copy_(self._step(slot["x"]))
+                    self.launches_per_step = sum(_lib.LAUNCHES.values()) - before   # our kernels in one warm frame
             self.stream.synchronize()
             if self.use_graph:
                 for slot in self.slots:

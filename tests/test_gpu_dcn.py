@@ -95,7 +95,11 @@ def test_tcgen05_zero_offsets(dtype):
     gate(got["y"], want["y"], 1e-2 if dtype == torch.bfloat16 else 1e-3, "y")
 
 
-@pytest.mark.parametrize("shape", [(1, 64, 64, 12, 20), (2, 128, 64, 9, 11)], ids=lambda s: "x".join(map(str, s)))
+BWD_SHAPES = [(1, 64, 64, 12, 20), (2, 128, 64, 9, 11), (1, 128, 128, 20, 36), (1, 256, 256, 9, 17), (1, 64, 64, 70, 90),
+              (1, 512, 256, 8, 16)]
+
+
+@pytest.mark.parametrize("shape", BWD_SHAPES, ids=lambda s: "x".join(map(str, s)))
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "fp32"])
 def test_backward_vs_oracle(shape, dtype):
     B, Cin, Cout, H, W = shape
