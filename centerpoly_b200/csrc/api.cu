@@ -86,11 +86,16 @@ int cpoly_dcn_forward(const cpoly_dcn_fwd_args* args, cpoly_stream_t stream) {
 static bool use_tc_wgrad(const cpoly_dcn_bwd_args& a) {
   return a.gweight && a.f.path != CPOLY_PATH_SIMT && dcn_tc_wgrad_eligible(a);
 }
+static bool use_tc_dgrad(const cpoly_dcn_bwd_args& a) {
+  return (a.gx.ptr || a.goffset.ptr || a.gmask.ptr) && a.f.path != CPOLY_PATH_SIMT && dcn_tc_dgrad_eligible(a);
+}
+static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 
 size_t cpoly_dcn_backward_workspace_bytes(const cpoly_dcn_bwd_args* args) {
   if (!args) return 0;
   const size_t simt = dcn_backward_simt_workspace(*args);
-  const size_t tc = use_tc_wgrad(*args) ? dcn_tc_wgrad_workspace(*args) : 0;
+  const size_t tc = (use_tc_wgrad(*args) ? align256(dcn_tc_wgrad_workspace(*args)) : 0) +
+                    (use_tc_dgrad(*args) ? align256(dcn_tc_dgrad_workspace(*args)) : 0);
   return simt > tc ? simt : tc;
 }
 
@@ -99,16 +104,28 @@ int cpoly_dcn_backward(const cpoly_dcn_bwd_args* args, cpoly_stream_t stream) {
   if (int rc = validate_dcn(args->f, false)) return rc;
   CPOLY_REQUIRE(args->gout.ptr && args->f.weight, CPOLY_EINVAL, "NULL grad_output / weight");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  if (use_tc_wgrad(*args)) {
-    // weight gradient on the tensor cores; the remaining gradients on the generic path
-    if (int rc = dcn_wgrad_tc(*args, args->workspace, args->workspace_bytes, s)) return rc;
-    cpoly_dcn_bwd_args rest = *args;
+  const bool tcw = use_tc_wgrad(*args), tcd = use_tc_dgrad(*args);
+  CPOLY_REQUIRE(args->f.path != CPOLY_PATH_TCGEN05 || ((tcw || !args->gweight) && (tcd || !(args->gx.ptr || args->goffset.ptr || args->gmask.ptr))),
+                CPOLY_EUNSUPPORTED, "tcgen05 path requested but the backward problem does not qualify");
+  cpoly_dcn_bwd_args rest = *args;   // what remains for the generic path
+  char* ws = reinterpret_cast<char*>(args->workspace);
+  size_t left = args->workspace_bytes;
+  if (tcw) {   // weight gradient on the tensor cores
+    const size_t need = align256(dcn_tc_wgrad_workspace(*args));
+    CPOLY_REQUIRE(ws && left >= need, CPOLY_EWORKSPACE, "dcn backward workspace too small");
+    if (int rc = dcn_wgrad_tc(*args, ws, need, s)) return rc;
+    ws += need; left -= need;
     rest.gweight = nullptr;
-    return dcn_backward_simt(rest, s);
   }
-  CPOLY_REQUIRE(args->f.path != CPOLY_PATH_TCGEN05 || !args->gweight, CPOLY_EUNSUPPORTED,
-                "tcgen05 path requested but the backward problem does not qualify");
-  return dcn_backward_simt(*args, s);
+  if (tcd) {   // data / coordinate gradients on the tensor cores
+    const size_t need = align256(dcn_tc_dgrad_workspace(*args));
+    CPOLY_REQUIRE(ws && left >= need, CPOLY_EWORKSPACE, "dcn backward workspace too small");
+    if (int rc = dcn_dgrad_tc(*args, ws, need, s)) return rc;
+    rest.gx.ptr = nullptr; rest.goffset.ptr = nullptr; rest.gmask.ptr = nullptr;
+  }
+  if (!tcw && !tcd) return dcn_backward_simt(*args, s);
+  if (rest.gweight || rest.gbias || rest.gx.ptr || rest.goffset.ptr || rest.gmask.ptr) return dcn_backward_simt(rest, s);
+  return CPOLY_OK;
 }
 
 size_t cpoly_decode_workspace_bytes(int32_t B, int32_t C, int32_t H, int32_t W, int32_t K) {

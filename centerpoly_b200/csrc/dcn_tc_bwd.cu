@@ -328,4 +328,459 @@ int dcn_wgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_
   return check_launch("wgrad_reduce_kernel");
 }
 
+
+// =====================================================================================================================
+// Part 2: data / coordinate gradients.
+//
+//   gcol[px,(tap,c)] = sum_o gout[px,o] * W[o,c,tap]                       (tcgen05: M = 128 pixels, N = channel chunk, K = Cout)
+//   grad_mask[px,tap]      = sum_c gcol * v_c(p)                           v = bilinear sample (unmasked)
+//   grad_offset[px,2tap..] = m * sum_c gcol * dv_c/dp                      floor-based corner differences
+//   grad_input[corner,c]  += gcol * m * w_corner                           vector reductions (red.global.add.v4.f32)
+//
+// Persistent warp-specialised CTA; a work item is (128-pixel tile, tap group) as in the forward kernel.
+//   warps 0-3  TMEM -> shared: the gcol tile of one block, converted to T, in the sampler's row layout
+//   warp  4    bulk-copies the block's pre-packed dgrad weights (K-major, rows = input channels) into a 2-stage ring
+//   warp  5    issues the MMAs (A = the item's gout tile, loaded once per item by the samplers)
+//   warps 6-21 gather the 4 corners of every (pixel, tap) exactly like the forward sampler, combine them with gcol,
+//              reduce the coordinate gradients over the 8 lanes of a pixel row (written once, no atomics) and scatter
+//              grad_input.
+namespace {
+
+constexpr int D_BUFS = 2;          // TMEM accumulators and shared gcol tiles
+constexpr int W_STAGES = 2;
+constexpr int DG_PARAM_BYTES = NUM_TAPS * TILE_PX * 16;
+constexpr int DG_POFF_OFF = 1024;
+constexpr int DG_PW_OFF = DG_POFF_OFF + DG_PARAM_BYTES;
+constexpr int DG_PM_OFF = DG_PW_OFF + DG_PARAM_BYTES;
+constexpr int DG_BUF_OFF = ((DG_PM_OFF + DG_PARAM_BYTES + 1023) / 1024) * 1024;
+
+struct DgradParams {
+  Geom g;
+  const void* gout;        // dense NHWC (B,H,W,Cout), element type T
+  const void* wpacked;     // dgrad weight image, see pack_dgrad_weights_kernel
+  float* gx;               // dense NHWC fp32 (B,H,W,Cin), pre-zeroed; or NULL
+  cpoly_tensor4 goffset, gmask;   // fp32, any strides; ptr may be NULL
+  int nchunk;              // channel chunks per tap
+  int split, taps_per_item, num_items;
+  int k_atoms;             // 128-byte atoms along K = Cout
+  int a_bufs;
+  int w_stage_bytes;
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// Four channels of one (pixel, tap): v[q][e] corner values (invalid corners already zeroed), g[e] = gcol.
+struct TapCtx {
+  float w[4];      // bilinear weights (unmasked)
+  float m, ly, lx;
+  uint32_t flags;  // bit q: corner q valid
+};
+__device__ __forceinline__ void quad_accumulate(const float (&v)[4][4], const float (&g)[4], const TapCtx& t, float& sm, float& sy,
+                                                float& sx, float (&out)[4][4]) {
+  const float hy = 1.0f - t.ly, hx = 1.0f - t.lx;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float val = fmaf(t.w[3], v[3][e], fmaf(t.w[2], v[2][e], fmaf(t.w[1], v[1][e], t.w[0] * v[0][e])));
+    const float ty = fmaf(t.lx, v[3][e] - v[1][e], hx * (v[2][e] - v[0][e]));
+    const float tx = fmaf(t.ly, v[3][e] - v[2][e], hy * (v[1][e] - v[0][e]));
+    sm = fmaf(g[e], val, sm);
+    sy = fmaf(g[e], ty, sy);
+    sx = fmaf(g[e], tx, sx);
+    const float gm = g[e] * t.m;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) out[q][e] = gm * t.w[q];
+  }
+}
+
+template <typename T>
+__global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
+  constexpr bool kTF32 = sizeof(T) == 4;
+  constexpr int kChunk = ROW_BYTES / sizeof(T);   // channels per block (= UMMA N): 64 bf16 / 32 tf32
+  constexpr int kVec = 16 / sizeof(T);            // channels per 16-byte piece
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t bar_fullG = smem_base, bar_emptyG = bar_fullG + 16, bar_Wfull = bar_emptyG + 16, bar_Wempty = bar_Wfull + 16;
+  const uint32_t bar_Dfull = bar_Wempty + 16, bar_Dempty = bar_Dfull + 16, bar_gfull = bar_Dempty + 16, bar_gempty = bar_gfull + 16;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + 8 * 16);
+  const uint32_t poff_s = smem_base + DG_POFF_OFF, pw_s = smem_base + DG_PW_OFF, pm_s = smem_base + DG_PM_OFF;
+  const uint32_t a_bytes = (uint32_t)p.k_atoms * ATOM_BYTES;
+  const uint32_t abuf0 = smem_base + DG_BUF_OFF;
+  const uint32_t wst0 = abuf0 + (uint32_t)p.a_bufs * a_bytes;
+  const uint32_t gcol0 = wst0 + (uint32_t)W_STAGES * (uint32_t)p.w_stage_bytes;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int blocks_per_item = p.taps_per_item * p.nchunk;
+
+  if (warp == 4 && lane == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_fullG + 8 * i, SAMPLER_WARPS); mbar_init(bar_emptyG + 8 * i, 1);
+      mbar_init(bar_Wfull + 8 * i, 1);             mbar_init(bar_Wempty + 8 * i, 1);
+      mbar_init(bar_Dfull + 8 * i, 1);             mbar_init(bar_Dempty + 8 * i, EPI_WARPS * 32);
+      mbar_init(bar_gfull + 8 * i, EPI_WARPS);     mbar_init(bar_gempty + 8 * i, SAMPLER_WARPS);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 5) tmem_alloc(smem_u32(tmem_ptr_smem), (uint32_t)(kChunk * D_BUFS < 32 ? 32 : kChunk * D_BUFS));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp >= SAMPLER_WARP0) {
+    // =========================================================================== samplers
+    const int st = threadIdx.x - SAMPLER_WARP0 * 32;
+    const int row_in_pass = st >> 3, cg = st & 7;
+    const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.g.x);
+    const uint8_t* gb = reinterpret_cast<const uint8_t*>(p.gout);
+    const int row_pieces = p.g.Cout * (int)sizeof(T) / 16;
+    float* gmp = reinterpret_cast<float*>(p.gmask.ptr);
+    float* gop = reinterpret_cast<float*>(p.goffset.ptr);
+    RingCursor ra;
+    uint32_t nblk = 0;   // blocks processed by this CTA so far (D / gcol buffer cursor)
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      const int tile = item / p.split, tap0 = (item - tile * p.split) * p.taps_per_item;
+      int b, ty0, tx0;
+      tile_coords(p.g, tile, b, ty0, tx0);
+      named_bar_sync(1, NS);
+      for (int e = st; e < p.taps_per_item * TILE_PX; e += NS) {
+        const int kl = e >> 7, r = e & (TILE_PX - 1);
+        const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
+        const TapGeom t = make_tap_geom<T>(p.g, b, y, x, tap0 + kl);
+        const uint32_t flags = (uint32_t)(t.valid[0] | (t.valid[1] << 1) | (t.valid[2] << 2) | (t.valid[3] << 3)) |
+                               ((y < p.g.H && x < p.g.W) ? 16u : 0u);
+        sts16(poff_s + (uint32_t)e * 16u, make_uint4(t.off[0], t.off[1], t.off[2], t.off[3]));
+        sts16(pw_s + (uint32_t)e * 16u, make_uint4(__float_as_uint(t.w[0]), __float_as_uint(t.w[1]), __float_as_uint(t.w[2]), __float_as_uint(t.w[3])));
+        sts16(pm_s + (uint32_t)e * 16u, make_uint4(__float_as_uint(t.m), __float_as_uint(t.ly), __float_as_uint(t.lx), flags));
+      }
+      // gout tile -> A buffer (K-major: row = pixel, 128-byte atoms along Cout)
+      mbar_wait(bar_emptyG + 8 * ra.s, ra.ph ^ 1u);
+      const uint32_t abuf = abuf0 + ra.s * a_bytes;
+      for (int pc = st; pc < TILE_PX * row_pieces; pc += NS) {
+        const int r = pc / row_pieces, j = pc - r * row_pieces;
+        const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (y < p.g.H && x < p.g.W) v = ldg16(gb + ((size_t)((b * p.g.H + y) * p.g.W + x) * row_pieces + j) * 16);
+        sts16(abuf + (uint32_t)(j >> 3) * ATOM_BYTES + (uint32_t)r * ROW_BYTES + (uint32_t)(((j & 7) ^ (r & 7)) << 4), v);
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_fullG + 8 * ra.s);
+      ra.advance((uint32_t)p.a_bufs);
+      named_bar_sync(1, NS);
+
+      uint4 c[PASSES][4];
+      auto issue = [&](int q, int pass) {   // corner loads of block q (tap-major, chunk-minor) of this item
+        const int kl = q / p.nchunk, cc = q - kl * p.nchunk;
+        const uint32_t idx = (uint32_t)(kl * TILE_PX + pass * ROWS_PER_PASS + row_in_pass) * 16u;
+        const uint4 po = lds16(poff_s + idx);
+        const uint32_t cbyte = (uint32_t)(cc * ROW_BYTES + cg * 16);
+        c[pass][0] = ldg16(xb + (po.x + cbyte));
+        c[pass][1] = ldg16(xb + (po.y + cbyte));
+        c[pass][2] = ldg16(xb + (po.z + cbyte));
+        c[pass][3] = ldg16(xb + (po.w + cbyte));
+      };
+#pragma unroll
+      for (int pass = 0; pass < PASSES; ++pass) issue(0, pass);
+      float sm[PASSES], sy[PASSES], sx[PASSES];
+      for (int q = 0; q < blocks_per_item; ++q, ++nblk) {
+        const int kl = q / p.nchunk, cc = q - kl * p.nchunk;
+        const uint32_t d = nblk & 1u, dph = (nblk >> 1) & 1u;
+        if (cc == 0) {
+#pragma unroll
+          for (int pass = 0; pass < PASSES; ++pass) sm[pass] = sy[pass] = sx[pass] = 0.f;
+        }
+        mbar_wait(bar_gfull + 8 * d, dph);
+        const uint32_t gt = gcol0 + d * ATOM_BYTES;
+#pragma unroll
+        for (int pass = 0; pass < PASSES; ++pass) {
+          const int r = pass * ROWS_PER_PASS + row_in_pass;
+          const uint32_t idx = (uint32_t)(kl * TILE_PX + r) * 16u;
+          const uint4 pm = lds16(pm_s + idx);
+          const uint32_t flags = pm.w;
+          if (flags & 15u) {
+            const uint4 po = lds16(poff_s + idx), pwv = lds16(pw_s + idx);
+            const uint4 gq = lds16(gt + (uint32_t)r * ROW_BYTES + (uint32_t)((cg ^ (r & 7)) << 4));
+            TapCtx t;
+            t.w[0] = __uint_as_float(pwv.x); t.w[1] = __uint_as_float(pwv.y); t.w[2] = __uint_as_float(pwv.z); t.w[3] = __uint_as_float(pwv.w);
+            t.m = __uint_as_float(pm.x); t.ly = __uint_as_float(pm.y); t.lx = __uint_as_float(pm.z); t.flags = flags;
+            const uint32_t offs[4] = {po.x, po.y, po.z, po.w};
+            const uint32_t* cw[4] = {&c[pass][0].x, &c[pass][1].x, &c[pass][2].x, &c[pass][3].x};
+            const uint32_t* gw = &gq.x;
+            constexpr int kQuads = kVec / 4;   // 2 (bf16) or 1 (fp32)
+#pragma unroll
+            for (int h = 0; h < kQuads; ++h) {
+              float v[4][4], g[4], out[4][4];
+#pragma unroll
+              for (int qq = 0; qq < 4; ++qq) {
+                const bool ok = (flags >> qq) & 1u;
+                if (kTF32) {
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) v[qq][e] = ok ? __uint_as_float(cw[qq][e]) : 0.f;
+                } else {
+                  const uint32_t w0 = ok ? cw[qq][2 * h] : 0u, w1 = ok ? cw[qq][2 * h + 1] : 0u;
+                  v[qq][0] = __uint_as_float(w0 << 16); v[qq][1] = __uint_as_float(w0 & 0xffff0000u);
+                  v[qq][2] = __uint_as_float(w1 << 16); v[qq][3] = __uint_as_float(w1 & 0xffff0000u);
+                }
+              }
+              if (kTF32) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) g[e] = __uint_as_float(gw[e]);
+              } else {
+                g[0] = __uint_as_float(gw[2 * h] << 16); g[1] = __uint_as_float(gw[2 * h] & 0xffff0000u);
+                g[2] = __uint_as_float(gw[2 * h + 1] << 16); g[3] = __uint_as_float(gw[2 * h + 1] & 0xffff0000u);
+              }
+              quad_accumulate(v, g, t, sm[pass], sy[pass], sx[pass], out);
+              if (p.gx) {
+#pragma unroll
+                for (int qq = 0; qq < 4; ++qq)
+                  if ((flags >> qq) & 1u)
+                    red_add_v4(p.gx + (offs[qq] / (uint32_t)sizeof(T)) + (uint32_t)(cc * kChunk + cg * kVec + h * 4), out[qq][0],
+                               out[qq][1], out[qq][2], out[qq][3]);
+              }
+            }
+          }
+          if (q + 1 < blocks_per_item) issue(q + 1, pass);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_gempty + 8 * d);
+        if (cc == p.nchunk - 1) {   // tap complete: reduce over the 8 lanes of each pixel row and write once
+#pragma unroll
+          for (int pass = 0; pass < PASSES; ++pass) {
+#pragma unroll
+            for (int sft = 1; sft <= 4; sft <<= 1) {
+              sm[pass] += __shfl_xor_sync(0xffffffffu, sm[pass], sft);
+              sy[pass] += __shfl_xor_sync(0xffffffffu, sy[pass], sft);
+              sx[pass] += __shfl_xor_sync(0xffffffffu, sx[pass], sft);
+            }
+            if (cg == 0) {
+              const int r = pass * ROWS_PER_PASS + row_in_pass;
+              const uint4 pm = lds16(pm_s + (uint32_t)(kl * TILE_PX + r) * 16u);
+              if (pm.w & 16u) {
+                const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1)), k = tap0 + kl;
+                const float m = __uint_as_float(pm.x);
+                if (gmp) {
+                  float gm = sm[pass];
+                  if (p.g.mask_is_logit) gm *= m * (1.f - m);
+                  gmp[(int64_t)b * p.gmask.sb + (int64_t)k * p.gmask.sc + (int64_t)y * p.gmask.sh + (int64_t)x * p.gmask.sw] = gm;
+                }
+                if (gop) {
+                  const int64_t ob = (int64_t)b * p.goffset.sb + (int64_t)y * p.goffset.sh + (int64_t)x * p.goffset.sw;
+                  gop[ob + (int64_t)(2 * k) * p.goffset.sc] = m * sy[pass];
+                  gop[ob + (int64_t)(2 * k + 1) * p.goffset.sc] = m * sx[pass];
+                }
+              }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 4) {
+    // =========================================================================== dgrad weight loader
+    if (lane == 0) {
+      const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.wpacked);
+      uint32_t nblk = 0;
+      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+        const int tap0 = (item % p.split) * p.taps_per_item;
+        for (int q = 0; q < blocks_per_item; ++q, ++nblk) {
+          const uint32_t ws = nblk & 1u, wph = (nblk >> 1) & 1u;
+          mbar_wait(bar_Wempty + 8 * ws, wph ^ 1u, 200);
+          mbar_arrive_expect_tx(bar_Wfull + 8 * ws, (uint32_t)p.w_stage_bytes);
+          bulk_copy_g2s(wst0 + ws * (uint32_t)p.w_stage_bytes, wsrc + (size_t)(tap0 * p.nchunk + q) * p.w_stage_bytes,
+                        (uint32_t)p.w_stage_bytes, bar_Wfull + 8 * ws);
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // =========================================================================== MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc(kTF32, TILE_PX, kChunk);
+      RingCursor ra;
+      uint32_t nblk = 0;
+      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+        mbar_wait(bar_fullG + 8 * ra.s, ra.ph, 100);
+        const uint32_t abuf = abuf0 + ra.s * a_bytes;
+        for (int q = 0; q < blocks_per_item; ++q, ++nblk) {
+          const uint32_t d = nblk & 1u, dph = (nblk >> 1) & 1u;
+          mbar_wait(bar_Wfull + 8 * d, dph, 50);
+          mbar_wait(bar_Dempty + 8 * d, dph ^ 1u, 50);
+          tc_fence_after();
+          const uint32_t wst = wst0 + d * (uint32_t)p.w_stage_bytes;
+          const uint32_t d_tmem = tmem_base + d * (uint32_t)kChunk;
+          for (int ka = 0; ka < p.k_atoms; ++ka) {
+            const uint64_t adesc = umma_desc_sw128(abuf + (uint32_t)ka * ATOM_BYTES);
+            const uint64_t bdesc = umma_desc_sw128(wst + (uint32_t)ka * (uint32_t)(kChunk * ROW_BYTES));
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              umma<kTF32>(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (ka | kk) != 0 ? 1u : 0u);
+          }
+          umma_commit(bar_Wempty + 8 * d);
+          umma_commit(bar_Dfull + 8 * d);
+        }
+        umma_commit(bar_emptyG + 8 * ra.s);
+        ra.advance((uint32_t)p.a_bufs);
+      }
+    }
+  } else {
+    // =========================================================================== TMEM -> shared gcol tile
+    const int r = warp * 32 + lane;
+    uint32_t nblk = 0;
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      for (int q = 0; q < blocks_per_item; ++q, ++nblk) {
+        const uint32_t d = nblk & 1u, dph = (nblk >> 1) & 1u;
+        mbar_wait(bar_Dfull + 8 * d, dph, 50);
+        mbar_wait(bar_gempty + 8 * d, dph ^ 1u, 50);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + d * (uint32_t)kChunk;
+        const uint32_t grow = gcol0 + d * ATOM_BYTES + (uint32_t)r * ROW_BYTES;
+#pragma unroll
+        for (int c0 = 0; c0 < kChunk; c0 += 16) {
+          uint32_t raw[16];
+          tmem_ld16(t_row + (uint32_t)c0, raw);
+          tmem_ld_wait();
+          if (kTF32) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              sts16(grow + (uint32_t)((((c0 >> 2) + j) ^ (r & 7)) << 4), make_uint4(raw[4 * j], raw[4 * j + 1], raw[4 * j + 2], raw[4 * j + 3]));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              uint4 v;
+              v.x = pack_bf16x2(__uint_as_float(raw[8 * j]), __uint_as_float(raw[8 * j + 1]));
+              v.y = pack_bf16x2(__uint_as_float(raw[8 * j + 2]), __uint_as_float(raw[8 * j + 3]));
+              v.z = pack_bf16x2(__uint_as_float(raw[8 * j + 4]), __uint_as_float(raw[8 * j + 5]));
+              v.w = pack_bf16x2(__uint_as_float(raw[8 * j + 6]), __uint_as_float(raw[8 * j + 7]));
+              sts16(grow + (uint32_t)((((c0 >> 3) + j) ^ (r & 7)) << 4), v);
+            }
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(bar_Dempty + 8 * d);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_gfull + 8 * d);
+      }
+    }
+  }
+
+  __syncwarp();
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)(kChunk * D_BUFS < 32 ? 32 : kChunk * D_BUFS));
+  }
+}
+
+// weight (Cout,Cin,3,3) fp32 -> dgrad image: per (tap, channel chunk) a blob of k_atoms x [kChunk rows (input channel)
+// x 128 B of K = output channels], 16-byte pieces XOR-swizzled by (row & 7): the K-major SWIZZLE_128B B operand.
+template <typename T>
+__global__ void pack_dgrad_weights_kernel(const float* __restrict__ w, uint4* __restrict__ out, int Cin, int Cout) {
+  constexpr int kVec = 16 / sizeof(T);
+  constexpr int kChunk = ROW_BYTES / sizeof(T);
+  const int nchunk = Cin / kChunk, k_atoms = Cout / kChunk;
+  const int64_t total = (int64_t)NUM_TAPS * nchunk * k_atoms * kChunk * 8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int j = (int)(i & 7);
+    int64_t t = i >> 3;
+    const int row = (int)(t % kChunk); t /= kChunk;
+    const int ka = (int)(t % k_atoms); t /= k_atoms;
+    const int cc = (int)(t % nchunk);
+    const int tap = (int)(t / nchunk);
+    const int c = cc * kChunk + row;
+    uint32_t words[4];
+    if (sizeof(T) == 4) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int o = ka * kChunk + j * kVec + e;
+        words[e] = to_tf32(w[((int64_t)o * Cin + c) * NUM_TAPS + tap]);
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int o = ka * kChunk + j * kVec + 2 * e;
+        words[e] = pack_bf16x2(w[((int64_t)o * Cin + c) * NUM_TAPS + tap], w[((int64_t)(o + 1) * Cin + c) * NUM_TAPS + tap]);
+      }
+    }
+    const int64_t blob = (int64_t)tap * nchunk + cc;
+    out[((blob * k_atoms + ka) * kChunk + row) * 8 + (j ^ (row & 7))] = make_uint4(words[0], words[1], words[2], words[3]);
+  }
+}
+
+struct DgradPlan {
+  int nchunk, k_atoms, a_bufs, w_stage_bytes, split, smem_bytes;
+  size_t packed_bytes;
+  bool ok;
+};
+
+DgradPlan plan_dgrad(const cpoly_dcn_fwd_args& a) {
+  DgradPlan d{};
+  const int esize = a.dtype == CPOLY_BF16 ? 2 : 4;
+  const int kchunk = ROW_BYTES / esize;
+  d.nchunk = a.Cin / kchunk;
+  d.k_atoms = a.Cout / kchunk;
+  d.w_stage_bytes = d.k_atoms * kchunk * ROW_BYTES;
+  const int a_bytes = d.k_atoms * ATOM_BYTES;
+  const int fixed = DG_BUF_OFF + W_STAGES * d.w_stage_bytes + D_BUFS * ATOM_BYTES;
+  d.a_bufs = (SMEM_LIMIT - fixed) / a_bytes >= 2 ? 2 : 1;
+  d.smem_bytes = fixed + d.a_bufs * a_bytes + 1024;
+  d.packed_bytes = (size_t)NUM_TAPS * a.Cin * a.Cout * esize;
+  const int tiles = a.B * ((a.W + TILE_W - 1) / TILE_W) * ((a.H + TILE_H - 1) / TILE_H);
+  d.split = tiles >= 148 ? 1 : (tiles * 3 >= 148 ? 3 : 9);
+  d.ok = a.Cout % kchunk == 0 && a.Cin % kchunk == 0 && fixed + a_bytes <= SMEM_LIMIT;
+  return d;
+}
+
+}  // namespace
+
+bool dcn_tc_dgrad_eligible(const cpoly_dcn_bwd_args& a) {
+  cpoly_dcn_fwd_args f = a.f;
+  f.y = a.gout;
+  f.weight_packed = nullptr;
+  if (!dcn_tc_eligible(f)) return false;
+  if (!dense_nhwc4(a.gout, a.f.Cout, a.f.H, a.f.W)) return false;
+  if (a.gx.ptr && (!dense_nhwc4(a.gx, a.f.Cin, a.f.H, a.f.W) || (reinterpret_cast<uintptr_t>(a.gx.ptr) & 15))) return false;
+  return plan_dgrad(a.f).ok;
+}
+
+size_t dcn_tc_dgrad_workspace(const cpoly_dcn_bwd_args& a) { return plan_dgrad(a.f).packed_bytes + 256; }
+
+int dcn_dgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+  const cpoly_dcn_fwd_args& f = a.f;
+  const DgradPlan d = plan_dgrad(f);
+  CPOLY_REQUIRE(d.ok, CPOLY_EUNSUPPORTED, "dgrad plan does not fit");
+  CPOLY_REQUIRE(workspace && workspace_bytes >= d.packed_bytes && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0, CPOLY_EWORKSPACE,
+                "dcn dgrad workspace too small or misaligned: need %zu bytes, have %zu", d.packed_bytes, workspace_bytes);
+  const bool bf = f.dtype == CPOLY_BF16;
+  const int64_t pieces = (int64_t)d.packed_bytes / 16;
+  const unsigned pblocks = (unsigned)((pieces + 255) / 256);
+  if (bf) pack_dgrad_weights_kernel<__nv_bfloat16><<<pblocks, 256, 0, stream>>>(f.weight, reinterpret_cast<uint4*>(workspace), f.Cin, f.Cout);
+  else pack_dgrad_weights_kernel<float><<<pblocks, 256, 0, stream>>>(f.weight, reinterpret_cast<uint4*>(workspace), f.Cin, f.Cout);
+  if (int rc = check_launch("pack_dgrad_weights_kernel")) return rc;
+  if (a.gx.ptr) CPOLY_CUDA_OK(cudaMemsetAsync(a.gx.ptr, 0, (size_t)f.B * f.H * f.W * f.Cin * sizeof(float), stream));
+  DgradParams p;
+  p.g.x = f.x.ptr; p.g.offset = f.offset; p.g.mask = f.mask; p.g.offset_bias = f.offset_bias; p.g.mask_bias = f.mask_bias;
+  p.g.B = f.B; p.g.Cin = f.Cin; p.g.Cout = f.Cout; p.g.H = f.H; p.g.W = f.W;
+  p.g.om_dtype = f.om_dtype; p.g.mask_is_logit = f.mask_is_logit;
+  p.g.tiles_x = (f.W + TILE_W - 1) / TILE_W; p.g.tiles_y = (f.H + TILE_H - 1) / TILE_H;
+  p.g.num_tiles = f.B * p.g.tiles_x * p.g.tiles_y;
+  p.gout = a.gout.ptr; p.wpacked = workspace; p.gx = reinterpret_cast<float*>(a.gx.ptr);
+  p.goffset = a.goffset; p.gmask = a.gmask;
+  p.nchunk = d.nchunk; p.split = d.split; p.taps_per_item = NUM_TAPS / d.split; p.num_items = p.g.num_tiles * d.split;
+  p.k_atoms = d.k_atoms; p.a_bufs = d.a_bufs; p.w_stage_bytes = d.w_stage_bytes;
+  if (p.num_items == 0) return CPOLY_OK;
+  int dev = 0, sms = 0;
+  CPOLY_CUDA_OK(cudaGetDevice(&dev));
+  CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = p.num_items < sms ? p.num_items : sms;
+  if (bf) {
+    CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_dgrad_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, d.smem_bytes));
+    dcn_dgrad_tc_kernel<__nv_bfloat16><<<grid, NTHREADS, d.smem_bytes, stream>>>(p);
+  } else {
+    CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_dgrad_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, d.smem_bytes));
+    dcn_dgrad_tc_kernel<float><<<grid, NTHREADS, d.smem_bytes, stream>>>(p);
+  }
+  return check_launch("dcn_dgrad_tc_kernel");
+}
+
 }  // namespace cpoly
