@@ -1,0 +1,24 @@
+"""GPU: the data-parallel trainer drives the full network (16 DCN forwards + backwards through the C ABI) and learns."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("dtype", [None, torch.bfloat16], ids=["fp32", "bf16"])
+def test_training_steps_reduce_the_loss(dtype):
+    from centerpoly_b200.harness.dla34 import PolydetDLA34, calibrate_random_init
+    from centerpoly_b200.harness.train import DataParallelTrainer, synthetic_batch
+    torch.manual_seed(317)
+    net = PolydetDLA34().cuda().to(memory_format=torch.channels_last)
+    calibrate_random_init(net, 64, 128)
+    trainer = DataParallelTrainer(net, lr=5e-4, dtype=dtype)
+    batch = synthetic_batch(2, 128, 256, n_obj=6, device="cuda", seed=3)
+    batch["input"] = batch["input"].contiguous(memory_format=torch.channels_last)
+    losses = [float(trainer.step(batch)) for _ in range(12)]
+    assert all(l == l and abs(l) < 1e6 for l in losses), losses
+    assert min(losses[-3:]) < losses[0], losses
+    # every DCN parameter received a gradient through the tensor-core backward
+    for n, p in net.named_parameters():
+        if ".conv.weight" in n or "conv_offset_mask" in n:
+            assert p.grad is not None and torch.isfinite(p.grad).all(), n
