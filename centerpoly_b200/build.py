@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcpoly.so")
-SOURCES = ["api.cu", "dcn_simt.cu", "dcn_tc.cu", "dcn_tc_bwd.cu", "neck.cu", "decode.cu"]
+SOURCES = ["api.cu", "dcn_simt.cu", "dcn_tc.cu", "dcn_tc_win.cu", "dcn_tc_bwd.cu", "neck.cu", "decode.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xptxas=-v",
@@ -36,7 +36,7 @@ def is_stale() -> bool:
         return True
     t = os.path.getmtime(LIB)
     deps = sources() + [os.path.join(CSRC, "common.cuh"), os.path.join(HERE, "..", "include", "cpoly.h"),
-                        os.path.join(CSRC, "tc_common.cuh")]
+                        os.path.join(CSRC, "tc_common.cuh"), os.path.join(CSRC, "dcn_sampler.cuh")]
     return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
 
 

@@ -1,6 +1,8 @@
 // extern "C" surface of libcpoly.so — see include/cpoly.h for the contract and the reference
 // interfaces each entry point replaces.
 #include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 
@@ -28,6 +30,18 @@ static int validate_dcn(const cpoly_dcn_fwd_args& a, bool need_y) {
   const DcnGeom g = make_geom(a);
   CPOLY_REQUIRE(g.Ho > 0 && g.Wo > 0, CPOLY_EINVAL, "empty output (%d x %d)", g.Ho, g.Wo);
   return CPOLY_OK;
+}
+
+// Forward sampler of the tcgen05 path: "gather" (dcn_tc.cu, corners gathered from global memory through L1; default)
+// or "window" (dcn_tc_win.cu, TMA-staged shared-memory window), selected with CPOLY_TC_SAMPLER=window.  The two are
+// within +-5 % of each other per layer (both saturate the same LSU/shared-memory data pipe).
+static bool want_window_sampler() {
+  const char* e = getenv("CPOLY_TC_SAMPLER");
+  return e && strcmp(e, "window") == 0;
+}
+static int dcn_forward_tc_any(const cpoly_dcn_fwd_args& a, cudaStream_t s) {
+  if (want_window_sampler() && dcn_tc_win_eligible(a)) return dcn_forward_tc_win(a, s);
+  return dcn_forward_tc(a, s);
 }
 
 }  // namespace cpoly
@@ -66,7 +80,8 @@ int cpoly_dcn_pack_weights(const float* weight, void* packed, int32_t Cin, int32
 
 size_t cpoly_dcn_forward_workspace_bytes(const cpoly_dcn_fwd_args* args) {
   if (!args || !dcn_tc_eligible(*args)) return 256;
-  return dcn_tc_forward_workspace(*args);
+  const size_t g = dcn_tc_forward_workspace(*args), w = dcn_tc_win_eligible(*args) ? dcn_tc_win_forward_workspace(*args) : 0;
+  return g > w ? g : w;
 }
 
 int cpoly_dcn_forward(const cpoly_dcn_fwd_args* args, cpoly_stream_t stream) {
@@ -76,9 +91,9 @@ int cpoly_dcn_forward(const cpoly_dcn_fwd_args* args, cpoly_stream_t stream) {
   const bool tc_ok = args->weight_packed && dcn_tc_eligible(*args);
   if (args->path == CPOLY_PATH_TCGEN05) {
     CPOLY_REQUIRE(tc_ok, CPOLY_EUNSUPPORTED, "tcgen05 path requested but the problem does not qualify (see cpoly_dcn_tcgen05_eligible)");
-    return dcn_forward_tc(*args, s);
+    return dcn_forward_tc_any(*args, s);
   }
-  if (args->path == CPOLY_PATH_AUTO && tc_ok) return dcn_forward_tc(*args, s);
+  if (args->path == CPOLY_PATH_AUTO && tc_ok) return dcn_forward_tc_any(*args, s);
   CPOLY_REQUIRE(args->weight, CPOLY_EINVAL, "the generic path needs the dense fp32 weights");
   return dcn_forward_simt(*args, s);
 }

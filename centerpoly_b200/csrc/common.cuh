@@ -121,6 +121,9 @@ size_t dcn_tc_packed_bytes(int Cin, int Cout, int kh, int kw, int dtype);
 int dcn_tc_pack_weights(const float* weight, void* packed, int Cin, int Cout, int kh, int kw, int dtype, cudaStream_t stream);
 int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream);
 size_t dcn_tc_forward_workspace(const cpoly_dcn_fwd_args& a);
+bool dcn_tc_win_eligible(const cpoly_dcn_fwd_args& a);
+size_t dcn_tc_win_forward_workspace(const cpoly_dcn_fwd_args& a);
+int dcn_forward_tc_win(const cpoly_dcn_fwd_args& a, cudaStream_t stream);
 bool dcn_tc_wgrad_eligible(const cpoly_dcn_bwd_args& a);
 size_t dcn_tc_wgrad_workspace(const cpoly_dcn_bwd_args& a);
 int dcn_wgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_bytes, cudaStream_t stream);

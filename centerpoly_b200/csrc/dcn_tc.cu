@@ -285,45 +285,48 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
     }
   } else if (warp == 4) {
     // =========================================================================== weight loader
-    if (lane == 0) {
-      RingCursor rc;
-      const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.wpacked);
-      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
-        const int q0 = (item % p.split) * chunks_per_item;
-        for (int q = 0; q < chunks_per_item; ++q) {
-          mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u, 500);
+    // (whole warp walks the ring, one elected lane issues: see elect_one() in tc_common.cuh)
+    RingCursor rc;
+    const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.wpacked);
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      const int q0 = (item % p.split) * chunks_per_item;
+      for (int q = 0; q < chunks_per_item; ++q) {
+        mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u, 100);
+        if (elect_one()) {
           mbar_arrive_expect_tx(bar_fullB + 8 * rc.s, (uint32_t)p.b_stage_bytes);
           bulk_copy_g2s(smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes + A_STAGE_BYTES,
                         wsrc + (size_t)(q0 + q) * p.b_stage_bytes, (uint32_t)p.b_stage_bytes, bar_fullB + 8 * rc.s);
-          rc.advance(nstages);
         }
+        __syncwarp();
+        rc.advance(nstages);
       }
     }
   } else if (warp == 5) {
     // =========================================================================== MMA issuer
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc(kTF32, TILE_PX, p.Cout);
-      RingCursor rc;
-      uint32_t tcount = 0;
-      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++tcount) {
-        const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
-        mbar_wait(bar_tempty + 8 * acc, accph ^ 1u, 200);  // epilogue drained this accumulator
+    const uint32_t idesc = umma_idesc(kTF32, TILE_PX, p.Cout);
+    RingCursor rc;
+    uint32_t tcount = 0;
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++tcount) {
+      const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
+      mbar_wait(bar_tempty + 8 * acc, accph ^ 1u, 50);  // epilogue drained this accumulator
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.acc_cols;
+      for (int q = 0; q < chunks_per_item; ++q) {
+        mbar_wait(bar_fullB + 8 * rc.s, rc.ph, 32);
+        mbar_wait(bar_fullA + 8 * rc.s, rc.ph, 32);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.acc_cols;
-        for (int q = 0; q < chunks_per_item; ++q) {
-          mbar_wait(bar_fullA + 8 * rc.s, rc.ph, 100);
-          mbar_wait(bar_fullB + 8 * rc.s, rc.ph, 100);
-          tc_fence_after();
-          const uint32_t a_addr = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
-          const uint64_t adesc = umma_desc_sw128(a_addr);
-          const uint64_t bdesc = umma_desc_sw128(a_addr + A_STAGE_BYTES);
+        const uint32_t a_addr = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
+        const uint64_t adesc = umma_desc_sw128(a_addr);
+        const uint64_t bdesc = umma_desc_sw128(a_addr + A_STAGE_BYTES);
+        if (elect_one()) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)  // 4 x 32 bytes of K per 128-byte row
             umma<kTF32>(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (q | kk) != 0 ? 1u : 0u);
           umma_commit(bar_empty + 8 * rc.s);       // frees the smem stage when these MMAs retire
-          rc.advance(nstages);
+          if (q == chunks_per_item - 1) umma_commit(bar_tfull + 8 * acc);   // accumulator complete -> epilogue
         }
-        umma_commit(bar_tfull + 8 * acc);          // accumulator complete -> epilogue
+        __syncwarp();
+        rc.advance(nstages);
       }
     }
   } else {
@@ -505,6 +508,17 @@ int dcn_tc_pack_weights(const float* weight, void* packed, int Cin, int Cout, in
   return check_launch("pack_weights_kernel");
 }
 
+int dcn_tc_launch_combine(const float* partial, void* y, int dtype, const float* scale, const float* bias, int64_t npix,
+                          int Cout, int split, int relu, cudaStream_t stream) {
+  const int64_t n4 = npix * Cout / 4;
+  const unsigned blocks = (unsigned)((n4 + 255) / 256 < 148 * 8 ? (n4 + 255) / 256 : 148 * 8);
+  if (dtype == CPOLY_BF16)
+    dcn_fwd_tc_combine_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(partial, reinterpret_cast<__nv_bfloat16*>(y), scale, bias, npix, Cout, split, relu);
+  else
+    dcn_fwd_tc_combine_kernel<float><<<blocks, 256, 0, stream>>>(partial, reinterpret_cast<float*>(y), scale, bias, npix, Cout, split, relu);
+  return check_launch("dcn_fwd_tc_combine_kernel");
+}
+
 int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   TcParams p;
   const int esize = a.dtype == CPOLY_BF16 ? 2 : 4;
@@ -551,15 +565,7 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
     dcn_fwd_tc_kernel<float><<<grid, NTHREADS, smem_bytes, stream>>>(p);
   }
   if (int rc = check_launch("dcn_fwd_tc_kernel")) return rc;
-  if (p.split > 1) {
-    const int64_t n4 = npix * a.Cout / 4;
-    const unsigned blocks = (unsigned)((n4 + 255) / 256 < 148 * 8 ? (n4 + 255) / 256 : 148 * 8);
-    if (a.dtype == CPOLY_BF16)
-      dcn_fwd_tc_combine_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(p.partial, reinterpret_cast<__nv_bfloat16*>(a.y.ptr), a.out_scale, a.bias, npix, a.Cout, p.split, a.relu);
-    else
-      dcn_fwd_tc_combine_kernel<float><<<blocks, 256, 0, stream>>>(p.partial, reinterpret_cast<float*>(a.y.ptr), a.out_scale, a.bias, npix, a.Cout, p.split, a.relu);
-    return check_launch("dcn_fwd_tc_combine_kernel");
-  }
+  if (p.split > 1) return dcn_tc_launch_combine(p.partial, a.y.ptr, a.dtype, a.out_scale, a.bias, npix, a.Cout, p.split, a.relu, stream);
   return CPOLY_OK;
 }
 

@@ -36,6 +36,7 @@ constexpr int DNT = 256;           // threads per CTA
 constexpr int DWARPS = DNT / 32;
 constexpr int KMAX = 1024;         // largest supported K
 constexpr int BAND = 128;          // columns per warp (4 per lane)
+constexpr int SCAN_RH = 8;         // rows per warp work item of the two scan passes
 constexpr int CAP = 4096;          // shared key list capacity of the select kernel
 constexpr int HBITS = 13;          // histogram over score bits [30:18]: exponent + 5 mantissa bits
 constexpr int HBINS = 1 << HBITS;
@@ -202,37 +203,86 @@ __device__ __forceinline__ float head_value(const cpoly_tensor4& t, int b, int c
 }
 
 
-// One warp scans its item (a 128-column band x rh rows of one class plane) and calls f(score, flat index) for
+// One warp scans its item (a 128-column band x RH rows of one class plane) and calls f(score, flat index) for
 // every NMS peak with a positive score, flat = c*H*W + y*W + x.
-template <typename T, typename F>
+// All RH + 2 rows (one halo row above and below) are LOADED FIRST - RH + 2 independent 16-byte loads per lane in
+// flight (5 KB per warp) - and only then shuffled / compared: with one row per loop iteration a warp paid one DRAM
+// latency per row, and a 64-image batch ran at 5 % of the HBM roof (tools/decode_bench.py).
+template <typename T, int RH, typename F>
 __device__ __forceinline__ void scan_item(const DecodeParams& p, int b, int item, int lane, F&& f) {
+  constexpr int NR = RH + 2;
+  const float NEG = -CUDART_INF_F;
   int t = item;
   const int band = t % p.nbands; t /= p.nbands;
   const int rc = t % p.nrowchunks;
   const int c = t / p.nrowchunks;
-  const int r0 = rc * p.rh, x0 = band * BAND;
+  const int r0 = rc * RH, x0 = band * BAND;
   const int HW = p.H * p.W;
   const bool logit = p.heat_is_logit != 0;
+  const int64_t sh = p.heat.sh, sw = p.heat.sw;
   const T* plane = reinterpret_cast<const T*>(p.heat.ptr) + (int64_t)b * p.heat.sb + (int64_t)c * p.heat.sc;
-  float v_cur[4], h_prev[4], h_cur[4], l, r, v[4];
-  load_row(plane, p.heat.sh, p.heat.sw, r0 - 1, p.H, p.W, x0, lane, logit, v, l, r);
-  hmax3(v, l, r, h_prev);
-  load_row(plane, p.heat.sh, p.heat.sw, r0, p.H, p.W, x0, lane, logit, v_cur, l, r);
-  hmax3(v_cur, l, r, h_cur);
-  for (int rr = 0; rr < p.rh; ++rr) {
-    const int y = r0 + rr;
-    if (y >= p.H) break;   // warp-uniform
-    float v_next[4], h_next[4];
-    load_row(plane, p.heat.sh, p.heat.sw, y + 1, p.H, p.W, x0, lane, logit, v_next, l, r);
-    hmax3(v_next, l, r, h_next);
+  const int xb = x0 + lane * 4;
+  // vector path: unit column stride, the lane's 4 columns inside the row, every row start aligned like the plane
+  const bool vec = sw == 1 && xb + 3 < p.W && ((sh * (int64_t)sizeof(T)) % (4 * sizeof(T)) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(plane + xb) % (4 * sizeof(T))) == 0);
+  const bool want_l = lane == 0 && x0 > 0, want_r = lane == 31 && x0 + BAND < p.W;
+  float v[NR][4], hl[NR], hr[NR];
+  // ---- phase 1: loads only
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float m = fmaxf(fmaxf(h_prev[j], h_cur[j]), h_next[j]);
-      const int x = x0 + lane * 4 + j;
-      if (x < p.W && v_cur[j] == m && v_cur[j] > 0.f) f(v_cur[j], (unsigned int)(c * HW + y * p.W + x));
+  for (int i = 0; i < NR; ++i) {
+    const int y = r0 - 1 + i;
+    const bool rv = (unsigned)y < (unsigned)p.H;
+    const T* row = plane + (int64_t)(rv ? y : 0) * sh;
+    v[i][0] = v[i][1] = v[i][2] = v[i][3] = NEG;
+    hl[i] = hr[i] = NEG;
+    if (rv) {
+      if (vec) {
+        if (sizeof(T) == 4) {
+          const float4 q = __ldg(reinterpret_cast<const float4*>(row + xb));
+          v[i][0] = q.x; v[i][1] = q.y; v[i][2] = q.z; v[i][3] = q.w;
+        } else {
+          const uint2 q = __ldg(reinterpret_cast<const uint2*>(row + xb));
+          v[i][0] = __uint_as_float(q.x << 16); v[i][1] = __uint_as_float(q.x & 0xffff0000u);
+          v[i][2] = __uint_as_float(q.y << 16); v[i][3] = __uint_as_float(q.y & 0xffff0000u);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (xb + j < p.W) v[i][j] = ld_as_float(row + (int64_t)(xb + j) * sw);
+      }
+      if (want_l) hl[i] = ld_as_float(row + (int64_t)(x0 - 1) * sw);
+      if (want_r) hr[i] = ld_as_float(row + (int64_t)(x0 + BAND) * sw);
     }
+  }
+  // ---- phase 2: logistic (fused hm.sigmoid_), horizontal neighbours, horizontal 3-max
+  float h[NR][4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { h_prev[j] = h_cur[j]; h_cur[j] = h_next[j]; v_cur[j] = v_next[j]; }
+  for (int i = 0; i < NR; ++i) {
+    if (logit) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[i][j] = v[i][j] == NEG ? NEG : sigmoidf_accurate(v[i][j]);
+      if (want_l && hl[i] != NEG) hl[i] = sigmoidf_accurate(hl[i]);
+      if (want_r && hr[i] != NEG) hr[i] = sigmoidf_accurate(hr[i]);
+    }
+    float left = __shfl_up_sync(0xffffffffu, v[i][3], 1);
+    float right = __shfl_down_sync(0xffffffffu, v[i][0], 1);
+    if (lane == 0) left = hl[i];
+    if (lane == 31) right = hr[i];
+    hmax3(v[i], left, right, h[i]);
+  }
+  // ---- phase 3: vertical 3-max, peak test
+#pragma unroll
+  for (int rr = 0; rr < RH; ++rr) {
+    const int y = r0 + rr;
+    if (y < p.H) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float m = fmaxf(fmaxf(h[rr][j], h[rr + 1][j]), h[rr + 2][j]);
+        const float cur = v[rr + 1][j];
+        const int x = xb + j;
+        if (x < p.W && cur == m && cur > 0.f) f(cur, (unsigned int)(c * HW + y * p.W + x));
+      }
+    }
   }
 }
 
@@ -247,7 +297,7 @@ __device__ __forceinline__ void cta_item_range(const DecodeParams& p, int64_t& b
 
 // ------------------------------------------------------------------ launch 1: NMS scan + score histogram
 template <typename T>
-__global__ void __launch_bounds__(DNT) decode_hist_kernel(DecodeParams p) {
+__global__ void __launch_bounds__(DNT, 2) decode_hist_kernel(DecodeParams p) {
   __shared__ unsigned int hist[HBINS];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int64_t beg, end;
@@ -262,7 +312,7 @@ __global__ void __launch_bounds__(DNT) decode_hist_kernel(DecodeParams p) {
     const int64_t lim = end < img_end ? end : img_end;
     const int64_t it = base + warp;
     if (it < lim) {
-      scan_item<T>(p, p.b0 + cur_b, (int)(it - (int64_t)cur_b * p.items_per_image), lane,
+      scan_item<T, SCAN_RH>(p, p.b0 + cur_b, (int)(it - (int64_t)cur_b * p.items_per_image), lane,
                    [&](float s, unsigned int) { atomicAdd(&hist[score_bin(s)], 1u); });
     }
     if (base + DWARPS >= lim) {   // uniform: image (or range) finished -> flush
@@ -321,7 +371,7 @@ __device__ int threshold_bin(const unsigned int* __restrict__ gh, int K, unsigne
 
 // ------------------------------------------------------------------ launch 2: threshold + candidate collection
 template <typename T>
-__global__ void __launch_bounds__(DNT) decode_collect_kernel(DecodeParams p) {
+__global__ void __launch_bounds__(DNT, 2) decode_collect_kernel(DecodeParams p) {
   __shared__ unsigned int sh[HBINS];
   __shared__ int s_tb;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -338,7 +388,7 @@ __global__ void __launch_bounds__(DNT) decode_collect_kernel(DecodeParams p) {
       const int b = p.b0 + cur_b;
       unsigned long long* cand = p.cand + (int64_t)b * CAND_CAP;
       unsigned int* cnt = p.cand_count + b;
-      scan_item<T>(p, b, (int)(it - (int64_t)cur_b * p.items_per_image), lane, [&](float s, unsigned int flat) {
+      scan_item<T, SCAN_RH>(p, b, (int)(it - (int64_t)cur_b * p.items_per_image), lane, [&](float s, unsigned int flat) {
         if (score_bin(s) >= tb) {
           const unsigned int pos = atomicAdd(cnt, 1u);   // the compiler aggregates same-address atomics per warp
           if (pos < (unsigned)CAND_CAP) cand[pos] = make_key(s, flat);
@@ -396,7 +446,7 @@ __global__ void __launch_bounds__(DNT) decode_select_kernel(DecodeParams p) {
     for (int base = 0; base < q.items_per_image; base += DWARPS) {
       const int it = base + warp;
       if (it < q.items_per_image) {
-        scan_item<T>(q, b, it, lane, [&](float s, unsigned int flat) {
+        scan_item<T, 2>(q, b, it, lane, [&](float s, unsigned int flat) {
           const unsigned long long key = make_key(s, flat);
           if (key > threshold) {
             const int pos = atomicAdd(&s_count, 1);
@@ -514,7 +564,7 @@ __global__ void __launch_bounds__(DNT) decode_select_kernel(DecodeParams p) {
 void plan(int B, int C, int H, int W, DecodeParams& p) {
   (void)B;
   p.nbands = (W + BAND - 1) / BAND;
-  p.rh = 8;
+  p.rh = SCAN_RH;
   p.nrowchunks = (H + p.rh - 1) / p.rh;
   p.items_per_image = C * p.nrowchunks * p.nbands;
 }
@@ -560,7 +610,7 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
     p.nb = a.B - b0 < group ? a.B - b0 : group;
     const int64_t items = (int64_t)p.nb * p.items_per_image;
     int64_t ctas = (items + DWARPS - 1) / DWARPS;
-    if (ctas > 2 * sms) ctas = 2 * sms;
+    if (ctas > 4 * sms) ctas = 4 * sms;   // 32 warps per SM, each with (SCAN_RH + 2) x 512 B of loads in flight
     if (bf) decode_hist_kernel<__nv_bfloat16><<<(unsigned)ctas, DNT, 0, stream>>>(p);
     else decode_hist_kernel<float><<<(unsigned)ctas, DNT, 0, stream>>>(p);
     if (int rc = check_launch("decode_hist_kernel")) return rc;

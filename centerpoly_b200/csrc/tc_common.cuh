@@ -50,6 +50,23 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, uint32_
     if ((++spins & 63u) == 0u && clock64() - t0 > WAIT_TIMEOUT_CYCLES) mbar_timeout(bar, parity);
   }
 }
+// Plain polling wait (no suspend-time hint, no nanosleep): lowest wake-up latency, for waits on the critical path of a
+// pipeline whose partner is known to be a few hundred cycles away.  Traps after ~2^26 polls instead of hanging.
+__device__ __forceinline__ void mbar_wait_poll(uint32_t bar, uint32_t parity) {
+  uint32_t spins = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (ok) return;
+    if (++spins > (1u << 26)) mbar_timeout(bar, parity);
+  }
+}
 __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                "l"(src), "r"(bytes), "r"(bar)
@@ -151,6 +168,19 @@ __device__ __forceinline__ uint32_t bf16x2_mul(uint32_t a, uint32_t b) {
   uint32_t d;
   asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
   return d;
+}
+
+// One lane of a CONVERGED warp (elect.sync): single-thread instructions (tcgen05.mma / commit, TMA copies) issued under
+// this predicate keep their operands on the uniform datapath; under a plain `lane == 0` test the compiler wraps each
+// of them in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~12 dependent instructions per MMA).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
 }
 
 // Incrementing (stage, phase) cursor of a ring of `n` pipeline stages — no runtime modulo.

@@ -77,9 +77,11 @@ TC_SHAPES = [  # (B, Cin, Cout, H, W) — reduced-resolution versions of the 7 I
 ]
 
 
+@pytest.mark.parametrize("sampler", ["gather", "window"])   # csrc/dcn_tc.cu (default) / csrc/dcn_tc_win.cu (TMA-staged window)
 @pytest.mark.parametrize("shape", TC_SHAPES, ids=lambda s: "x".join(map(str, s)))
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "fp32"])
-def test_tcgen05_forward_vs_oracle(shape, dtype):
+def test_tcgen05_forward_vs_oracle(shape, dtype, sampler, monkeypatch):
+    monkeypatch.setenv("CPOLY_TC_SAMPLER", sampler)   # read by libcpoly.so at every call
     B, Cin, Cout, H, W = shape
     case = make_dcn_case(317 + Cin + Cout, B, Cin, Cout, H, W, dtype=dtype)
     got = run_ours(case, "tcgen05", dtype=dtype, channels_last=True, backward=False)
@@ -87,8 +89,10 @@ def test_tcgen05_forward_vs_oracle(shape, dtype):
     gate(got["y"], want["y"], 1e-2 if dtype == torch.bfloat16 else 1e-3, "y")
 
 
+@pytest.mark.parametrize("sampler", ["gather", "window"])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "fp32"])
-def test_tcgen05_zero_offsets(dtype):
+def test_tcgen05_zero_offsets(dtype, sampler, monkeypatch):
+    monkeypatch.setenv("CPOLY_TC_SAMPLER", sampler)
     case = make_dcn_case(5, 1, 64, 64, 16, 32, offset_mode="zero", dtype=dtype)
     got = run_ours(case, "tcgen05", dtype=dtype, channels_last=True, backward=False)
     want = oracle(case, backward=False)

@@ -48,6 +48,8 @@ def main():
     ap.add_argument("--batch", type=int, default=1)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--dtypes", default="bf16,fp32")
+    ap.add_argument("--offset-std", type=float, default=2.0, help="std of the synthetic offsets in pixels (SURVEY 8d: 2)")
+    ap.add_argument("--shapes", type=int, default=len(SHAPES), help="only the first N shape classes")
     args = ap.parse_args()
     hbm, tf, src = peaks()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -57,11 +59,11 @@ def main():
         dtype = torch.bfloat16 if dname == "bf16" else torch.float32
         es = 2 if dname == "bf16" else 4
         total_ms = 0.0
-        for (Cin, Cout, H, W) in SHAPES:
+        for (Cin, Cout, H, W) in SHAPES[:args.shapes]:
             g = torch.Generator(device="cuda").manual_seed(317)
             x = torch.randn(B, Cin, H, W, device="cuda", generator=g).to(dtype).contiguous(memory_format=torch.channels_last)
             om = torch.randn(B, 27, H, W, device="cuda", generator=g)
-            om[:, :18] *= 2.0
+            om[:, :18] *= args.offset_std
             om = om.to(dtype).contiguous(memory_format=torch.channels_last)
             m = cp.DCN(Cin, Cout, (3, 3), 1, 1).cuda()
             w, bias = m.weight.detach(), m.bias.detach()
