@@ -383,41 +383,65 @@ __global__ void __launch_bounds__(256) dcn_bwd_bias_kernel(DcnGeom g, cpoly_tens
   if (threadIdx.x == 0) gb[o] = red[0];
 }
 
-// Channels-last fast path of the bias gradient (256 % Cout == 0): consecutive threads read consecutive channels of
-// consecutive pixels (coalesced), every thread keeps ONE channel, a CTA owns a fixed pixel range; partial[blk][o] is
-// then summed in block order by dcn_bwd_bias_final_kernel.  Fixed partition + fixed order = deterministic.
+// Channels-last fast path of the bias gradient: a thread owns one 16-byte piece of the channel vector (8 bf16 / 4 fp32
+// channels) and walks the pixels of its CTA's fixed range with four independent 16-byte loads in flight; the pieces
+// of a pixel are consecutive threads (coalesced).  partial[blk][o] is then summed over the blocks by one warp per
+// channel in a fixed order (dcn_bwd_bias_final_kernel).  Fixed partition + fixed order = deterministic.
 // (The one-CTA-per-channel kernel above reads NHWC with a stride of Cout elements: 341 us for 64 ch @256x512.)
-constexpr int BIAS_MAX_BLOCKS = 296;
+constexpr int BIAS_MAX_BLOCKS = 592;
 template <typename T>
 __global__ void __launch_bounds__(256) dcn_bwd_bias_partial_kernel(const T* __restrict__ gout, float* __restrict__ partial, int64_t npix,
                                                                   int Cout, int64_t pix_per_block) {
-  __shared__ float red[256];
-  const int rows = 256 / Cout, o = threadIdx.x % Cout, row = threadIdx.x / Cout;
+  constexpr int kVec = 16 / sizeof(T);
+  __shared__ float red[256][kVec];
+  const int lpp = Cout / kVec;                       // 16-byte pieces (threads) per pixel; divides 256
+  const int rows = 256 / lpp, piece = threadIdx.x % lpp, row = threadIdx.x / lpp;
   const int64_t p0 = (int64_t)blockIdx.x * pix_per_block;
   const int64_t p1 = p0 + pix_per_block < npix ? p0 + pix_per_block : npix;
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;   // four independent chains, combined in a fixed order
+  float acc[4][kVec];
+#pragma unroll
+  for (int u = 0; u < 4; ++u)
+#pragma unroll
+    for (int e = 0; e < kVec; ++e) acc[u][e] = 0.f;
+  auto add = [&](int u, int64_t p) {
+    const uint4 q = __ldg(reinterpret_cast<const uint4*>(gout + p * Cout) + piece);
+    if (sizeof(T) == 4) {
+      acc[u][0] += __uint_as_float(q.x); acc[u][1] += __uint_as_float(q.y);
+      acc[u][2 % kVec] += __uint_as_float(q.z); acc[u][3 % kVec] += __uint_as_float(q.w);
+    } else {
+      const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        acc[u][(2 * e) % kVec] += __uint_as_float(w[e] << 16);
+        acc[u][(2 * e + 1) % kVec] += __uint_as_float(w[e] & 0xffff0000u);
+      }
+    }
+  };
   int64_t p = p0 + row;
   for (; p + 3 * rows < p1; p += 4 * rows) {
-    s0 += ld_as_float(gout + p * Cout + o);
-    s1 += ld_as_float(gout + (p + rows) * Cout + o);
-    s2 += ld_as_float(gout + (p + 2 * rows) * Cout + o);
-    s3 += ld_as_float(gout + (p + 3 * rows) * Cout + o);
+    add(0, p); add(1, p + rows); add(2, p + 2 * rows); add(3, p + 3 * rows);
   }
-  for (; p < p1; p += rows) s0 += ld_as_float(gout + p * Cout + o);
-  red[threadIdx.x] = (s0 + s1) + (s2 + s3);
+  for (; p < p1; p += rows) add(0, p);
+#pragma unroll
+  for (int e = 0; e < kVec; ++e) red[threadIdx.x][e] = (acc[0][e] + acc[1][e]) + (acc[2][e] + acc[3][e]);
   __syncthreads();
   if (row == 0) {
-    float s = red[o];
-    for (int r = 1; r < rows; ++r) s += red[r * Cout + o];
-    partial[(int64_t)blockIdx.x * Cout + o] = s;
+#pragma unroll
+    for (int e = 0; e < kVec; ++e) {
+      float s = red[piece][e];
+      for (int r = 1; r < rows; ++r) s += red[r * lpp + piece][e];
+      partial[(int64_t)blockIdx.x * Cout + piece * kVec + e] = s;
+    }
   }
 }
-__global__ void dcn_bwd_bias_final_kernel(const float* __restrict__ partial, float* __restrict__ gb, int Cout, int nblk) {
-  const int o = blockIdx.x * blockDim.x + threadIdx.x;
-  if (o >= Cout) return;
+// one warp per channel: lane l sums blocks l, l+32, ... in order, then a fixed shuffle tree
+__global__ void __launch_bounds__(32) dcn_bwd_bias_final_kernel(const float* __restrict__ partial, float* __restrict__ gb, int Cout, int nblk) {
+  const int o = blockIdx.x, lane = threadIdx.x;
   float s = 0.f;
-  for (int b = 0; b < nblk; ++b) s += partial[(int64_t)b * Cout + o];
-  gb[o] = s;
+  for (int b = lane; b < nblk; b += 32) s += partial[(int64_t)b * Cout + o];
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+  if (lane == 0) gb[o] = s;
 }
 
 __global__ void zero_strided_kernel(cpoly_tensor4 t, int B, int C, int H, int W) {
@@ -511,9 +535,12 @@ int dcn_backward_simt(const cpoly_dcn_bwd_args& a, cudaStream_t stream) {
     if (int rc = check_launch("reduce_splits_kernel")) return rc;
   }
   const bool gout_nhwc = a.gout.sc == 1 && a.gout.sw == g.Cout && a.gout.sh == (int64_t)g.Wo * g.Cout && a.gout.sb == (int64_t)g.Ho * g.Wo * g.Cout;
-  if (a.gbias && gout_nhwc && g.Cout <= 256 && 256 % g.Cout == 0 && a.workspace &&
-      a.workspace_bytes >= (size_t)BIAS_MAX_BLOCKS * g.Cout * sizeof(float)) {
-    const int64_t min_ppb = (int64_t)(256 / g.Cout) * 8;   // >= 8 loads per thread, else as many CTAs as the cap allows
+  const int bias_vec = bf ? 8 : 4;
+  const bool bias_fast = gout_nhwc && g.Cout % bias_vec == 0 && 256 % (g.Cout / bias_vec) == 0 && g.Cout / bias_vec <= 256 &&
+                         (reinterpret_cast<uintptr_t>(a.gout.ptr) & 15) == 0;
+  if (a.gbias && bias_fast && a.workspace && a.workspace_bytes >= (size_t)BIAS_MAX_BLOCKS * g.Cout * sizeof(float)) {
+    const int rows = 256 / (g.Cout / bias_vec);
+    const int64_t min_ppb = (int64_t)rows * 8;   // >= 8 loads per thread, else as many CTAs as the cap allows
     int64_t nblk = (npix + min_ppb - 1) / min_ppb;
     if (nblk > BIAS_MAX_BLOCKS) nblk = BIAS_MAX_BLOCKS;
     const int64_t ppb = (npix + nblk - 1) / nblk;
@@ -522,7 +549,7 @@ int dcn_backward_simt(const cpoly_dcn_bwd_args& a, cudaStream_t stream) {
     if (bf) dcn_bwd_bias_partial_kernel<__nv_bfloat16><<<(unsigned)nblk, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(a.gout.ptr), partial, npix, g.Cout, ppb);
     else dcn_bwd_bias_partial_kernel<float><<<(unsigned)nblk, 256, 0, stream>>>(reinterpret_cast<const float*>(a.gout.ptr), partial, npix, g.Cout, ppb);
     if (int rc = check_launch("dcn_bwd_bias_partial_kernel")) return rc;
-    dcn_bwd_bias_final_kernel<<<(g.Cout + 63) / 64, 64, 0, stream>>>(partial, a.gbias, g.Cout, (int)nblk);
+    dcn_bwd_bias_final_kernel<<<g.Cout, 32, 0, stream>>>(partial, a.gbias, g.Cout, (int)nblk);
     if (int rc = check_launch("dcn_bwd_bias_final_kernel")) return rc;
   } else if (a.gbias) {
     if (bf) dcn_bwd_bias_kernel<__nv_bfloat16><<<g.Cout, 256, 0, stream>>>(g, a.gout, a.gbias);

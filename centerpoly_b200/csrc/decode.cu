@@ -51,6 +51,8 @@ struct DecodeParams {
   unsigned int* hist;          // [B][HBINS]
   unsigned long long* cand;    // [B][CAND_CAP]
   unsigned int* cand_count;    // [B]
+  int* tbin;                   // [B] histogram bin of the K-th best peak (decode_threshold_kernel)
+  unsigned int* item_max;      // [B][items_per_image] upper bound (float bits) of the peak scores of every scan item
   int rh;                      // rows per warp work item
   int nbands, nrowchunks, items_per_image;
   int b0, nb;                  // image group handled by this launch (kernels 1 and 2)
@@ -203,8 +205,10 @@ __device__ __forceinline__ float head_value(const cpoly_tensor4& t, int b, int c
 }
 
 
-// One warp scans its item (a 128-column band x RH rows of one class plane) and calls f(score, flat index) for
-// every NMS peak with a positive score, flat = c*H*W + y*W + x.
+// One warp scans its item (a 128-column band x RH rows of one class plane) and calls f(is_peak, score, max3x3, flat)
+// for EVERY pixel slot (flat = c*H*W + y*W + x; is_peak = NMS peak with a positive score) - unconditionally, so the
+// caller decides between predicated work (histogram: one predicated RED.shared, no branch) and a rare warp-uniform
+// branch (candidate collection).  Out-of-image rows / columns hold -inf and can never be peaks: no bounds tests.
 // All RH + 2 rows (one halo row above and below) are LOADED FIRST - RH + 2 independent 16-byte loads per lane in
 // flight (5 KB per warp) - and only then shuffled / compared: with one row per loop iteration a warp paid one DRAM
 // latency per row, and a 64-image batch ran at 5 % of the HBM roof (tools/decode_bench.py).
@@ -217,73 +221,106 @@ __device__ __forceinline__ void scan_item(const DecodeParams& p, int b, int item
   const int rc = t % p.nrowchunks;
   const int c = t / p.nrowchunks;
   const int r0 = rc * RH, x0 = band * BAND;
-  const int HW = p.H * p.W;
   const bool logit = p.heat_is_logit != 0;
   const int64_t sh = p.heat.sh, sw = p.heat.sw;
   const T* plane = reinterpret_cast<const T*>(p.heat.ptr) + (int64_t)b * p.heat.sb + (int64_t)c * p.heat.sc;
   const int xb = x0 + lane * 4;
-  // vector path: unit column stride, the lane's 4 columns inside the row, every row start aligned like the plane
-  const bool vec = sw == 1 && xb + 3 < p.W && ((sh * (int64_t)sizeof(T)) % (4 * sizeof(T)) == 0) &&
-                   ((reinterpret_cast<uintptr_t>(plane + xb) % (4 * sizeof(T))) == 0);
-  const bool want_l = lane == 0 && x0 > 0, want_r = lane == 31 && x0 + BAND < p.W;
-  float v[NR][4], hl[NR], hr[NR];
+  // vector path: unit column stride, every row start aligned like the plane
+  const bool aligned = sw == 1 && (sh % 4 == 0) && ((reinterpret_cast<uintptr_t>(plane + x0) % (4 * sizeof(T))) == 0);
+  const bool full = aligned && x0 + BAND <= p.W;   // warp-uniform: the whole band is inside the row
+  // lane 0 fetches the column left of the band, lane 31 the one right of it: one halo register per row
+  const bool want_h = (lane == 0 && x0 > 0) || (lane == 31 && x0 + BAND < p.W);
+  const int hx = lane == 0 ? x0 - 1 : x0 + BAND;
+  float v[NR][4], hv[NR];
+  auto vec_load = [&](const T* row, float (&o)[4]) {
+    if (sizeof(T) == 4) {
+      const float4 q = __ldg(reinterpret_cast<const float4*>(row + xb));
+      o[0] = q.x; o[1] = q.y; o[2] = q.z; o[3] = q.w;
+    } else {
+      const uint2 q = __ldg(reinterpret_cast<const uint2*>(row + xb));
+      o[0] = __uint_as_float(q.x << 16); o[1] = __uint_as_float(q.x & 0xffff0000u);
+      o[2] = __uint_as_float(q.y << 16); o[3] = __uint_as_float(q.y & 0xffff0000u);
+    }
+  };
   // ---- phase 1: loads only
+  if (full) {
 #pragma unroll
-  for (int i = 0; i < NR; ++i) {
-    const int y = r0 - 1 + i;
-    const bool rv = (unsigned)y < (unsigned)p.H;
-    const T* row = plane + (int64_t)(rv ? y : 0) * sh;
-    v[i][0] = v[i][1] = v[i][2] = v[i][3] = NEG;
-    hl[i] = hr[i] = NEG;
-    if (rv) {
-      if (vec) {
-        if (sizeof(T) == 4) {
-          const float4 q = __ldg(reinterpret_cast<const float4*>(row + xb));
-          v[i][0] = q.x; v[i][1] = q.y; v[i][2] = q.z; v[i][3] = q.w;
-        } else {
-          const uint2 q = __ldg(reinterpret_cast<const uint2*>(row + xb));
-          v[i][0] = __uint_as_float(q.x << 16); v[i][1] = __uint_as_float(q.x & 0xffff0000u);
-          v[i][2] = __uint_as_float(q.y << 16); v[i][3] = __uint_as_float(q.y & 0xffff0000u);
-        }
-      } else {
+    for (int i = 0; i < NR; ++i) {
+      const int y = r0 - 1 + i;
+      const bool rv = (unsigned)y < (unsigned)p.H;
+      const T* row = plane + (int64_t)(rv ? y : 0) * sh;
+      v[i][0] = v[i][1] = v[i][2] = v[i][3] = NEG;
+      hv[i] = NEG;
+      if (rv) {
+        vec_load(row, v[i]);
+        if (want_h) hv[i] = ld_as_float(row + hx);
+      }
+    }
+  } else if (aligned && p.W % 4 == 0) {   // ragged band, but every lane's 4 columns are all inside or all outside the row
+    const bool in = xb < p.W;
+#pragma unroll
+    for (int i = 0; i < NR; ++i) {
+      const int y = r0 - 1 + i;
+      const bool rv = (unsigned)y < (unsigned)p.H;
+      const T* row = plane + (int64_t)(rv ? y : 0) * sh;
+      v[i][0] = v[i][1] = v[i][2] = v[i][3] = NEG;
+      hv[i] = NEG;
+      if (rv) {
+        if (in) vec_load(row, v[i]);
+        if (want_h) hv[i] = ld_as_float(row + hx);
+      }
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < NR; ++i) {
+      const int y = r0 - 1 + i;
+      const bool rv = (unsigned)y < (unsigned)p.H;
+      const T* row = plane + (int64_t)(rv ? y : 0) * sh;
+      v[i][0] = v[i][1] = v[i][2] = v[i][3] = NEG;
+      hv[i] = NEG;
+      if (rv) {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
           if (xb + j < p.W) v[i][j] = ld_as_float(row + (int64_t)(xb + j) * sw);
+        if (want_h) hv[i] = ld_as_float(row + (int64_t)hx * sw);
       }
-      if (want_l) hl[i] = ld_as_float(row + (int64_t)(x0 - 1) * sw);
-      if (want_r) hr[i] = ld_as_float(row + (int64_t)(x0 + BAND) * sw);
     }
   }
-  // ---- phase 2: logistic (fused hm.sigmoid_), horizontal neighbours, horizontal 3-max
-  float h[NR][4];
+  // ---- phase 2 (rolling, three rows of horizontal maxima live): logistic (fused hm.sigmoid_), horizontal
+  // neighbours + 3-max of row i, then vertical 3-max + peak test of row i - 1
+  const unsigned int flat0 = (unsigned int)(c * (p.H * p.W) + r0 * p.W + xb);
+  float h_prev[4], h_cur[4], h_next[4];
 #pragma unroll
   for (int i = 0; i < NR; ++i) {
     if (logit) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) v[i][j] = v[i][j] == NEG ? NEG : sigmoidf_accurate(v[i][j]);
-      if (want_l && hl[i] != NEG) hl[i] = sigmoidf_accurate(hl[i]);
-      if (want_r && hr[i] != NEG) hr[i] = sigmoidf_accurate(hr[i]);
+      if (hv[i] != NEG) hv[i] = sigmoidf_accurate(hv[i]);
     }
     float left = __shfl_up_sync(0xffffffffu, v[i][3], 1);
     float right = __shfl_down_sync(0xffffffffu, v[i][0], 1);
-    if (lane == 0) left = hl[i];
-    if (lane == 31) right = hr[i];
-    hmax3(v[i], left, right, h[i]);
-  }
-  // ---- phase 3: vertical 3-max, peak test
-#pragma unroll
-  for (int rr = 0; rr < RH; ++rr) {
-    const int y = r0 + rr;
-    if (y < p.H) {
+    if (lane == 0) left = hv[i];
+    if (lane == 31) right = hv[i];
+    hmax3(v[i], left, right, h_next);
+    if (i >= 2) {
+      const int rr = i - 2;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float m = fmaxf(fmaxf(h[rr][j], h[rr + 1][j]), h[rr + 2][j]);
+        const float m = fmaxf(fmaxf(h_prev[j], h_cur[j]), h_next[j]);
         const float cur = v[rr + 1][j];
-        const int x = xb + j;
-        if (x < p.W && cur == m && cur > 0.f) f(cur, (unsigned int)(c * HW + y * p.W + x));
+        f(cur == m && cur > 0.f, cur, m, flat0 + (unsigned int)(rr * p.W + j));
       }
     }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { h_prev[j] = h_cur[j]; h_cur[j] = h_next[j]; }
   }
+}
+
+// hist[bin]++ when `on`: one predicated RED.shared, no branch around it
+__device__ __forceinline__ void red_shared_inc_if(bool on, uint32_t addr) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %0, 0;\n\t@q red.shared.add.u32 [%1], 1;\n\t}" ::"r"((uint32_t)on), "r"(addr)
+      : "memory");
 }
 
 // Work items of the image group [b0, b0+nb) are dealt to warps in CTA-contiguous blocks, so one CTA touches one
@@ -297,7 +334,7 @@ __device__ __forceinline__ void cta_item_range(const DecodeParams& p, int64_t& b
 
 // ------------------------------------------------------------------ launch 1: NMS scan + score histogram
 template <typename T>
-__global__ void __launch_bounds__(DNT, 2) decode_hist_kernel(DecodeParams p) {
+__global__ void __launch_bounds__(DNT, 3) decode_hist_kernel(DecodeParams p) {
   __shared__ unsigned int hist[HBINS];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int64_t beg, end;
@@ -305,6 +342,7 @@ __global__ void __launch_bounds__(DNT, 2) decode_hist_kernel(DecodeParams p) {
   if (beg >= end) return;
   int cur_b = (int)(beg / p.items_per_image);
   for (int i = tid; i < HBINS; i += DNT) hist[i] = 0u;
+  const uint32_t hist_addr = (uint32_t)__cvta_generic_to_shared(hist);
   __syncthreads();
   for (int64_t base = beg; base < end; base += DWARPS) {
     // all warps of an iteration work on the same image: stop the batch at the image boundary
@@ -312,8 +350,15 @@ __global__ void __launch_bounds__(DNT, 2) decode_hist_kernel(DecodeParams p) {
     const int64_t lim = end < img_end ? end : img_end;
     const int64_t it = base + warp;
     if (it < lim) {
-      scan_item<T, SCAN_RH>(p, p.b0 + cur_b, (int)(it - (int64_t)cur_b * p.items_per_image), lane,
-                   [&](float s, unsigned int) { atomicAdd(&hist[score_bin(s)], 1u); });
+      const int item = (int)(it - (int64_t)cur_b * p.items_per_image);
+      float mx = 0.f;   // upper bound of the item's peak scores: lets the collection pass skip items below the threshold bin
+      scan_item<T, SCAN_RH>(p, p.b0 + cur_b, item, lane, [&](bool pk, float s, float m3, unsigned int) {
+        red_shared_inc_if(pk, hist_addr + ((uint32_t)score_bin(s) << 2));
+        mx = fmaxf(mx, m3);   // >= every peak of the item (3x3 maxima incl. the halo): a conservative bound, one instruction
+      });
+#pragma unroll
+      for (int d = 16; d >= 1; d >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+      if (lane == 0) p.item_max[(int64_t)(p.b0 + cur_b) * p.items_per_image + item] = __float_as_uint(mx);
     }
     if (base + DWARPS >= lim) {   // uniform: image (or range) finished -> flush
       __syncthreads();
@@ -336,12 +381,13 @@ __global__ void __launch_bounds__(DNT, 2) decode_hist_kernel(DecodeParams p) {
 __device__ int threshold_bin(const unsigned int* __restrict__ gh, int K, unsigned int* sh, int* s_result) {
   const int tid = threadIdx.x;
   constexpr int PER = HBINS / DNT;   // bins per thread, thread t owns the descending range starting at HBINS-1-t*PER
-  unsigned int mine = 0;
-#pragma unroll 4
+  unsigned int mine = 0, cnt[PER];
+#pragma unroll
+  for (int q = 0; q < PER; ++q) cnt[q] = __ldcg(gh + (HBINS - 1 - tid * PER - q));   // all PER loads in flight
+#pragma unroll
   for (int q = 0; q < PER; ++q) {
-    const unsigned int n = __ldcg(gh + (HBINS - 1 - tid * PER - q));
-    sh[HBINS - 1 - tid * PER - q] = n;
-    mine += n;
+    sh[HBINS - 1 - tid * PER - q] = cnt[q];
+    mine += cnt[q];
   }
   // inclusive scan of per-thread sums over the block (descending bin order)
   __shared__ unsigned int warp_tot[DWARPS];
@@ -369,41 +415,57 @@ __device__ int threshold_bin(const unsigned int* __restrict__ gh, int K, unsigne
   return *s_result;
 }
 
-// ------------------------------------------------------------------ launch 2: threshold + candidate collection
+// ------------------------------------------------------------------ launch 2: threshold bin of every image
 template <typename T>
-__global__ void __launch_bounds__(DNT, 2) decode_collect_kernel(DecodeParams p) {
+__global__ void __launch_bounds__(DNT) decode_threshold_kernel(DecodeParams p) {
   __shared__ unsigned int sh[HBINS];
   __shared__ int s_tb;
+  const int b = p.b0 + blockIdx.x;
+  const int tb = threshold_bin(p.hist + (int64_t)b * HBINS, p.K, sh, &s_tb);
+  if (threadIdx.x == 0) p.tbin[b] = tb;
+}
+
+// ------------------------------------------------------------------ launch 3: candidate collection
+// Only the items whose best peak reaches the image's threshold bin are re-scanned (about K + one bin's worth of peaks
+// per image lie there), so this pass touches a few percent of the heat map instead of all of it again.
+template <typename T>
+__global__ void __launch_bounds__(DNT, 3) decode_collect_kernel(DecodeParams p) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  int64_t beg, end;
-  cta_item_range(p, beg, end);
-  if (beg >= end) return;
-  int cur_b = (int)(beg / p.items_per_image);
-  int tb = threshold_bin(p.hist + (int64_t)(p.b0 + cur_b) * HBINS, p.K, sh, &s_tb);
-  for (int64_t base = beg; base < end; base += DWARPS) {
-    const int64_t img_end = (int64_t)(cur_b + 1) * p.items_per_image;
-    const int64_t lim = end < img_end ? end : img_end;
-    const int64_t it = base + warp;
-    if (it < lim) {
-      const int b = p.b0 + cur_b;
+  const int64_t total = (int64_t)p.nb * p.items_per_image;
+  // a warp looks at 32 consecutive items at once (one per lane: coalesced reads of item_max) and re-scans the few
+  // whose best peak reaches their image's threshold bin
+  for (int64_t base = ((int64_t)blockIdx.x * DWARPS + warp) * 32; base < total; base += (int64_t)gridDim.x * DWARPS * 32) {
+    const int64_t mine = base + lane;
+    bool need = false;
+    if (mine < total) {
+      const int lb = (int)(mine / p.items_per_image);
+      const float mx = __uint_as_float(__ldcg(p.item_max + (int64_t)p.b0 * p.items_per_image + mine));
+      need = mx > 0.f && score_bin(mx) >= __ldcg(p.tbin + p.b0 + lb);
+    }
+    unsigned int todo = __ballot_sync(0xffffffffu, need);
+    while (todo) {   // warp-uniform
+      const int i = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int64_t it = base + i;
+      const int lb = (int)(it / p.items_per_image), item = (int)(it - (int64_t)lb * p.items_per_image);
+      const int b = p.b0 + lb;
+      const int tb = __ldcg(p.tbin + b);
       unsigned long long* cand = p.cand + (int64_t)b * CAND_CAP;
       unsigned int* cnt = p.cand_count + b;
-      scan_item<T, SCAN_RH>(p, b, (int)(it - (int64_t)cur_b * p.items_per_image), lane, [&](float s, unsigned int flat) {
-        if (score_bin(s) >= tb) {
-          const unsigned int pos = atomicAdd(cnt, 1u);   // the compiler aggregates same-address atomics per warp
-          if (pos < (unsigned)CAND_CAP) cand[pos] = make_key(s, flat);
+      scan_item<T, SCAN_RH>(p, b, item, lane, [&](bool pk, float s, float, unsigned int flat) {
+        const bool take = pk && score_bin(s) >= tb;
+        if (__any_sync(0xffffffffu, take)) {
+          if (take) {
+            const unsigned int pos = atomicAdd(cnt, 1u);   // the compiler aggregates same-address atomics per warp
+            if (pos < (unsigned)CAND_CAP) cand[pos] = make_key(s, flat);
+          }
         }
       });
-    }
-    if (base + DWARPS >= lim && lim < end) {   // uniform: next image
-      cur_b += 1;
-      base = lim - DWARPS;
-      tb = threshold_bin(p.hist + (int64_t)(p.b0 + cur_b) * HBINS, p.K, sh, &s_tb);
     }
   }
 }
 
-// ------------------------------------------------------------------ launch 3: select + sort + gather (one CTA per image)
+// ------------------------------------------------------------------ launch 4: select + sort (one CTA per image)
 template <typename T>
 __global__ void __launch_bounds__(DNT) decode_select_kernel(DecodeParams p) {
   __shared__ unsigned long long list[CAP];
@@ -446,9 +508,9 @@ __global__ void __launch_bounds__(DNT) decode_select_kernel(DecodeParams p) {
     for (int base = 0; base < q.items_per_image; base += DWARPS) {
       const int it = base + warp;
       if (it < q.items_per_image) {
-        scan_item<T, 2>(q, b, it, lane, [&](float s, unsigned int flat) {
+        scan_item<T, 2>(q, b, it, lane, [&](bool pk, float s, float, unsigned int flat) {
           const unsigned long long key = make_key(s, flat);
-          if (key > threshold) {
+          if (pk && key > threshold) {
             const int pos = atomicAdd(&s_count, 1);
             if (pos < CAP) list[pos] = key;  // cannot overflow: a prune precedes any round that could
           }
@@ -506,16 +568,33 @@ __global__ void __launch_bounds__(DNT) decode_select_kernel(DecodeParams p) {
       __syncthreads();
     }
 
-  // ---- gather epilogue: one warp per detection
+  // ---- the K sorted keys go back to the head of this image's candidate list (all of it is in shared memory by now);
+  // decode_gather_kernel, one warp per detection over the whole batch, turns them into output rows.
+  unsigned long long* dst = p.cand + (int64_t)b * CAND_CAP;
+  for (int k = tid; k < K; k += DNT) dst[k] = list[k];
+}
+
+// ------------------------------------------------------------------ launch 5: gather + polygon assembly
+// One warp per detection, B*K warps in flight: inside the select kernel (one CTA per image, 8 warps) the ~13 rounds
+// of dependent head reads of a K = 100 image cost 25-30 us of pure DRAM latency.
+template <typename T>
+__global__ void __launch_bounds__(DNT) decode_gather_kernel(DecodeParams p) {
+  const int lane = threadIdx.x & 31;
+  const int K = p.K;
+  const int HW = p.H * p.W;
+  const int64_t det = (int64_t)blockIdx.x * DWARPS + (threadIdx.x >> 5);
+  if (det >= (int64_t)p.B * K) return;
+  const int b = (int)(det / K), k = (int)(det - (int64_t)b * K);
   const int N = p.n_poly / 2;
   const int row_len = p.n_poly + 7;
-  for (int k = warp; k < K; k += DWARPS) {
-    const unsigned long long key = list[k];
+  {
+    const unsigned long long key = __ldcg(p.cand + (int64_t)b * CAND_CAP + k);
     const unsigned int flat = 0xffffffffu - (unsigned int)(key & 0xffffffffull);
     const float score = ordered_to_float((unsigned int)(key >> 32));
     const int cls = (int)(flat / (unsigned int)HW);
     const int pix = (int)(flat - (unsigned int)cls * (unsigned int)HW);
     const int y = pix / p.W, x = pix - y * p.W;
+    const float dep = head_value<T>(p.depth, b, 0, y, x);   // issued with the other head reads, used last
     float xs, ys;
     if (p.reg.ptr) {  // decode.py:523-527
       xs = __fadd_rn((float)x, head_value<T>(p.reg, b, 0, y, x));
@@ -555,10 +634,10 @@ __global__ void __launch_bounds__(DNT) decode_select_kernel(DecodeParams p) {
       orow[0] = xmin; orow[1] = ymin; orow[2] = xmax; orow[3] = ymax;  // decode.py:647-659
       orow[4] = score;
       orow[5] = (float)cls;
-      orow[6 + p.n_poly] = head_value<T>(p.depth, b, 0, y, x);
+      orow[6 + p.n_poly] = dep;
       if (p.out_inds) p.out_inds[(int64_t)b * K + k] = pix;
     }
-  }
+    }
 }
 
 void plan(int B, int C, int H, int W, DecodeParams& p) {
@@ -573,9 +652,13 @@ size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 
 }  // namespace
 
+static size_t decode_zero_bytes(int B) { return (size_t)B * HBINS * sizeof(unsigned int) + 2 * (size_t)B * sizeof(unsigned int); }
+static size_t decode_items_per_image(int C, int H, int W) {
+  return (size_t)C * ((H + SCAN_RH - 1) / SCAN_RH) * ((W + BAND - 1) / BAND);
+}
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K) {
-  (void)C; (void)H; (void)W; (void)K;
-  return align256((size_t)B * HBINS * sizeof(unsigned int) + (size_t)B * sizeof(unsigned int)) +
+  (void)K;
+  return align256(decode_zero_bytes(B)) + align256((size_t)B * decode_items_per_image(C, H, W) * sizeof(unsigned int)) +
          align256((size_t)B * CAND_CAP * sizeof(unsigned long long)) + 256;
 }
 
@@ -591,36 +674,46 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
                 "decode workspace too small: need %zu bytes, have %zu", need, a.workspace_bytes);
   CPOLY_REQUIRE((reinterpret_cast<uintptr_t>(a.workspace) & 255) == 0, CPOLY_EINVAL, "decode workspace must be 256-byte aligned");
   char* ws = reinterpret_cast<char*>(a.workspace);
-  const size_t zero_bytes = (size_t)a.B * HBINS * sizeof(unsigned int) + (size_t)a.B * sizeof(unsigned int);
+  const size_t zero_bytes = decode_zero_bytes(a.B);
   p.hist = reinterpret_cast<unsigned int*>(ws);
   p.cand_count = p.hist + (size_t)a.B * HBINS;
+  p.tbin = reinterpret_cast<int*>(p.cand_count + a.B);
   ws += align256(zero_bytes);
+  p.item_max = reinterpret_cast<unsigned int*>(ws);
+  ws += align256((size_t)a.B * decode_items_per_image(a.C, a.H, a.W) * sizeof(unsigned int));
   p.cand = reinterpret_cast<unsigned long long*>(ws);
   CPOLY_CUDA_OK(cudaMemsetAsync(p.hist, 0, zero_bytes, stream));
   int dev = 0, sms = 0;
   CPOLY_CUDA_OK(cudaGetDevice(&dev));
   CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  // image groups whose heat maps (<= 48 MB) stay L2 resident between the histogram and the collection pass
-  const size_t img_bytes = (size_t)a.C * a.H * a.W * (a.dtype == CPOLY_BF16 ? 2 : 4);
-  int group = (int)((48u << 20) / (img_bytes ? img_bytes : 1));
-  if (group < 1) group = 1;
   const bool bf = a.dtype == CPOLY_BF16;
-  for (int b0 = 0; b0 < a.B; b0 += group) {
-    p.b0 = b0;
-    p.nb = a.B - b0 < group ? a.B - b0 : group;
+  {
+    // one pass over the whole batch: the collection pass re-reads only the few items that hold top-K candidates,
+    // so there is no L2-residency reason to split the batch into groups any more
+    p.b0 = 0;
+    p.nb = a.B;
     const int64_t items = (int64_t)p.nb * p.items_per_image;
     int64_t ctas = (items + DWARPS - 1) / DWARPS;
-    if (ctas > 4 * sms) ctas = 4 * sms;   // 32 warps per SM, each with (SCAN_RH + 2) x 512 B of loads in flight
+    if (ctas > 3 * sms) ctas = 3 * sms;   // one resident wave: 24 warps per SM, each with (SCAN_RH + 2) x 512 B of loads in flight
     if (bf) decode_hist_kernel<__nv_bfloat16><<<(unsigned)ctas, DNT, 0, stream>>>(p);
     else decode_hist_kernel<float><<<(unsigned)ctas, DNT, 0, stream>>>(p);
     if (int rc = check_launch("decode_hist_kernel")) return rc;
-    if (bf) decode_collect_kernel<__nv_bfloat16><<<(unsigned)ctas, DNT, 0, stream>>>(p);
-    else decode_collect_kernel<float><<<(unsigned)ctas, DNT, 0, stream>>>(p);
+    if (bf) decode_threshold_kernel<__nv_bfloat16><<<(unsigned)a.B, DNT, 0, stream>>>(p);
+    else decode_threshold_kernel<float><<<(unsigned)a.B, DNT, 0, stream>>>(p);
+    if (int rc = check_launch("decode_threshold_kernel")) return rc;
+    int64_t cctas = (items + 32 * DWARPS - 1) / (32 * DWARPS);
+    if (cctas > 3 * sms) cctas = 3 * sms;
+    if (bf) decode_collect_kernel<__nv_bfloat16><<<(unsigned)cctas, DNT, 0, stream>>>(p);
+    else decode_collect_kernel<float><<<(unsigned)cctas, DNT, 0, stream>>>(p);
     if (int rc = check_launch("decode_collect_kernel")) return rc;
   }
   if (bf) decode_select_kernel<__nv_bfloat16><<<(unsigned)a.B, DNT, 0, stream>>>(p);
   else decode_select_kernel<float><<<(unsigned)a.B, DNT, 0, stream>>>(p);
-  return check_launch("decode_select_kernel");
+  if (int rc = check_launch("decode_select_kernel")) return rc;
+  const unsigned gblocks = (unsigned)(((int64_t)a.B * a.K + DWARPS - 1) / DWARPS);
+  if (bf) decode_gather_kernel<__nv_bfloat16><<<gblocks, DNT, 0, stream>>>(p);
+  else decode_gather_kernel<float><<<gblocks, DNT, 0, stream>>>(p);
+  return check_launch("decode_gather_kernel");
 }
 
 }  // namespace cpoly

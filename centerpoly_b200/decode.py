@@ -52,9 +52,7 @@ def _decode(heat, polys, depth, reg, cat_spec_poly, K, rep, heat_is_logit, retur
         a.out_inds = inds.data_ptr() if inds is not None else None
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
         _lib.check(L.cpoly_decode(byref(a), _lib.stream_ptr(dev)), "cpoly_decode")
-        img_bytes = C * H * W * heat.element_size()
-        groups = -(-B // max(1, (48 << 20) // max(1, img_bytes)))
-        _lib.LAUNCHES["decode"] += 2 * groups + 1      # (histogram + collect) per image group, one select
+        _lib.LAUNCHES["decode"] += 5   # histogram, threshold, collect, select, gather (csrc/decode.cu)
     return (out, inds) if return_inds else out
 
 

@@ -6,7 +6,7 @@ Two workloads: the Cityscapes frame of BASELINE.json configs[1] (B=1, 8 classes,
 4.44 MB algorithmic -> latency-bound, reported in us) and the polar IDD batch of configs[4] (B=64, 9 classes,
 272x488 maps, rep='polar'; 321 MB algorithmic -> bandwidth-bound, reported as a fraction of the measured HBM peak).
 Algorithmic bytes = s*B*C*H*W (heat once) + B*K*(2N+3)*32 (sector-granular gathers from NCHW heads) + B*K*(2N+7)*4.
-CUDA events, L2 flushed before every call.  Prints one JSON line per workload."""
+CUDA events around a CUDA-graph replay of one call, L2 flushed before every replay.  Prints one JSON line per workload."""
 import argparse
 import json
 import os
@@ -43,12 +43,17 @@ def main():
         for _ in range(3):
             fn()
         torch.cuda.synchronize()
+        # replayed from a CUDA graph like the inference engine does (5 small launches: without it the B=1 number is
+        # the host's launch rate, not the kernels)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            fn()
         ts = []
         for _ in range(args.iters):
             flush.zero_()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            fn()
+            graph.replay()
             b.record()
             torch.cuda.synchronize()
             ts.append(a.elapsed_time(b))
@@ -57,7 +62,7 @@ def main():
         alg = 4 * B * C * H * W + B * K * (2 * N + 3) * 32 + B * K * (2 * N + 7) * 4
         print(json.dumps(dict(workload=name, B=B, C=C, H=H, W=W, K=K, rep=rep, us=round(ms * 1000, 1),
                               algorithmic_mb=round(alg / 1e6, 2), gbs=round(alg / ms / 1e6, 1), hbm_peak_gbs=peak,
-                              frac_hbm=round(alg / ms / 1e6 / peak, 3), peak_source=src, launches_per_call=3)), flush=True)
+                              frac_hbm=round(alg / ms / 1e6 / peak, 3), peak_source=src, launches_per_call=5, timed="CUDA graph replay, L2 flushed")), flush=True)
 
 
 if __name__ == "__main__":

@@ -34,8 +34,9 @@ def launches(path):
         v = float(row["Metric Value"].replace(",", ""))
         unit = row["Metric Unit"]
         v = v / 1e3 if unit in ("ns", "nsecond") else (v * 1e3 if unit in ("ms", "msecond") else v)
-        name = re.sub(r"\(.*", "", row["Kernel Name"])
-        name = re.sub(r"<.*", "", name)[:90]
+        name = row["Kernel Name"]
+        m = re.search(r"(?:<unnamed>::|cpoly::)+(\w+)", name)   # our kernels: bare name without namespace / template args
+        name = m.group(1) if m else re.sub(r"<.*", "", re.sub(r"\(.*", "", name))[:90]
         e = agg.setdefault(name, [0, 0.0])
         e[0] += 1
         e[1] += v
