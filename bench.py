@@ -4,7 +4,7 @@
     python bench.py --gpus N --steps K --warmup W [--dtype bf16|fp32] [--impl reference]
 
 A step = one pass of the hot path over one synthetic 2048x1024 frame: DLA-34 network (16 DCNv2 layers through
-libcpoly.so) -> sigmoid -> fused polydet_decode, replayed from a CUDA graph.  Prints ONE JSON line (rank 0).
+libcpoly.so) -> sigmoid -> fused polydet_decode (+ the back-mapping of polydet_post_process), replayed from a CUDA graph.  Prints ONE JSON line (rank 0).
 See DESIGN.md "Measurement" for how every field is produced.
 """
 import argparse
@@ -13,6 +13,8 @@ import os
 import sys
 import threading
 import time
+
+import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -112,6 +114,7 @@ class CpuArm:
 
     def frame_seconds(self, height, width):
         from oracle.decode_oracle import polydet_decode_oracle, sigmoid_f32
+        from oracle.postprocess_oracle import polydet_post_process_oracle
         torch = self.torch
         x = self.frames.get((height, width))
         if x is None:
@@ -120,7 +123,10 @@ class CpuArm:
         with torch.no_grad():
             out = self.net(x)[-1]
         heat = sigmoid_f32(out["hm"].numpy())
-        polydet_decode_oracle(heat, out["poly"].numpy(), out["pseudo_depth"].numpy(), reg=out["reg"].numpy(), K=K_DET)
+        dets = polydet_decode_oracle(heat, out["poly"].numpy(), out["pseudo_depth"].numpy(), reg=out["reg"].numpy(), K=K_DET)
+        # the detector's post_process (detectors/polydet.py:45-50), which the GPU arm fuses into its decode
+        c = [np.array([width / 2.0, height / 2.0], dtype=np.float32)]
+        polydet_post_process_oracle(dets, c, [float(max(height, width))], height // 4, width // 4, N_CLS)
         return time.perf_counter() - t0
 
 
@@ -143,7 +149,7 @@ def run_reference(args):
     for _ in range(args.steps):
         dt += arm.frame_seconds(h, w)
     fps = args.steps / frac / dt
-    sample = f"{args.steps} steps, each one {w}x{h} crop = 1/{frac} of a 2048x1024 frame (cost linear in pixels); torchvision CPU deform_conv2d + numpy decode oracle"
+    sample = f"{args.steps} steps, each one {w}x{h} crop = 1/{frac} of a 2048x1024 frame (cost linear in pixels); torchvision CPU deform_conv2d + numpy decode and post-process oracles"
     line = dict(impl="reference", metric=METRIC, value=fps, unit="frames/s", n_gpus=args.gpus, steps=args.steps,
                 warmup=args.warmup, ms_per_step=1000.0 * dt / args.steps * frac, higher_is_better=True, scaling="weak",
                 vs_baseline=None, dtype="f32", data="synthetic",
@@ -265,7 +271,7 @@ def run_ours(args):
             t_cpu = arm.frame_seconds(512, 1024)
             cpu = dict(value=1.0 / (4.0 * t_cpu), unit="frames/s", cores=threads, kind="port",
                        sample="one 1024x512 crop (1/4 of the 2048x1024 frame, cost linear in pixels) through the same DLA-34 "
-                              "network with torchvision CPU deform_conv2d + numpy decode oracle; %.2f s" % t_cpu)
+                              "network with torchvision CPU deform_conv2d + numpy decode and post-process oracles; %.2f s" % t_cpu)
         # our kernels per frame, counted by the shims on a warm eager frame: 16 dcn_fwd_tc_kernel (+ a combine kernel
         # on the tap-split layers) + 8 upsample_nhwc_kernel + 3 decode kernels
         launches_per_step = eng.launches_per_step

@@ -54,7 +54,8 @@ class UpsampleArgs(Structure):
 class DecodeArgs(Structure):
     _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "n_poly", "K", "rep", "heat_is_logit", "dtype")] + [
         ("heat", Tensor4), ("polys", Tensor4), ("depth", Tensor4), ("reg", Tensor4),
-        ("out", c_void_p), ("out_inds", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+        ("out", c_void_p), ("out_inds", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+        ("post_affine", c_void_p)]
 
 
 _lib = None
@@ -94,7 +95,7 @@ def lib():
         L.cpoly_decode_workspace_bytes.argtypes = [c_int32] * 5
         L.cpoly_decode.restype = c_int32
         L.cpoly_decode.argtypes = [POINTER(DecodeArgs), c_void_p]
-        if L.cpoly_abi_version() != 2:
+        if L.cpoly_abi_version() != 3:
             raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
         _lib = L
     return _lib

@@ -48,6 +48,7 @@ struct DecodeParams {
   cpoly_tensor4 heat, polys, depth, reg;
   float* out;
   int64_t* out_inds;
+  const double* post_affine;   // (B,6) inverse affine of polydet_post_process, or NULL
   unsigned int* hist;          // [B][HBINS]
   unsigned long long* cand;    // [B][CAND_CAP]
   unsigned int* cand_count;    // [B]
@@ -604,6 +605,13 @@ __global__ void __launch_bounds__(DNT) decode_gather_kernel(DecodeParams p) {
       ys = (float)y + 0.5f;
     }
     float* orow = p.out + ((int64_t)b * K + k) * row_len;
+    // optional back-mapping to the original image (utils/post_process.py:105-112): fp64 like the reference's np.dot
+    double t00 = 1.0, t01 = 0.0, t02 = 0.0, t10 = 0.0, t11 = 1.0, t12 = 0.0;
+    const bool post = p.post_affine != nullptr;
+    if (post) {
+      const double* t = p.post_affine + (int64_t)b * 6;
+      t00 = t[0]; t01 = t[1]; t02 = t[2]; t10 = t[3]; t11 = t[4]; t12 = t[5];
+    }
     float xmin = CUDART_INF_F, ymin = CUDART_INF_F, xmax = -CUDART_INF_F, ymax = -CUDART_INF_F;
     for (int vtx = lane; vtx < N; vtx += 32) {
       float px = head_value<T>(p.polys, b, 2 * vtx, y, x);
@@ -618,8 +626,13 @@ __global__ void __launch_bounds__(DNT) decode_gather_kernel(DecodeParams p) {
       }
       px = __fadd_rn(px, xs);  // decode.py:624-625
       py = __fadd_rn(py, ys);
-      orow[6 + 2 * vtx] = px;
-      orow[6 + 2 * vtx + 1] = py;
+      if (post) {   // the box below is the min/max of the UNMAPPED vertices (decode.py:647-659), mapped afterwards
+        orow[6 + 2 * vtx] = (float)(t00 * (double)px + t01 * (double)py + t02);
+        orow[6 + 2 * vtx + 1] = (float)(t10 * (double)px + t11 * (double)py + t12);
+      } else {
+        orow[6 + 2 * vtx] = px;
+        orow[6 + 2 * vtx + 1] = py;
+      }
       xmin = fminf(xmin, px); xmax = fmaxf(xmax, px);
       ymin = fminf(ymin, py); ymax = fmaxf(ymax, py);
     }
@@ -631,7 +644,14 @@ __global__ void __launch_bounds__(DNT) decode_gather_kernel(DecodeParams p) {
       ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, d));
     }
     if (lane == 0) {
-      orow[0] = xmin; orow[1] = ymin; orow[2] = xmax; orow[3] = ymax;  // decode.py:647-659
+      if (post) {   // post_process.py:109-110: the two corners are mapped as points
+        orow[0] = (float)(t00 * (double)xmin + t01 * (double)ymin + t02);
+        orow[1] = (float)(t10 * (double)xmin + t11 * (double)ymin + t12);
+        orow[2] = (float)(t00 * (double)xmax + t01 * (double)ymax + t02);
+        orow[3] = (float)(t10 * (double)xmax + t11 * (double)ymax + t12);
+      } else {
+        orow[0] = xmin; orow[1] = ymin; orow[2] = xmax; orow[3] = ymax;  // decode.py:647-659
+      }
       orow[4] = score;
       orow[5] = (float)cls;
       orow[6 + p.n_poly] = dep;
@@ -667,7 +687,7 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
   p.B = a.B; p.C = a.C; p.H = a.H; p.W = a.W; p.n_poly = a.n_poly; p.K = a.K; p.rep = a.rep;
   p.heat_is_logit = a.heat_is_logit; p.dtype = a.dtype;
   p.heat = a.heat; p.polys = a.polys; p.depth = a.depth; p.reg = a.reg;
-  p.out = a.out; p.out_inds = a.out_inds;
+  p.out = a.out; p.out_inds = a.out_inds; p.post_affine = a.post_affine;
   plan(a.B, a.C, a.H, a.W, p);
   const size_t need = decode_workspace_bytes(a.B, a.C, a.H, a.W, a.K);
   CPOLY_REQUIRE(a.workspace && a.workspace_bytes >= need, CPOLY_EWORKSPACE,

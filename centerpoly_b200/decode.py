@@ -16,7 +16,7 @@ from . import _lib
 __all__ = ["polydet_decode", "polydet_decode_from_logits"]
 
 
-def _decode(heat, polys, depth, reg, cat_spec_poly, K, rep, heat_is_logit, return_inds=False):
+def _decode(heat, polys, depth, reg, cat_spec_poly, K, rep, heat_is_logit, return_inds=False, post_affine=None):
     if cat_spec_poly:
         # dead/buggy branch of the reference (decode.py:514,534-537 uses W as the vertex count)
         raise NotImplementedError("cat_spec_poly=True is not supported (it is broken in the reference as well)")
@@ -49,6 +49,14 @@ def _decode(heat, polys, depth, reg, cat_spec_poly, K, rep, heat_is_logit, retur
         a.dtype = _lib.dtype_code(heat)
         a.heat, a.polys, a.depth, a.reg = _lib.t4(heat), _lib.t4(polys), _lib.t4(depth), _lib.t4(reg)
         a.out = out.data_ptr()
+        if post_affine is not None:
+            # (B,2,3) inverse affine of polydet_post_process; fp64 on the device, applied by the gather kernel
+            if not (torch.is_tensor(post_affine) and post_affine.is_cuda):
+                post_affine = torch.as_tensor(post_affine, dtype=torch.float64).to(dev, non_blocking=True)
+            post_affine = post_affine.to(torch.float64).contiguous()
+            if post_affine.numel() != B * 6:
+                raise RuntimeError(f"polydet_decode: post_affine must hold {B} 2x3 matrices")
+            a.post_affine = post_affine.data_ptr()
         a.out_inds = inds.data_ptr() if inds is not None else None
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
         _lib.check(L.cpoly_decode(byref(a), _lib.stream_ptr(dev)), "cpoly_decode")
@@ -56,11 +64,14 @@ def _decode(heat, polys, depth, reg, cat_spec_poly, K, rep, heat_is_logit, retur
     return (out, inds) if return_inds else out
 
 
-def polydet_decode(heat, polys, depth, reg=None, cat_spec_poly=False, K=100, rep='cartesian'):
-    """(B, K, 2N+7) float32: [xmin, ymin, xmax, ymax, score, class, x0, y0, ..., pseudo_depth]."""
-    return _decode(heat, polys, depth, reg, cat_spec_poly, K, rep, heat_is_logit=False)
+def polydet_decode(heat, polys, depth, reg=None, cat_spec_poly=False, K=100, rep='cartesian', post_affine=None):
+    """(B, K, 2N+7) float32: [xmin, ymin, xmax, ymax, score, class, x0, y0, ..., pseudo_depth].
+
+    ``post_affine`` (optional, (B,2,3), see ``centerpoly_b200.post_process.batch_inverse_affine``) additionally fuses the
+    coordinate back-mapping of ``polydet_post_process`` (src/lib/utils/post_process.py:105-112) into the gather kernel."""
+    return _decode(heat, polys, depth, reg, cat_spec_poly, K, rep, heat_is_logit=False, post_affine=post_affine)
 
 
-def polydet_decode_from_logits(hm_logits, polys, depth, reg=None, cat_spec_poly=False, K=100, rep='cartesian'):
+def polydet_decode_from_logits(hm_logits, polys, depth, reg=None, cat_spec_poly=False, K=100, rep='cartesian', post_affine=None):
     """Same, but takes the raw ``hm`` head and fuses the ``sigmoid_`` of detectors/polydet.py:28."""
-    return _decode(hm_logits, polys, depth, reg, cat_spec_poly, K, rep, heat_is_logit=True)
+    return _decode(hm_logits, polys, depth, reg, cat_spec_poly, K, rep, heat_is_logit=True, post_affine=post_affine)

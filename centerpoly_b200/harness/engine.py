@@ -1,5 +1,6 @@
 """Inference engine around the hot path: DLA-34 polydet network (harness/dla34.py) -> ``hm.sigmoid_()`` ->
-``polydet_decode``, i.e. what ``PolydetDetector.process`` does (src/lib/detectors/polydet.py:25-43), captured
+``polydet_decode`` (+ the coordinate back-mapping of ``polydet_post_process``, fused into the decode), i.e. what
+``PolydetDetector.process`` and ``post_process`` do (src/lib/detectors/polydet.py:25-60), captured
 once into a CUDA graph so the ~250 launches of a frame replay without host overhead.
 
 ``infer_resident`` replays on a frame already in HBM; ``infer_host`` is the end-to-end call: pinned host
@@ -14,6 +15,7 @@ import contextlib
 import torch
 
 from .. import decode as cdecode
+from .. import post_process as cpost
 from .dla34 import PolydetDLA34, calibrate_random_init
 
 HEADS = {"hm": 8, "poly": 64, "pseudo_depth": 1, "reg": 2}
@@ -21,7 +23,7 @@ HEADS = {"hm": 8, "poly": 64, "pseudo_depth": 1, "reg": 2}
 
 class PolydetEngine:
     def __init__(self, height=1024, width=2048, batch=1, dtype="bf16", K=100, rep="cartesian", heads=None,
-                 device="cuda:0", seed=317, calibrate=True, use_graph=True, n_slots=2, optimize=True):
+                 device="cuda:0", seed=317, calibrate=True, use_graph=True, n_slots=2, optimize=True, post_process=True):
         self.device = torch.device(device)
         self.dtype = dtype
         self.K, self.rep = K, rep
@@ -48,6 +50,14 @@ class PolydetEngine:
             self._xin = torch.zeros((batch, self.in_channels, height, width), device=self.device,
                                     dtype=torch.bfloat16 if dtype == "bf16" else torch.float32
                                     ).contiguous(memory_format=torch.channels_last)
+        # fused polydet_post_process (utils/post_process.py:105-112): frames are fed at network resolution, so the meta of
+        # base_detector.py:55-57 (fix_res) is c = (W/2, H/2), s = max(H, W), out = (W/4, H/4); the (B,2,3) inverse affine
+        # lives on the device and is read by the decode's gather kernel inside the captured graph
+        self.post_affine = None
+        if post_process:
+            c = [[width / 2.0, height / 2.0]] * batch
+            self.post_affine = torch.as_tensor(cpost.batch_inverse_affine(c, [float(max(height, width))] * batch, width // 4, height // 4),
+                                               dtype=torch.float64).to(self.device)
         self.stream = torch.cuda.Stream(self.device)
         self.copy_stream = torch.cuda.Stream(self.device)   # H2D
         self.d2h_stream = torch.cuda.Stream(self.device)    # D2H (separate, or it would serialise behind the next H2D)
@@ -78,9 +88,10 @@ class PolydetEngine:
             out = self.net(x)[-1]
             if self.optimize:   # the sigmoid of detectors/polydet.py:28 is fused into the decode kernel
                 return cdecode.polydet_decode_from_logits(out["hm"], out["poly"], out["pseudo_depth"], reg=out.get("reg"),
-                                                          K=self.K, rep=self.rep)
+                                                          K=self.K, rep=self.rep, post_affine=self.post_affine)
             hm = out["hm"].sigmoid_()
-            return cdecode.polydet_decode(hm, out["poly"], out["pseudo_depth"], reg=out.get("reg"), K=self.K, rep=self.rep)
+            return cdecode.polydet_decode(hm, out["poly"], out["pseudo_depth"], reg=out.get("reg"), K=self.K, rep=self.rep,
+                                          post_affine=self.post_affine)
 
     def _warm_and_capture(self):
         from .. import _lib

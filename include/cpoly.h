@@ -16,7 +16,8 @@
  *                           (Cout,Cin,kh,kw) so checkpoints (src/lib/models/model.py:31-130) are unaffected.
  *   cpoly_idaup_upsample_forward <- the depthwise `nn.ConvTranspose2d` `up_i` of IDAUp
  *                           (src/lib/models/networks/pose_dla_dcn.py:372-375,385) fused with the skip add of :387.
- *   cpoly_decode         <- `polydet_decode(heat, polys, depth, reg, cat_spec_poly, K, rep)`
+ *   cpoly_decode         <- `polydet_decode(heat, polys, depth, reg, cat_spec_poly, K, rep)`  [+ optionally the
+ *                           coordinate back-mapping of `polydet_post_process`, src/lib/utils/post_process.py:105-112]
  *                           src/lib/models/decode.py:512-670, i.e. `_nms` :13-19, `_topk` :117-133,
  *                           `_transpose_and_gather_feat` src/lib/models/utils.py:22-26, and (optionally, with
  *                           heat_is_logit=1) the `hm.sigmoid_()` of src/lib/detectors/polydet.py:28.
@@ -43,7 +44,7 @@
 extern "C" {
 #endif
 
-#define CPOLY_ABI_VERSION 2
+#define CPOLY_ABI_VERSION 3
 
 /* element types */
 #define CPOLY_F32 0
@@ -177,6 +178,13 @@ typedef struct {
   int64_t* out_inds;    /* optional (B,K) flat y*W+x of every detection, or NULL */
   void* workspace;      /* >= cpoly_decode_workspace_bytes(B,C,H,W,K), 256-byte aligned */
   size_t workspace_bytes;
+  /* Optional fused `polydet_post_process` back-mapping (src/lib/utils/post_process.py:105-112 calling
+   * `transform_preds` / `affine_transform`, src/lib/utils/image.py:19-24,63-66): (B,6) fp64 on the device, the
+   * row-major 2x3 inverse affine `get_affine_transform(c, s, 0, (out_w, out_h), inv=1)` of every image.  When
+   * given, the two bounding-box corners and all N vertices of every detection are written in ORIGINAL-image
+   * coordinates, x' = fp32(t00*x + t01*y + t02) evaluated in fp64 like the reference's np.dot; score, class and
+   * pseudo-depth are untouched.  NULL => feature-map coordinates, exactly `polydet_decode`. */
+  const double* post_affine;
 } cpoly_decode_args;
 
 size_t cpoly_decode_workspace_bytes(int32_t B, int32_t C, int32_t H, int32_t W, int32_t K);

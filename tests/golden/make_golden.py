@@ -8,6 +8,9 @@
   on the CPU — the stand-in BASELINE.json names for the missing DCNv2 submodule
   (/root/reference/.SUBMODULES.json:8-14).
 
+* post_*.npz   : inputs + outputs of the UNMODIFIED reference ``polydet_post_process``
+  (/root/reference/src/lib/utils/post_process.py:105-122) on the stored decode outputs.
+
 The fixtures are what travels to the GPU box; /root/reference does not.
 """
 import os
@@ -111,7 +114,53 @@ def make_dcn():
         print("dcn", name, tuple(y.shape))
 
 
+def make_post():
+    """post_*.npz: the UNMODIFIED reference ``polydet_post_process`` (src/lib/utils/post_process.py:105-122, which
+    calls ``transform_preds`` / ``get_affine_transform`` / ``affine_transform`` of src/lib/utils/image.py) applied to
+    the outputs of the reference decode stored in decode_*.npz, for the two (c, s) conventions of
+    src/lib/detectors/base_detector.py:55-63 (fix_res: scalar s; keep_res: s = [inp_w, inp_h])."""
+    if REF not in sys.path:
+        sys.path.insert(0, REF)
+    from utils.post_process import polydet_post_process  # the reference, unmodified
+    from utils.image import get_affine_transform
+
+    cases = [
+        # name, decode fixture, num_classes, original (h, w), fix_res, down_ratio
+        ("fixres_small", "decode_small_cart_reg", 3, (37, 91), True, 4),
+        ("keepres_small", "decode_small_polar_reg", 3, (45, 77), False, 4),
+        ("fixres_mid", "decode_mid_cart_reg", 8, (1024, 2048), True, 4),
+        ("keepres_mid", "decode_mid_polar_reg", 8, (125, 190), False, 4),
+    ]
+    for name, fix, ncls, (h, w), fix_res, down in cases:
+        d = np.load(os.path.join(HERE, fix + ".npz"))
+        dets = d["out"].astype(np.float32)
+        B = dets.shape[0]
+        fh, fw = d["heat"].shape[2:]
+        inp_h, inp_w = fh * down, fw * down
+        cs, ss = [], []
+        for i in range(B):   # detectors/base_detector.py:51-63 (scale 1); a different image size per batch entry
+            hh, ww = h + 3 * i, w + 5 * i
+            if fix_res:
+                cs.append(np.array([ww / 2., hh / 2.], dtype=np.float32))
+                ss.append(max(hh, ww) * 1.0)
+            else:
+                cs.append(np.array([ww // 2, hh // 2], dtype=np.float32))
+                ss.append(np.array([inp_w, inp_h], dtype=np.float32))
+        out_h, out_w = inp_h // down, inp_w // down
+        ret = polydet_post_process(dets.copy(), cs, ss, out_h, out_w, ncls)
+        trans = np.stack([get_affine_transform(cs[i], ss[i], 0, (out_w, out_h), inv=1) for i in range(B)])
+        blob = dict(dets=dets, c=np.stack(cs), s=np.stack([np.broadcast_to(np.asarray(x, dtype=np.float32), (2,)) for x in ss]),
+                    s_is_scalar=np.array(fix_res), out_h=np.array(out_h), out_w=np.array(out_w), num_classes=np.array(ncls), trans=trans)
+        for i in range(B):
+            for j in range(1, ncls + 1):
+                blob[f"ret_{i}_{j}"] = np.array(ret[i][j], dtype=np.float32).reshape(-1, dets.shape[2] - 1)
+        np.savez_compressed(os.path.join(HERE, f"post_{name}.npz"), **blob)
+        print("post", name, dets.shape, [len(ret[0][j]) for j in range(1, ncls + 1)])
+
+
 if __name__ == "__main__":
     torch.set_num_threads(4)
-    make_decode()
-    make_dcn()
+    if "--post-only" not in sys.argv:
+        make_decode()
+        make_dcn()
+    make_post()

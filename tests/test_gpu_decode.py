@@ -138,3 +138,37 @@ def test_decode_errors():
         cp.polydet_decode(z, torch.zeros(1, 8, 4, 4, device="cuda"), z[:, :1], K=100)  # K > H*W
     with pytest.raises(RuntimeError):
         cp.polydet_decode(z.cpu(), torch.zeros(1, 8, 4, 4), z[:, :1].cpu(), K=4)
+
+
+POST_GOLDEN = sorted(__import__("glob").glob(os.path.join(os.path.dirname(__file__), "golden", "post_*.npz")))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", POST_GOLDEN, ids=lambda p: os.path.basename(p)[:-4])
+def test_fused_post_process_vs_reference_golden(path):
+    """decode + fused back-mapping (cpoly_decode with post_affine) == reference polydet_decode followed by the
+    reference polydet_post_process (golden vectors of both, tests/golden/make_golden.py)."""
+    import centerpoly_b200 as cp
+    d = np.load(path)
+    src = {"post_fixres_small": "decode_small_cart_reg", "post_keepres_small": "decode_small_polar_reg",
+           "post_fixres_mid": "decode_mid_cart_reg", "post_keepres_mid": "decode_mid_polar_reg"}[os.path.basename(path)[:-4]]
+    g = np.load(os.path.join(os.path.dirname(path), src + ".npz"))
+    B = d["dets"].shape[0]
+    c = [d["c"][i] for i in range(B)]
+    s = [float(d["s"][i][0]) if bool(d["s_is_scalar"]) else d["s"][i] for i in range(B)]
+    h, w, nc = int(d["out_h"]), int(d["out_w"]), int(d["num_classes"])
+    trans = cp.batch_inverse_affine(c, s, w, h)
+    t = lambda k: torch.from_numpy(g[k]).cuda()
+    out = cp.polydet_decode(t("heat"), t("polys"), t("depth"), reg=t("reg"), K=int(g["K"]), rep=str(g["rep"]), post_affine=trans)
+    ret = cp.group_by_class(out.cpu().numpy(), nc)
+    D = d["dets"].shape[2] - 1
+    for i in range(B):
+        for j in range(1, nc + 1):
+            got = np.array(ret[i][j], dtype=np.float32).reshape(-1, D)
+            want = d[f"ret_{i}_{j}"]
+            assert got.shape == want.shape
+            assert np.array_equal(got[:, 4], want[:, 4]) and np.array_equal(got[:, -1], want[:, -1])   # score, depth
+            np.testing.assert_allclose(got, want, rtol=2e-6, atol=0)   # polar vertices: <= 1 ulp of cos/sin, then the affine
+    # and without the affine the call is still the plain decode
+    plain = cp.polydet_decode(t("heat"), t("polys"), t("depth"), reg=t("reg"), K=int(g["K"]), rep=str(g["rep"]))
+    np.testing.assert_allclose(plain.cpu().numpy(), g["out"], rtol=2e-6, atol=0)
