@@ -157,34 +157,40 @@ __global__ void __maxnreg__(80) dcn_wgrad_tc_kernel(const WgradParams p) {
     }
   } else if (warp == 5) {
     // =========================================================================== MMA issuer
-    if (lane == 0) {
+    // (whole warp walks the loops, one elected lane issues: see elect_one() in tc_common.cuh)
+    {
       const uint32_t idesc = umma_idesc(kTF32, 128, kChunk, /*a_mn_major=*/true, /*b_mn_major=*/true);
       const int atoms_per_half = 128 * (int)sizeof(T) / ROW_BYTES;   // 128 output channels = 2 bf16 / 4 tf32 atoms
       RingCursor rb, ra;
       for (int tile = tile0; tile < tile1; ++tile) {
-        mbar_wait(bar_fullG + 8 * ra.s, ra.ph, 100);
+        mbar_wait(bar_fullG + 8 * ra.s, ra.ph, 32);
         const uint32_t abuf = abuf0 + ra.s * a_bytes;
         for (int blk = blk0; blk < blk1; ++blk) {
-          mbar_wait(bar_fullB + 8 * rb.s, rb.ph, 100);
+          mbar_wait(bar_fullB + 8 * rb.s, rb.ph, 32);
           tc_fence_after();
           const uint32_t bst = bstage0 + rb.s * ATOM_BYTES;
-          for (int mhalf = 0; mhalf < p.mh; ++mhalf) {
-            const uint32_t d_tmem = tmem_base + (uint32_t)(((blk - blk0) * p.mh + mhalf) * kChunk);
-            const uint32_t a_addr = abuf + (uint32_t)(mhalf * atoms_per_half) * ATOM_BYTES;
-#pragma unroll 4
-            for (int kk = 0; kk < TILE_PX / kInstrK; ++kk) {
-              const uint64_t adesc = umma_desc_sw128(a_addr + kk * kInstrK * ROW_BYTES, ATOM_BYTES, 1024);
-              const uint64_t bdesc = umma_desc_sw128(bst + kk * kInstrK * ROW_BYTES, ATOM_BYTES, 1024);
-              umma<kTF32>(d_tmem, adesc, bdesc, idesc, (tile > tile0 || kk > 0) ? 1u : 0u);
+          if (elect_one()) {
+            for (int mhalf = 0; mhalf < p.mh; ++mhalf) {
+              const uint32_t d_tmem = tmem_base + (uint32_t)(((blk - blk0) * p.mh + mhalf) * kChunk);
+              const uint64_t adesc0 = umma_desc_sw128(abuf + (uint32_t)(mhalf * atoms_per_half) * ATOM_BYTES, ATOM_BYTES, 1024);
+              const uint64_t bdesc0 = umma_desc_sw128(bst, ATOM_BYTES, 1024);
+#pragma unroll
+              for (int kk = 0; kk < TILE_PX / kInstrK; ++kk) {   // the start address advances by whole 128-byte rows
+                const uint64_t step = (uint64_t)((kk * kInstrK * ROW_BYTES) >> 4);
+                umma<kTF32>(d_tmem, adesc0 + step, bdesc0 + step, idesc, (tile > tile0 || kk > 0) ? 1u : 0u);
+              }
+            }
+            umma_commit(bar_emptyB + 8 * rb.s);
+            if (blk == blk1 - 1) {
+              umma_commit(bar_emptyG + 8 * ra.s);
+              if (tile == tile1 - 1) umma_commit(bar_done);
             }
           }
-          umma_commit(bar_emptyB + 8 * rb.s);
+          __syncwarp();
           rb.advance((uint32_t)p.b_stages);
         }
-        umma_commit(bar_emptyG + 8 * ra.s);
         ra.advance((uint32_t)p.a_bufs);
       }
-      umma_commit(bar_done);
     }
   } else if (warp < EPI_WARPS) {
     // =========================================================================== epilogue: TMEM -> fp32 partial
@@ -594,31 +600,35 @@ __global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
     }
   } else if (warp == 5) {
     // =========================================================================== MMA issuer
-    if (lane == 0) {
+    // (whole warp walks the loops, one elected lane issues)
+    {
       const uint32_t idesc = umma_idesc(kTF32, TILE_PX, kChunk);
       RingCursor ra;
       uint32_t nblk = 0;
       for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
-        mbar_wait(bar_fullG + 8 * ra.s, ra.ph, 100);
+        mbar_wait(bar_fullG + 8 * ra.s, ra.ph, 32);
         const uint32_t abuf = abuf0 + ra.s * a_bytes;
         for (int q = 0; q < blocks_per_item; ++q, ++nblk) {
           const uint32_t d = nblk & 1u, dph = (nblk >> 1) & 1u;
-          mbar_wait(bar_Wfull + 8 * d, dph, 50);
-          mbar_wait(bar_Dempty + 8 * d, dph ^ 1u, 50);
+          mbar_wait(bar_Wfull + 8 * d, dph, 32);
+          mbar_wait(bar_Dempty + 8 * d, dph ^ 1u, 32);
           tc_fence_after();
           const uint32_t wst = wst0 + d * (uint32_t)p.w_stage_bytes;
           const uint32_t d_tmem = tmem_base + d * (uint32_t)kChunk;
-          for (int ka = 0; ka < p.k_atoms; ++ka) {
-            const uint64_t adesc = umma_desc_sw128(abuf + (uint32_t)ka * ATOM_BYTES);
-            const uint64_t bdesc = umma_desc_sw128(wst + (uint32_t)ka * (uint32_t)(kChunk * ROW_BYTES));
+          if (elect_one()) {
+            for (int ka = 0; ka < p.k_atoms; ++ka) {
+              const uint64_t adesc = umma_desc_sw128(abuf + (uint32_t)ka * ATOM_BYTES);
+              const uint64_t bdesc = umma_desc_sw128(wst + (uint32_t)ka * (uint32_t)(kChunk * ROW_BYTES));
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk)
-              umma<kTF32>(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (ka | kk) != 0 ? 1u : 0u);
+              for (int kk = 0; kk < 4; ++kk)
+                umma<kTF32>(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (ka | kk) != 0 ? 1u : 0u);
+            }
+            umma_commit(bar_Wempty + 8 * d);
+            umma_commit(bar_Dfull + 8 * d);
+            if (q == blocks_per_item - 1) umma_commit(bar_emptyG + 8 * ra.s);
           }
-          umma_commit(bar_Wempty + 8 * d);
-          umma_commit(bar_Dfull + 8 * d);
+          __syncwarp();
         }
-        umma_commit(bar_emptyG + 8 * ra.s);
         ra.advance((uint32_t)p.a_bufs);
       }
     }
