@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import POINTER, Structure, c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
+from ctypes import POINTER, Structure, c_char_p, c_double, c_float, c_int32, c_int64, c_size_t, c_uint32, c_void_p
 
 import torch
 
@@ -23,6 +23,7 @@ EXPORTED_SYMBOLS = (
     "cpoly_dcn_packed_weight_bytes", "cpoly_dcn_pack_weights", "cpoly_dcn_forward_workspace_bytes", "cpoly_dcn_forward",
     "cpoly_idaup_upsample_forward",
     "cpoly_dcn_backward_workspace_bytes", "cpoly_dcn_backward", "cpoly_decode_workspace_bytes", "cpoly_decode",
+    "cpoly_rasterise_workspace_bytes", "cpoly_rasterise",
 )
 
 
@@ -58,9 +59,17 @@ class DecodeArgs(Structure):
         ("post_affine", c_void_p)]
 
 
+class RasterArgs(Structure):
+    _fields_ = [(n, c_int32) for n in ("B", "K", "N", "W", "H")] + [
+        ("thresh", c_double), ("occluder_score", c_double), ("min_area", c_int32), ("skip_classes", c_uint32),
+        ("dets", c_void_p), ("order", c_void_p), ("count", c_void_p), ("verts", c_void_p), ("area", c_void_p),
+        ("keep", c_void_p), ("conf", c_void_p), ("status", c_void_p), ("masks", c_void_p),
+        ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+
+
 _lib = None
 # kernels launched by the shims since import (our kernels only; bench.py reports it as gpu_launches)
-LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "decode": 0}
+LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "decode": 0, "rasterise": 0}
 
 
 def lib():
@@ -95,7 +104,11 @@ def lib():
         L.cpoly_decode_workspace_bytes.argtypes = [c_int32] * 5
         L.cpoly_decode.restype = c_int32
         L.cpoly_decode.argtypes = [POINTER(DecodeArgs), c_void_p]
-        if L.cpoly_abi_version() != 3:
+        L.cpoly_rasterise_workspace_bytes.restype = c_size_t
+        L.cpoly_rasterise_workspace_bytes.argtypes = [c_int32] * 2
+        L.cpoly_rasterise.restype = c_int32
+        L.cpoly_rasterise.argtypes = [POINTER(RasterArgs), c_void_p]
+        if L.cpoly_abi_version() != 4:
             raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
         _lib = L
     return _lib

@@ -163,6 +163,24 @@ int cpoly_decode(const cpoly_decode_args* a, cpoly_stream_t stream) {
   return decode_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+size_t cpoly_rasterise_workspace_bytes(int32_t B, int32_t K) {
+  if (B <= 0 || K <= 0) return 256;
+  return raster_workspace_bytes(B, K);
+}
+
+int cpoly_rasterise(const cpoly_raster_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->K >= 1 && a->K <= 256, CPOLY_EINVAL, "K must be in [1, 256], got %d", a->K);
+  CPOLY_REQUIRE(a->N >= 3 && a->N <= 64, CPOLY_EINVAL, "N (vertices) must be in [3, 64], got %d", a->N);
+  CPOLY_REQUIRE(a->W >= 1 && a->W <= 8192 && a->H >= 1 && a->H <= 8192, CPOLY_EINVAL, "mask size must be in [1, 8192]^2, got %dx%d", a->W, a->H);
+  CPOLY_REQUIRE(a->dets && a->order && a->count && a->verts && a->area && a->keep && a->conf && a->status, CPOLY_EINVAL, "NULL pointer");
+  CPOLY_REQUIRE((reinterpret_cast<uintptr_t>(a->verts) & 3) == 0 && (reinterpret_cast<uintptr_t>(a->masks) & 7) == 0 &&
+                (reinterpret_cast<uintptr_t>(a->workspace) & 15) == 0, CPOLY_EINVAL, "verts / masks / workspace must be 4 / 8 / 16-byte aligned");
+  if (a->B == 0) return CPOLY_OK;
+  CPOLY_REQUIRE(a->workspace && a->workspace_bytes >= raster_workspace_bytes(a->B, a->K), CPOLY_EWORKSPACE, "raster workspace too small");
+  return raster_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int cpoly_idaup_upsample_forward(const cpoly_upsample_args* a, cpoly_stream_t stream) {
   CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
   CPOLY_REQUIRE(a->B >= 0 && a->C > 0 && a->H > 0 && a->W > 0 && a->f >= 1, CPOLY_EINVAL, "bad upsample dims");

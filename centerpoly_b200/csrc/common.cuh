@@ -133,4 +133,6 @@ int dcn_dgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_
 int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream);
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K);
 int decode_launch(const cpoly_decode_args& a, cudaStream_t stream);
+size_t raster_workspace_bytes(int B, int K);
+int raster_launch(const cpoly_raster_args& a, cudaStream_t stream);
 }  // namespace cpoly

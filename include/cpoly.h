@@ -21,6 +21,8 @@
  *                           src/lib/models/decode.py:512-670, i.e. `_nms` :13-19, `_topk` :117-133,
  *                           `_transpose_and_gather_feat` src/lib/models/utils.py:22-26, and (optionally, with
  *                           heat_is_logit=1) the `hm.sigmoid_()` of src/lib/detectors/polydet.py:28.
+ *   cpoly_rasterise      <- the mask construction inside `format_and_write_to_cityscapes`,
+ *                           src/lib/datasets/dataset/cityscapes.py:226-279 (PIL ImageDraw + `bresenham` + numpy).
  *
  * Ownership: the caller allocates every input, output and workspace in device memory and passes raw
  * device pointers; the library allocates nothing, keeps no global state and never synchronises the
@@ -44,7 +46,7 @@
 extern "C" {
 #endif
 
-#define CPOLY_ABI_VERSION 3
+#define CPOLY_ABI_VERSION 4
 
 /* element types */
 #define CPOLY_F32 0
@@ -189,6 +191,43 @@ typedef struct {
 
 size_t cpoly_decode_workspace_bytes(int32_t B, int32_t C, int32_t H, int32_t W, int32_t K);
 int cpoly_decode(const cpoly_decode_args* args, cpoly_stream_t stream);
+
+/* --------------------------------------------------------------------------- instance rasterisation */
+
+/* Depth-ordered rasterisation of the decoded polygons into per-instance masks: the compute half of
+ * `Cityscapes.format_and_write_to_cityscapes` (src/lib/datasets/dataset/cityscapes.py:226-279), i.e. what that
+ * function does between reading `all_bboxes` and writing the PNG / txt files:
+ *   - keep detections with score > thresh (:228), round the vertices to 2 decimals and truncate (:120-121,231-232), stable sort by
+ *     pseudo-depth, ties in (class, detection index) order like the reference's per-class dict walk (:239);
+ *   - mask = PIL polygon fill  U  radius-2 discs on every point of the Bresenham contour (:253-264) - evaluated
+ *     per pixel in closed form (even-odd crossing count on pixel centres U distance test against the exact
+ *     Bresenham steps), no scan conversion;
+ *   - remove what nearer instances with score >= occluder_score already cover (:265-271);
+ *   - keep = class is drawn && count_nonzero(mask) > min_area (:273), confidence = min(1, 1.2*score) (:277).
+ * Bit-exact to the reference's PIL result when every truncated vertex lies in [-8192, 8191] (vertices outside
+ * are clamped and counted in `status[b]`); W, H <= 8192; K <= 256; N <= 64. */
+typedef struct {
+  int32_t B, K, N;        /* dets is (B,K,2N+7) fp32 as written by cpoly_decode (with post_affine): box4, score, class, 2N, depth */
+  int32_t W, H;           /* mask size = original image size (2048 x 1024 for Cityscapes) */
+  double thresh;          /* opt.thresh, compared in fp64 like the reference's Python float */
+  double occluder_score;  /* 0.5 */
+  int32_t min_area;       /* 100 */
+  uint32_t skip_classes;  /* bit c set => 0-based class c is never drawn (the reference's pole / traffic sign / traffic light) */
+  const float* dets;
+  int32_t* order;         /* (B,K)  slot -> detection index, nearest first; slots >= count[b] are -1 */
+  int32_t* count;         /* (B)    instances with score > thresh */
+  int16_t* verts;         /* (B,K,N,2) truncated vertices per slot */
+  int32_t* area;          /* (B,K)  visible pixels per slot */
+  uint8_t* keep;          /* (B,K)  1 => the reference would write this instance */
+  double* conf;           /* (B,K)  min(1, 1.2*score) */
+  int32_t* status;        /* (B)    vertices that had to be clamped (0 => exact) */
+  uint8_t* masks;         /* (B,K,H,W) 0 / 255, slots >= count[b] untouched; NULL => areas / keep only */
+  void* workspace;        /* >= cpoly_rasterise_workspace_bytes(B,K) */
+  size_t workspace_bytes;
+} cpoly_raster_args;
+
+size_t cpoly_rasterise_workspace_bytes(int32_t B, int32_t K);
+int cpoly_rasterise(const cpoly_raster_args* args, cpoly_stream_t stream);
 
 #ifdef __cplusplus
 }
