@@ -7,10 +7,12 @@
 //   covered(p)  =  even-odd crossing count of the ray p -> +x over the integer polygon (pixel centres)
 //               OR  p within the 21-pixel disc (5x5 minus corners = PIL's radius-2 ellipse) of a Bresenham step,
 //                   the step's minor coordinate being floor((2*dmin*k + dmaj) / (2*dmaj)) for major step k.
-// Both were checked exhaustively against PIL (tests/test_oracle_raster.py).  One thread owns PX=8 horizontally
+// Both were checked against PIL on random polygons (tests/test_oracle_raster.py).  One thread owns PX=8 horizontally
 // adjacent pixels and walks the instances nearest-first, carrying the 8 "already removed" bits in a register, so
 // the occlusion rule costs nothing and the only HBM traffic is the (B,K,H,W) byte masks, written once with 8-byte
-// stores (a warp writes 256 contiguous bytes per instance).  HBM-write bound: count*H*W bytes per image.
+// stores (a warp writes 256 contiguous bytes per instance).  Algorithmic bytes: count*H*W per image (HBM writes).
+// Measured (tools/raster_bench.py, profiles/r01l_*): 58-63 % of the HBM peak on a batch of 8 frames; a single frame
+// (one wave of CTAs) is bound by the serial instruction chain of the warps that own the most crowded row segments.
 #include <limits.h>
 #include <stdlib.h>
 
@@ -206,7 +208,7 @@ __global__ void __launch_bounds__(32 * TILE_H) raster_cover_kernel(const RasterP
   int4* s_bbox = reinterpret_cast<int4*>(smem_raw);                      // K dilated boxes (.x > .z when not drawn)
   uint32_t* s_occ = reinterpret_cast<uint32_t*>(s_bbox + p.K);           // K occluder flags
   uint32_t* sv = s_occ + p.K;                                            // n * N packed vertices
-  const int tx0 = blockIdx.x * TILE_W, ty0 = blockIdx.y * TILE_H;
+  const int tx0 = blockIdx.x * TILE_W;
   const size_t base = (size_t)b * p.K;
   const uint32_t* gv = reinterpret_cast<const uint32_t*>(p.verts) + base * p.N;
   for (int t = threadIdx.x; t < n * p.N; t += blockDim.x) sv[t] = gv[t];
@@ -216,43 +218,57 @@ __global__ void __launch_bounds__(32 * TILE_H) raster_cover_kernel(const RasterP
     s_occ[s] = (fl & FLAG_OCCLUDER) ? 1u : 0u;
   }
   __syncthreads();
-  const int lane = threadIdx.x & 31, Y = ty0 + (threadIdx.x >> 5), X0 = tx0 + lane * PX;
+  // the CTA's 8 rows are spread over the image (stride gridDim.y) so that every CTA gets the same mix of crowded
+  // and empty regions: with one wave of CTAs the kernel ends when the slowest one does
+  const int lane = threadIdx.x & 31, Y = blockIdx.y + (threadIdx.x >> 5) * gridDim.y, X0 = tx0 + lane * PX;
   if (Y >= p.H) return;
-  constexpr uint32_t ALL = PX == 32 ? 0xffffffffu : (1u << PX) - 1u;
+  constexpr uint32_t ALL = (1u << PX) - 1u;
   const uint32_t vm = X0 >= p.W ? 0u : (X0 + PX <= p.W ? ALL : (1u << (p.W - X0)) - 1u);
-  const bool vec = (p.W % PX == 0) && vm;
+  // 0: no masks wanted, 1: one aligned PX-byte store per instance, 2: ragged width, byte stores
+  const int mode = !p.masks ? 0 : ((p.W % PX == 0) ? (vm ? 1 : 0) : 2);
   uint8_t* out = p.masks ? p.masks + ((base * p.H + Y) * (size_t)p.W + X0) : nullptr;
   const size_t plane = (size_t)p.H * p.W;
-  uint32_t removed = 0u, hit = 0u, occ = 0u;
-  for (int s = 0; s < n; ++s, out += (out ? plane : 0)) {
-    if ((s & 31) == 0) {   // which of the next 32 instances touch this row segment
-      const int s2 = s + lane;
-      bool h = false, o = false;
-      if (s2 < n) {
-        const int4 bb = s_bbox[s2];
-        h = bb.x <= bb.z && bb.x <= tx0 + TILE_W - 1 && bb.z >= tx0 && bb.y <= Y && bb.w >= Y;
-        o = s_occ[s2] != 0u;
+  uint32_t removed = 0u;
+  for (int g = 0; g < n; g += 32) {
+    // which of the next 32 instances touch this row segment (lane j looks at instance g + j)
+    bool h = false, o = false;
+    if (g + lane < n) {
+      const int4 bb = s_bbox[g + lane];
+      h = bb.x <= bb.z && bb.x <= tx0 + TILE_W - 1 && bb.z >= tx0 && bb.y <= Y && bb.w >= Y;
+      o = s_occ[g + lane] != 0u;
+    }
+    const uint32_t hit = __ballot_sync(FULL, h), occ = __ballot_sync(FULL, o);
+    const int cnt = min(32, n - g);
+    if (mode == 1 && hit == 0u) {   // nothing here: a run of zero stores
+#pragma unroll 4
+      for (int j = 0; j < cnt; ++j, out += plane) {
+        if (PX == 8) __stcs(reinterpret_cast<uint2*>(out), make_uint2(0u, 0u));
+        else __stcs(reinterpret_cast<uint4*>(out), make_uint4(0u, 0u, 0u, 0u));
       }
-      hit = __ballot_sync(FULL, h); occ = __ballot_sync(FULL, o);
+      continue;
     }
-    uint32_t m = 0u;
-    if ((hit >> (s & 31)) & 1u) {
-      m = cover_bits<PX>(sv + s * p.N, p.N, X0, Y, lane, tx0) & ~removed & vm;
-      if ((occ >> (s & 31)) & 1u) removed |= m;
-      const int c = __reduce_add_sync(FULL, __popc(m));
-      if (lane == 0 && c) atomicAdd(p.area + base + s, c);
-    }
-    if (out) {
-      if (vec) {
+    for (int j = 0; j < cnt; ++j) {
+      uint32_t m = 0u;
+      if ((hit >> j) & 1u) {
+        const int s = g + j;
+        m = cover_bits<PX>(sv + s * p.N, p.N, X0, Y, lane, tx0) & ~removed & vm;
+        if ((occ >> j) & 1u) removed |= m;
+        const int c = __reduce_add_sync(FULL, __popc(m));
+        if (lane == 0 && c) atomicAdd(p.area + base + s, c);
+      }
+      if (mode == 1) {
         if (PX == 8) {
-          __stcs(reinterpret_cast<uint2*>(out), make_uint2(bits_to_bytes(m & 15u), bits_to_bytes(m >> 4)));
+          __stcs(reinterpret_cast<uint2*>(out), m ? make_uint2(bits_to_bytes(m & 15u), bits_to_bytes(m >> 4)) : make_uint2(0u, 0u));
         } else {
-          __stcs(reinterpret_cast<uint4*>(out), make_uint4(bits_to_bytes(m & 15u), bits_to_bytes((m >> 4) & 15u),
-                                                           bits_to_bytes((m >> 8) & 15u), bits_to_bytes(m >> 12)));
+          __stcs(reinterpret_cast<uint4*>(out), m ? make_uint4(bits_to_bytes(m & 15u), bits_to_bytes((m >> 4) & 15u),
+                                                              bits_to_bytes((m >> 8) & 15u), bits_to_bytes(m >> 12))
+                                                  : make_uint4(0u, 0u, 0u, 0u));
         }
-      } else {
-        for (int j = 0; j < PX; ++j)
-          if ((vm >> j) & 1u) out[j] = ((m >> j) & 1u) ? 255 : 0;
+        out += plane;
+      } else if (mode == 2) {
+        for (int k = 0; k < PX; ++k)
+          if ((vm >> k) & 1u) out[k] = ((m >> k) & 1u) ? 255 : 0;
+        out += plane;
       }
     }
   }
