@@ -7,12 +7,12 @@
 //   covered(p)  =  even-odd crossing count of the ray p -> +x over the integer polygon (pixel centres)
 //               OR  p within the 21-pixel disc (5x5 minus corners = PIL's radius-2 ellipse) of a Bresenham step,
 //                   the step's minor coordinate being floor((2*dmin*k + dmaj) / (2*dmaj)) for major step k.
-// Both were checked against PIL on random polygons (tests/test_oracle_raster.py).  One thread owns PX=8 horizontally
-// adjacent pixels and walks the instances nearest-first, carrying the 8 "already removed" bits in a register, so
-// the occlusion rule costs nothing and the only HBM traffic is the (B,K,H,W) byte masks, written once with 8-byte
-// stores (a warp writes 256 contiguous bytes per instance).  Algorithmic bytes: count*H*W per image (HBM writes).
-// Measured (tools/raster_bench.py, profiles/r01l_*): 58-63 % of the HBM peak on a batch of 8 frames; a single frame
-// (one wave of CTAs) is bound by the serial instruction chain of the warps that own the most crowded row segments.
+// Both were checked against PIL on random polygons (tests/test_oracle_raster.py).  One thread owns PX = 16 (or 8)
+// horizontally adjacent pixels and walks the instances nearest-first, carrying the "already removed" bits in a
+// register, so the occlusion rule costs nothing and the only HBM traffic is the (B,K,H,W) byte masks, written once
+// with 16-byte stores (a warp writes 512 contiguous bytes per instance).  Algorithmic bytes: count*H*W per image.
+// Measured (tools/raster_bench.py, profiles/r01l_*): 86 % of the measured HBM peak on a batch of 8 Cityscapes frames,
+// 46 % on a single frame (one wave; launch + prep + keep are ~10 of its 68 us).
 #include <limits.h>
 #include <stdlib.h>
 
@@ -21,7 +21,7 @@
 namespace cpoly {
 namespace {
 
-constexpr int TILE_H = 8;         // 8 warps per CTA
+constexpr int TILE_H = 4;         // warps (= rows in flight) per CTA
 constexpr int VCLAMP = 8192;      // vertices are clamped to [-VCLAMP, VCLAMP-1] so every product below fits in 32 bits
 constexpr int FLAG_DRAWN = 1, FLAG_OCCLUDER = 2;
 
@@ -41,6 +41,8 @@ struct RasterParams {
   uint8_t* masks;
   int4* bbox;      // workspace: dilated integer bounding box per slot (empty when the class is not drawn)
   int32_t* flags;  // workspace
+  int32_t* clamped;  // workspace: clamped vertices per slot
+  int rows_per_warp;
 };
 
 // int(float("{:.2f}".format(x))) of cityscapes.py:120-121,231-232: decimal rounding to two places, then truncation.
@@ -55,60 +57,75 @@ __device__ __forceinline__ int round2_trunc(float x) {
 }
 
 // ---- 1. filter, depth sort, vertex truncation ------------------------------------------------------------------
-// One CTA per image, one thread per detection.  Rank sort on (depth, class, index): Python's sorted() is stable and
-// the reference builds its list class by class (cityscapes.py:226-239), so equal depths keep (class, index) order.
-__global__ void __launch_bounds__(256) raster_prep_kernel(const RasterParams p) {
+// Grid (B, ceil(K/8)), one WARP per detection (a single thread per detection walked its 2N strided vertex loads one
+// DRAM round trip at a time: 30 us).  Every CTA reads the K (score, class, depth) triples of its image; the warp of
+// detection i rank-sorts i on (depth, class, index) - Python's sorted() is stable and the reference builds its list
+// class by class (cityscapes.py:226-239), so equal depths keep (class, index) order - and writes slot `rank`.
+constexpr int PREP_WARPS = 8;
+__global__ void __launch_bounds__(32 * PREP_WARPS) raster_prep_kernel(const RasterParams p) {
+  constexpr uint32_t FULL = 0xffffffffu;
   __shared__ float s_depth[256];
   __shared__ int s_cls[256];
   __shared__ uint8_t s_valid[256];
-  __shared__ int s_clamped;
-  const int b = blockIdx.x, i = threadIdx.x;
+  const int b = blockIdx.x, t = threadIdx.x, lane = t & 31;
   const int row_len = 2 * p.N + 7;
-  const float* row = p.dets + ((size_t)b * p.K + (i < p.K ? i : 0)) * row_len;
-  const float score = row[4];
-  const bool valid = i < p.K && (double)score > p.thresh;
-  float depth = row[row_len - 1];
-  if (depth != depth) depth = __int_as_float(0x7f800000);   // NaN sorts last
-  const int cls = (int)row[5];
-  s_depth[i] = depth; s_cls[i] = cls; s_valid[i] = valid;
-  if (i == 0) s_clamped = 0;
-  const int n = __syncthreads_count(valid);
+  const float* __restrict__ img = p.dets + (size_t)b * p.K * row_len;
+  bool tv = false;
+  if (t < p.K) {
+    const float* row = img + (size_t)t * row_len;
+    float depth = row[row_len - 1];
+    if (depth != depth) depth = __int_as_float(0x7f800000);   // NaN sorts last
+    tv = (double)row[4] > p.thresh;
+    s_depth[t] = depth; s_cls[t] = (int)row[5]; s_valid[t] = tv;
+  }
+  const int n = __syncthreads_count(tv);
   const size_t base = (size_t)b * p.K;
-  if (valid) {
-    int rank = 0;
-    for (int j = 0; j < p.K; ++j) {
-      if (!s_valid[j]) continue;
-      const float dj = s_depth[j];
-      const int cj = s_cls[j];
-      rank += (dj < depth) || (dj == depth && (cj < cls || (cj == cls && j < i)));
+  if (blockIdx.y == 0) {   // per-image bookkeeping and the unused slots
+    if (t == 0) p.count[b] = n;
+    if (t < p.K) {
+      p.area[base + t] = 0;
+      if (t >= n) {
+        p.order[base + t] = -1; p.conf[base + t] = 0.0; p.flags[base + t] = 0; p.bbox[base + t] = make_int4(1, 1, 0, 0);
+        p.clamped[base + t] = 0;
+        uint32_t* v = reinterpret_cast<uint32_t*>(p.verts) + (base + t) * p.N;
+        for (int k = 0; k < p.N; ++k) v[k] = 0u;
+      }
     }
+  }
+  const int i = blockIdx.y * PREP_WARPS + (t >> 5);
+  if (i >= p.K || !s_valid[i]) return;
+  const float depth = s_depth[i];
+  const int cls = s_cls[i];
+  int rank = 0;
+  for (int j = lane; j < p.K; j += 32) {
+    const float dj = s_depth[j];
+    const int cj = s_cls[j];
+    rank += s_valid[j] && ((dj < depth) || (dj == depth && (cj < cls || (cj == cls && j < i))));
+  }
+  rank = __reduce_add_sync(FULL, rank);
+  const float* row = img + (size_t)i * row_len;
+  int xmin = INT_MAX, xmax = INT_MIN, ymin = INT_MAX, ymax = INT_MIN, clamped = 0;
+  uint32_t* v = reinterpret_cast<uint32_t*>(p.verts) + (base + rank) * p.N;
+  for (int k = lane; k < p.N; k += 32) {
+    const int x = round2_trunc(row[6 + 2 * k]), y = round2_trunc(row[7 + 2 * k]);
+    const int cx = min(max(x, -VCLAMP), VCLAMP - 1), cy = min(max(y, -VCLAMP), VCLAMP - 1);
+    clamped += (cx != x) + (cy != y);
+    v[k] = ((uint32_t)cx & 0xffffu) | ((uint32_t)cy << 16);
+    xmin = min(xmin, cx); xmax = max(xmax, cx); ymin = min(ymin, cy); ymax = max(ymax, cy);
+  }
+  xmin = __reduce_min_sync(FULL, xmin); xmax = __reduce_max_sync(FULL, xmax);
+  ymin = __reduce_min_sync(FULL, ymin); ymax = __reduce_max_sync(FULL, ymax);
+  clamped = __reduce_add_sync(FULL, clamped);
+  if (lane == 0) {
+    const float score = row[4];
     const bool drawn = cls < 0 || cls > 31 || !((p.skip_classes >> cls) & 1u);
-    int xmin = INT_MAX, xmax = INT_MIN, ymin = INT_MAX, ymax = INT_MIN, clamped = 0;
-    int16_t* v = p.verts + (base + rank) * p.N * 2;
-    for (int k = 0; k < p.N; ++k) {
-      const int x = round2_trunc(row[6 + 2 * k]), y = round2_trunc(row[7 + 2 * k]);
-      const int cx = min(max(x, -VCLAMP), VCLAMP - 1), cy = min(max(y, -VCLAMP), VCLAMP - 1);
-      clamped += (cx != x) + (cy != y);
-      v[2 * k] = (int16_t)cx; v[2 * k + 1] = (int16_t)cy;
-      xmin = min(xmin, cx); xmax = max(xmax, cx); ymin = min(ymin, cy); ymax = max(ymax, cy);
-    }
-    if (clamped) atomicAdd(&s_clamped, clamped);
     p.order[base + rank] = i;
     p.bbox[base + rank] = drawn ? make_int4(xmin - 2, ymin - 2, xmax + 2, ymax + 2) : make_int4(1, 1, 0, 0);
     p.flags[base + rank] = (drawn ? FLAG_DRAWN : 0) | ((double)score >= p.occluder_score ? FLAG_OCCLUDER : 0);
+    p.clamped[base + rank] = clamped;
     const double c = (double)score * 1.2;
     p.conf[base + rank] = c < 1.0 ? c : 1.0;
   }
-  if (i < p.K) {
-    p.area[base + i] = 0;
-    if (i >= n) {
-      p.order[base + i] = -1; p.conf[base + i] = 0.0; p.flags[base + i] = 0; p.bbox[base + i] = make_int4(1, 1, 0, 0);
-      int16_t* v = p.verts + (base + i) * p.N * 2;
-      for (int k = 0; k < 2 * p.N; ++k) v[k] = 0;
-    }
-  }
-  __syncthreads();
-  if (i == 0) { p.count[b] = n; p.status[b] = s_clamped; }
 }
 
 // ---- 2. per-pixel coverage ---------------------------------------------------------------------------------------
@@ -122,39 +139,60 @@ __device__ __forceinline__ uint32_t span_bits(int lo, int hi) {   // bits lo..hi
   return ((2u << hi) - 1u) & ~((1u << lo) - 1u);
 }
 
-// discs around the Bresenham steps of edge (x0,y0)->(x1,y1) (walked in that direction, as the reference does)
-template <int PX>
-__device__ __forceinline__ uint32_t near_bits(int x0, int y0, int x1, int y1, int X0, int Y) {
-  const int exmin = min(x0, x1), exmax = max(x0, x1), eymin = min(y0, y1), eymax = max(y0, y1);
-  if (X0 + PX - 1 < exmin - 2 || X0 > exmax + 2) return 0u;
-  uint32_t near = 0u;
-  const int adx = exmax - exmin, ady = eymax - eymin;
+// floor(a / b) for b > 0 when the quotient is known to be small (|q| < 2^16): one approximate fp32 division and a
+// +-1 fix-up instead of the ~25-instruction integer division sequence
+__device__ __forceinline__ int floor_div(int a, int b) {
+  int q = __float2int_rd(__fdividef((float)a, (float)b));
+  const int r = a - q * b;
+  if (r < 0) --q; else if (r >= b) ++q;
+  return q;
+}
+__device__ __forceinline__ int ceil_div(int a, int b) { return -floor_div(-a, b); }
+
+// Steps k in [0, adx] of an x-major edge whose row offset m(k) = floor((2*ady*k + adx) / (2*adx)) lies in [ta, tb]
+// (m is non-decreasing and moves by at most 1 per step).  Empty => lo > hi.
+__device__ __forceinline__ void step_range(int adx, int ady, int ta, int tb, int& lo, int& hi) {
+  ta = max(ta, 0); tb = min(tb, ady);   // 0 <= m(k) <= ady: keeps the quotients below within [0, adx + 1]
+  lo = 1; hi = 0;
+  if (tb < ta) return;
+  if (ady == 0) { if (ta == 0) { lo = 0; hi = adx; } return; }
+  lo = max(0, ceil_div(2 * adx * ta - adx, 2 * ady));
+  hi = min(adx, ceil_div(2 * adx * (tb + 1) - adx, 2 * ady) - 1);
+}
+
+// Pixels of row Y covered by the radius-2 discs (5x5 minus corners) on the Bresenham steps of edge (x0,y0)->(x1,y1),
+// walked in that direction as the reference does: always ONE span [xl, xr] (steps within one row of Y reach 2 pixels
+// sideways, steps two rows away reach 1, and consecutive steps move by at most one pixel).  Empty => xl > xr.
+__device__ __forceinline__ void near_span(int x0, int y0, int x1, int y1, int Y, int& xl, int& xr) {
+  const int adx = abs(x1 - x0), ady = abs(y1 - y0);
   const int sx = x1 > x0 ? 1 : -1, sy = y1 > y0 ? 1 : -1;
-  if (adx > ady) {   // x-major: one step per column, row = y0 + sy*floor((2*ady*k + adx) / (2*adx))
-    const int c_lo = max(X0 - 2, exmin), c_hi = min(X0 + PX + 1, exmax);
-    const int k0 = sx > 0 ? c_lo - x0 : x0 - c_hi;
-    const int num = 2 * ady * k0 + adx;
-    int m = num / (2 * adx), r = num - m * 2 * adx;
-    for (int k = k0; k <= k0 + (c_hi - c_lo); ++k) {
-      const int cx = x0 + sx * k, d = abs(Y - (y0 + sy * m));
-      if (d <= 2) { const int rad = d == 2 ? 1 : 2; near |= span_bits<PX>(cx - rad - X0, cx + rad - X0); }
-      r += 2 * ady;
-      if (r >= 2 * adx) { r -= 2 * adx; ++m; }
+  xl = 1; xr = 0;
+  if (adx > ady) {   // x-major: step k sits at (x0 + sx*k, y0 + sy*m(k))
+    const int t = (Y - y0) * sy;
+    int alo, ahi, clo, chi;
+    step_range(adx, ady, t - 2, t + 2, alo, ahi);
+    if (alo > ahi) return;
+    step_range(adx, ady, t - 1, t + 1, clo, chi);
+    int klo = alo - 1, khi = ahi + 1;
+    if (clo <= chi) { klo = min(klo, clo - 2); khi = max(khi, chi + 2); }
+    xl = sx > 0 ? x0 + klo : x0 - khi;
+    xr = sx > 0 ? x0 + khi : x0 - klo;
+  } else {           // y-major (and the single-point edge): step k sits at (x0 + sx*m(k), y0 + sy*k), one per row
+    int lo = INT_MAX, hi = INT_MIN;
+    const int k0 = max((Y - y0) * sy - 2, 0), k1 = min((Y - y0) * sy + 2, ady);   // the rows Y-2..Y+2 that hold a step
+    if (k0 <= k1) {
+      int m = 0, r = 0;
+      if (ady) { const int num = 2 * adx * k0 + ady; m = floor_div(num, 2 * ady); r = num - m * 2 * ady; }
+      for (int k = k0; k <= k1; ++k) {
+        const int d = k - (Y - y0) * sy;
+        const int cx = x0 + sx * m, rad = (d == 2 || d == -2) ? 1 : 2;
+        lo = min(lo, cx - rad); hi = max(hi, cx + rad);
+        r += 2 * adx;
+        if (r >= 2 * ady && ady) { r -= 2 * ady; ++m; }
+      }
     }
-  } else {           // y-major (and the single-point edge): one step per row
-    const int r_lo = max(Y - 2, eymin), r_hi = min(Y + 2, eymax);
-    const int k0 = sy > 0 ? r_lo - y0 : y0 - r_hi;
-    int m = 0, r = 0;
-    if (ady > 0) { const int num = 2 * adx * k0 + ady; m = num / (2 * ady); r = num - m * 2 * ady; }
-    for (int k = k0; k <= k0 + (r_hi - r_lo); ++k) {
-      const int cx = x0 + sx * m, d = abs(Y - (y0 + sy * k));
-      const int rad = d == 2 ? 1 : 2;
-      near |= span_bits<PX>(cx - rad - X0, cx + rad - X0);
-      r += 2 * adx;
-      if (ady > 0 && r >= 2 * ady) { r -= 2 * ady; ++m; }
-    }
+    if (lo <= hi) { xl = lo; xr = hi; }
   }
-  return near;
 }
 
 // coverage bits of pixels (X0..X0+PX-1, Y) for the polygon whose N vertices (x | y<<16) sit at sv[0..N); whole warp
@@ -175,19 +213,18 @@ __device__ __forceinline__ uint32_t cover_bits(const uint32_t* sv, int N, int X0
     if (cross) {
       int dy = y1 - y0, num = (Y - y0) * (x1 - x0) + x0 * dy;
       if (dy < 0) { dy = -dy; num = -num; }
-      const int t = num + dy - 1;
-      xc = t / dy;
-      if (t % dy < 0) --xc;   // floor division
+      xc = ceil_div(num, dy);
     }
-    for (uint32_t cm = __ballot_sync(FULL, cross); cm; cm &= cm - 1) {
+    for (uint32_t cm = __ballot_sync(FULL, cross && xc > XW0); cm; cm &= cm - 1) {
       const int t = __shfl_sync(FULL, xc, __ffs(cm) - 1);
       inside ^= span_bits<PX>(0, t - 1 - X0);
     }
-    const bool close = have && Y >= min(y0, y1) - 2 && Y <= max(y0, y1) + 2 && max(x0, x1) + 2 >= XW0 && min(x0, x1) - 2 <= XW0 + 32 * PX - 1;
-    for (uint32_t nm = __ballot_sync(FULL, close); nm; nm &= nm - 1) {
+    int xl = 1, xr = 0;
+    if (have && Y >= min(y0, y1) - 2 && Y <= max(y0, y1) + 2) near_span(x0, y0, x1, y1, Y, xl, xr);
+    for (uint32_t nm = __ballot_sync(FULL, xl <= xr && xr >= XW0 && xl <= XW0 + 32 * PX - 1); nm; nm &= nm - 1) {
       const int src = __ffs(nm) - 1;
-      const uint32_t a = __shfl_sync(FULL, pv, src), b = __shfl_sync(FULL, cv, src);
-      near |= near_bits<PX>((int16_t)(a & 0xffffu), (int16_t)(a >> 16), (int16_t)(b & 0xffffu), (int16_t)(b >> 16), X0, Y);
+      const int l = __shfl_sync(FULL, xl, src), r = __shfl_sync(FULL, xr, src);
+      near |= span_bits<PX>(l - X0, r - X0);
     }
   }
   return inside | near;
@@ -218,10 +255,12 @@ __global__ void __launch_bounds__(32 * TILE_H) raster_cover_kernel(const RasterP
     s_occ[s] = (fl & FLAG_OCCLUDER) ? 1u : 0u;
   }
   __syncthreads();
-  // the CTA's 8 rows are spread over the image (stride gridDim.y) so that every CTA gets the same mix of crowded
-  // and empty regions: with one wave of CTAs the kernel ends when the slowest one does
-  const int lane = threadIdx.x & 31, Y = blockIdx.y + (threadIdx.x >> 5) * gridDim.y, X0 = tx0 + lane * PX;
-  if (Y >= p.H) return;
+  // The CTA's rows are spread over the image (stride gridDim.y) so that every CTA sees the same mix of crowded and
+  // empty regions; a warp takes rows_per_warp of them, chosen by the host so that a small batch is ONE balanced wave.
+  const int lane = threadIdx.x & 31, X0 = tx0 + lane * PX;
+  for (int rr = 0; rr < p.rows_per_warp; ++rr) {
+  const int Y = blockIdx.y + ((threadIdx.x >> 5) + TILE_H * rr) * gridDim.y;
+  if (Y >= p.H) break;
   constexpr uint32_t ALL = (1u << PX) - 1u;
   const uint32_t vm = X0 >= p.W ? 0u : (X0 + PX <= p.W ? ALL : (1u << (p.W - X0)) - 1u);
   // 0: no masks wanted, 1: one aligned PX-byte store per instance, 2: ragged width, byte stores
@@ -272,18 +311,32 @@ __global__ void __launch_bounds__(32 * TILE_H) raster_cover_kernel(const RasterP
       }
     }
   }
+  }
 }
 
-// ---- 3. area filter (cityscapes.py:273) -----------------------------------------------------------------------------
-__global__ void raster_keep_kernel(const RasterParams p) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= p.B * p.K) return;
-  p.keep[idx] = (p.flags[idx] & FLAG_DRAWN) && p.area[idx] > p.min_area;
+// ---- 3. area filter (cityscapes.py:273) and the per-image count of clamped vertices -----------------------------------
+__global__ void __launch_bounds__(256) raster_keep_kernel(const RasterParams p) {
+  const int b = blockIdx.x, t = threadIdx.x;
+  int c = 0;
+  if (t < p.K) {
+    const size_t idx = (size_t)b * p.K + t;
+    p.keep[idx] = (p.flags[idx] & FLAG_DRAWN) && p.area[idx] > p.min_area;
+    c = p.clamped[idx];
+  }
+  __shared__ int s_sum[8];
+  c = __reduce_add_sync(0xffffffffu, c);
+  if ((t & 31) == 0) s_sum[t >> 5] = c;
+  __syncthreads();
+  if (t == 0) {
+    int tot = 0;
+    for (int w = 0; w < 8; ++w) tot += s_sum[w];
+    p.status[b] = tot;
+  }
 }
 
 }  // namespace
 
-size_t raster_workspace_bytes(int B, int K) { return (size_t)B * K * (sizeof(int4) + sizeof(int32_t)) + 256; }
+size_t raster_workspace_bytes(int B, int K) { return (size_t)B * K * (sizeof(int4) + 2 * sizeof(int32_t)) + 256; }
 
 int raster_launch(const cpoly_raster_args& a, cudaStream_t stream) {
   RasterParams p;
@@ -293,20 +346,31 @@ int raster_launch(const cpoly_raster_args& a, cudaStream_t stream) {
   p.conf = a.conf; p.status = a.status; p.masks = a.masks;
   p.bbox = reinterpret_cast<int4*>(a.workspace);
   p.flags = reinterpret_cast<int32_t*>(p.bbox + (size_t)a.B * a.K);
-  raster_prep_kernel<<<a.B, 256, 0, stream>>>(p);
+  p.clamped = p.flags + (size_t)a.B * a.K;
+  raster_prep_kernel<<<dim3(a.B, (a.K + PREP_WARPS - 1) / PREP_WARPS), 32 * PREP_WARPS, 0, stream>>>(p);
   if (int rc = check_launch("raster_prep_kernel")) return rc;
   const size_t smem = (size_t)a.K * (a.N * 4 + sizeof(int4) + sizeof(uint32_t));
-  // 8 pixels per thread (8-byte stores); CPOLY_RASTER_PX=16 selects 16 (16-byte stores, needs W % 16 == 0 and 16-byte masks)
+  // 16 pixels per thread (one 16-byte store per instance; a warp writes 512 contiguous bytes) when the row pitch and
+  // the buffer allow it, else 8 (8-byte stores).  CPOLY_RASTER_PX=8 forces the narrow variant (tests, profiling).
   const char* env = getenv("CPOLY_RASTER_PX");
-  const bool px16 = env && atoi(env) == 16 && a.W % 16 == 0 && (reinterpret_cast<uintptr_t>(a.masks) & 15) == 0;
+  const bool px16 = !(env && atoi(env) == 8) && a.W % 16 == 0 && (reinterpret_cast<uintptr_t>(a.masks) & 15) == 0;
   auto kernel = px16 ? raster_cover_kernel<16> : raster_cover_kernel<8>;
   if (smem > 48 * 1024) CPOLY_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int tile_w = 32 * (px16 ? 16 : 8);
-  const dim3 grid((a.W + tile_w - 1) / tile_w, (a.H + TILE_H - 1) / TILE_H, a.B);
+  // rows per warp: 1 when the grid is many waves deep (or fits in one), else just enough for one balanced wave
+  int dev = 0, sms = 0, per_sm = 0;
+  CPOLY_CUDA_OK(cudaGetDevice(&dev));
+  CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  CPOLY_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 32 * TILE_H, smem));
+  const long long capacity = (long long)sms * (per_sm > 0 ? per_sm : 1);
+  const int tiles_x = (a.W + tile_w - 1) / tile_w, row_groups = (a.H + TILE_H - 1) / TILE_H;
+  const long long ctas = (long long)tiles_x * row_groups * a.B;
+  p.rows_per_warp = (ctas > capacity && ctas <= 4 * capacity) ? (int)((ctas + capacity - 1) / capacity) : 1;
+  const dim3 grid(tiles_x, (row_groups + p.rows_per_warp - 1) / p.rows_per_warp, a.B);
   CPOLY_REQUIRE(grid.y <= 65535 && grid.z <= 65535, CPOLY_EINVAL, "raster grid too large");
   kernel<<<grid, 32 * TILE_H, smem, stream>>>(p);
   if (int rc = check_launch("raster_cover_kernel")) return rc;
-  raster_keep_kernel<<<(a.B * a.K + 255) / 256, 256, 0, stream>>>(p);
+  raster_keep_kernel<<<a.B, 256, 0, stream>>>(p);
   return check_launch("raster_keep_kernel");
 }
 

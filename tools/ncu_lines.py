@@ -1,6 +1,6 @@
 """Per-source-line instruction counts and stall samples from an ncu report (first profiled launch only).
 
-    python tools/ncu_lines.py gpurun_out/prof.ncu-rep [top_n]
+    python tools/ncu_lines.py gpurun_out/prof.ncu-rep [top_n] [kernel-name regex]
 
 Needs `ncu` on PATH (no GPU); the kernels must have been built with -lineinfo."""
 import collections
@@ -14,7 +14,8 @@ import sys
 def main():
     rep = sys.argv[1]
     top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"],
+    pick = ["-k", "regex:" + sys.argv[3]] if len(sys.argv) > 3 else []
+    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass", *pick],
                          capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     data = collections.OrderedDict()
