@@ -11,8 +11,8 @@
 // horizontally adjacent pixels and walks the instances nearest-first, carrying the "already removed" bits in a
 // register, so the occlusion rule costs nothing and the only HBM traffic is the (B,K,H,W) byte masks, written once
 // with 16-byte stores (a warp writes 512 contiguous bytes per instance).  Algorithmic bytes: count*H*W per image.
-// Measured (tools/raster_bench.py, profiles/r01l_*): 86 % of the measured HBM peak on a batch of 8 Cityscapes frames,
-// 46 % on a single frame (one wave; launch + prep + keep are ~10 of its 68 us).
+// Measured (tools/raster_bench.py, profiles/r01l_*): 88 % of the measured HBM peak on a batch of 8 Cityscapes frames,
+// 45 % on a single frame (one wave; launch + prep + keep are ~10 of its 68 us).
 #include <limits.h>
 #include <stdlib.h>
 
@@ -244,16 +244,24 @@ __global__ void __launch_bounds__(32 * TILE_H) raster_cover_kernel(const RasterP
   if (n == 0) return;
   int4* s_bbox = reinterpret_cast<int4*>(smem_raw);                      // K dilated boxes (.x > .z when not drawn)
   uint32_t* s_occ = reinterpret_cast<uint32_t*>(s_bbox + p.K);           // K occluder flags
-  uint32_t* sv = s_occ + p.K;                                            // n * N packed vertices
+  uint32_t* sv = s_occ + ((p.K + 3) & ~3);                                          // n * N packed vertices
   const int tx0 = blockIdx.x * TILE_W;
   const size_t base = (size_t)b * p.K;
   const uint32_t* gv = reinterpret_cast<const uint32_t*>(p.verts) + base * p.N;
-  for (int t = threadIdx.x; t < n * p.N; t += blockDim.x) sv[t] = gv[t];
+  // all copies in flight at once (a plain load/store loop walked one L2 round trip per iteration: ~15 % of a frame)
+  if ((p.N & 3) == 0 && (reinterpret_cast<uintptr_t>(gv) & 15) == 0) {
+    for (int t = threadIdx.x; t < n * p.N / 4; t += blockDim.x)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(sv + 4 * t)), "l"(gv + 4 * t));
+  } else {
+    for (int t = threadIdx.x; t < n * p.N; t += blockDim.x)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(sv + t)), "l"(gv + t));
+  }
   for (int s = threadIdx.x; s < n; s += blockDim.x) {
     const int fl = p.flags[base + s];
     s_bbox[s] = (fl & FLAG_DRAWN) ? p.bbox[base + s] : make_int4(1, 1, 0, 0);
     s_occ[s] = (fl & FLAG_OCCLUDER) ? 1u : 0u;
   }
+  asm volatile("cp.async.wait_all;" ::: "memory");
   __syncthreads();
   // The CTA's rows are spread over the image (stride gridDim.y) so that every CTA sees the same mix of crowded and
   // empty regions; a warp takes rows_per_warp of them, chosen by the host so that a small batch is ONE balanced wave.
@@ -279,11 +287,28 @@ __global__ void __launch_bounds__(32 * TILE_H) raster_cover_kernel(const RasterP
     const uint32_t hit = __ballot_sync(FULL, h), occ = __ballot_sync(FULL, o);
     const int cnt = min(32, n - g);
     if (mode == 1 && hit == 0u) {   // nothing here: a run of zero stores
-#pragma unroll 4
-      for (int j = 0; j < cnt; ++j, out += plane) {
-        if (PX == 8) __stcs(reinterpret_cast<uint2*>(out), make_uint2(0u, 0u));
-        else __stcs(reinterpret_cast<uint4*>(out), make_uint4(0u, 0u, 0u, 0u));
+      // four independent address registers per round: with one pointer bumped in place every store waits for the
+      // previous one to leave the LSU queue before its address register may be overwritten
+      int j = 0;
+      for (; j + 4 <= cnt; j += 4) {
+        uint8_t* o0 = out + (size_t)j * plane;
+        uint8_t* o1 = o0 + plane;
+        uint8_t* o2 = o1 + plane;
+        uint8_t* o3 = o2 + plane;
+        if (PX == 8) {
+          __stcs(reinterpret_cast<uint2*>(o0), make_uint2(0u, 0u)); __stcs(reinterpret_cast<uint2*>(o1), make_uint2(0u, 0u));
+          __stcs(reinterpret_cast<uint2*>(o2), make_uint2(0u, 0u)); __stcs(reinterpret_cast<uint2*>(o3), make_uint2(0u, 0u));
+        } else {
+          __stcs(reinterpret_cast<uint4*>(o0), make_uint4(0u, 0u, 0u, 0u)); __stcs(reinterpret_cast<uint4*>(o1), make_uint4(0u, 0u, 0u, 0u));
+          __stcs(reinterpret_cast<uint4*>(o2), make_uint4(0u, 0u, 0u, 0u)); __stcs(reinterpret_cast<uint4*>(o3), make_uint4(0u, 0u, 0u, 0u));
+        }
       }
+      for (; j < cnt; ++j) {
+        uint8_t* o0 = out + (size_t)j * plane;
+        if (PX == 8) __stcs(reinterpret_cast<uint2*>(o0), make_uint2(0u, 0u));
+        else __stcs(reinterpret_cast<uint4*>(o0), make_uint4(0u, 0u, 0u, 0u));
+      }
+      out += (size_t)cnt * plane;
       continue;
     }
     for (int j = 0; j < cnt; ++j) {
@@ -295,21 +320,21 @@ __global__ void __launch_bounds__(32 * TILE_H) raster_cover_kernel(const RasterP
         const int c = __reduce_add_sync(FULL, __popc(m));
         if (lane == 0 && c) atomicAdd(p.area + base + s, c);
       }
+      uint8_t* o = out + (size_t)j * plane;
       if (mode == 1) {
         if (PX == 8) {
-          __stcs(reinterpret_cast<uint2*>(out), m ? make_uint2(bits_to_bytes(m & 15u), bits_to_bytes(m >> 4)) : make_uint2(0u, 0u));
+          __stcs(reinterpret_cast<uint2*>(o), m ? make_uint2(bits_to_bytes(m & 15u), bits_to_bytes(m >> 4)) : make_uint2(0u, 0u));
         } else {
-          __stcs(reinterpret_cast<uint4*>(out), m ? make_uint4(bits_to_bytes(m & 15u), bits_to_bytes((m >> 4) & 15u),
-                                                              bits_to_bytes((m >> 8) & 15u), bits_to_bytes(m >> 12))
-                                                  : make_uint4(0u, 0u, 0u, 0u));
+          __stcs(reinterpret_cast<uint4*>(o), m ? make_uint4(bits_to_bytes(m & 15u), bits_to_bytes((m >> 4) & 15u),
+                                                            bits_to_bytes((m >> 8) & 15u), bits_to_bytes(m >> 12))
+                                                : make_uint4(0u, 0u, 0u, 0u));
         }
-        out += plane;
       } else if (mode == 2) {
         for (int k = 0; k < PX; ++k)
-          if ((vm >> k) & 1u) out[k] = ((m >> k) & 1u) ? 255 : 0;
-        out += plane;
+          if ((vm >> k) & 1u) o[k] = ((m >> k) & 1u) ? 255 : 0;
       }
     }
+    if (mode) out += (size_t)cnt * plane;
   }
   }
 }
@@ -349,7 +374,7 @@ int raster_launch(const cpoly_raster_args& a, cudaStream_t stream) {
   p.clamped = p.flags + (size_t)a.B * a.K;
   raster_prep_kernel<<<dim3(a.B, (a.K + PREP_WARPS - 1) / PREP_WARPS), 32 * PREP_WARPS, 0, stream>>>(p);
   if (int rc = check_launch("raster_prep_kernel")) return rc;
-  const size_t smem = (size_t)a.K * (a.N * 4 + sizeof(int4) + sizeof(uint32_t));
+  const size_t smem = (size_t)a.K * (a.N * 4 + sizeof(int4)) + (size_t)((a.K + 3) & ~3) * sizeof(uint32_t);
   // 16 pixels per thread (one 16-byte store per instance; a warp writes 512 contiguous bytes) when the row pitch and
   // the buffer allow it, else 8 (8-byte stores).  CPOLY_RASTER_PX=8 forces the narrow variant (tests, profiling).
   const char* env = getenv("CPOLY_RASTER_PX");

@@ -61,8 +61,16 @@ def check_against_oracle(r, dets, b, W, H, thresh):
             assert np.array_equal(masks[s], vis), s
 
 
+@pytest.fixture(params=["px16", "px8"])
+def store_width(request, monkeypatch):
+    """both store variants of raster_cover_kernel (16-byte stores by default, 8-byte when forced or W % 16 != 0)"""
+    if request.param == "px8":
+        monkeypatch.setenv("CPOLY_RASTER_PX", "8")
+    return request.param
+
+
 @pytest.mark.parametrize("name", ["raster_street", "raster_tangled", "raster_tiny"])
-def test_vs_reference_golden(name):
+def test_vs_reference_golden(name, store_width):
     import centerpoly_b200 as cp
     g = np.load(os.path.join(GOLDEN, name + ".npz"))
     dets = torch.from_numpy(g["dets"])[None].cuda()
@@ -82,8 +90,8 @@ def test_vs_reference_golden(name):
 
 
 @pytest.mark.parametrize("B,K,N,W,H,wild", [(1, 100, 32, 256, 128, False), (3, 40, 32, 203, 97, True), (2, 64, 16, 517, 64, True),
-                                            (1, 256, 8, 96, 33, True), (2, 17, 64, 64, 200, True), (1, 5, 3, 9, 9, True)])
-def test_vs_oracle(B, K, N, W, H, wild):
+                                            (1, 256, 8, 96, 33, True), (2, 17, 64, 64, 200, True), (1, 5, 3, 9, 9, True), (2, 30, 32, 1040, 48, True)])
+def test_vs_oracle(B, K, N, W, H, wild, store_width):
     import centerpoly_b200 as cp
     dets = np.stack([scene(100 * B + b, K, N, W, H, wild) for b in range(B)])
     d = torch.from_numpy(dets).cuda()
