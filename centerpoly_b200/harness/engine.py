@@ -16,6 +16,7 @@ import torch
 
 from .. import decode as cdecode
 from .. import post_process as cpost
+from .. import raster as craster
 from .dla34 import PolydetDLA34, calibrate_random_init
 
 HEADS = {"hm": 8, "poly": 64, "pseudo_depth": 1, "reg": 2}
@@ -23,7 +24,8 @@ HEADS = {"hm": 8, "poly": 64, "pseudo_depth": 1, "reg": 2}
 
 class PolydetEngine:
     def __init__(self, height=1024, width=2048, batch=1, dtype="bf16", K=100, rep="cartesian", heads=None,
-                 device="cuda:0", seed=317, calibrate=True, use_graph=True, n_slots=2, optimize=True, post_process=True):
+                 device="cuda:0", seed=317, calibrate=True, use_graph=True, n_slots=2, optimize=True, post_process=True,
+                 rasterise=False, thresh=0.05):
         self.device = torch.device(device)
         self.dtype = dtype
         self.K, self.rep = K, rep
@@ -58,6 +60,11 @@ class PolydetEngine:
             c = [[width / 2.0, height / 2.0]] * batch
             self.post_affine = torch.as_tensor(cpost.batch_inverse_affine(c, [float(max(height, width))] * batch, width // 4, height // 4),
                                                dtype=torch.float64).to(self.device)
+        # optional: depth-ordered instance masks of format_and_write_to_cityscapes (datasets/dataset/cityscapes.py:226-279)
+        # from the image-coordinate detections, inside the same captured graph (needs post_process)
+        if rasterise and not post_process:
+            raise ValueError("rasterise=True needs post_process=True (masks are drawn in image coordinates)")
+        self.rasterise, self.thresh = bool(rasterise), float(thresh)
         self.stream = torch.cuda.Stream(self.device)
         self.copy_stream = torch.cuda.Stream(self.device)   # H2D
         self.d2h_stream = torch.cuda.Stream(self.device)    # D2H (separate, or it would serialise behind the next H2D)
@@ -69,7 +76,8 @@ class PolydetEngine:
                 x=torch.zeros(self.shape, device=self.device).contiguous(memory_format=torch.channels_last),
                 dets=torch.zeros((batch, K, n_poly + 7), device=self.device),
                 host_out=torch.zeros((batch, K, n_poly + 7)).pin_memory(),
-                graph=None, h2d_done=torch.cuda.Event(), compute_done=torch.cuda.Event(), d2h_done=torch.cuda.Event()))
+                masks=torch.zeros((batch, K, height, width), dtype=torch.uint8, device=self.device) if rasterise else None,
+                raster=None, graph=None, h2d_done=torch.cuda.Event(), compute_done=torch.cuda.Event(), d2h_done=torch.cuda.Event()))
         self._warm_and_capture()
 
     # ------------------------------------------------------------------------------------------
@@ -93,20 +101,27 @@ class PolydetEngine:
             return cdecode.polydet_decode(hm, out["poly"], out["pseudo_depth"], reg=out.get("reg"), K=self.K, rep=self.rep,
                                           post_affine=self.post_affine)
 
+    def _frame(self, slot):
+        """Everything one replay does for a slot: network + decode (+ back-mapping) into slot['dets'], then the masks."""
+        slot["dets"].copy_(self._step(slot["x"]))
+        if self.rasterise:
+            _, _, h, w = self.shape
+            slot["raster"] = craster.rasterise_instances(slot["dets"], w, h, self.thresh, out=slot["masks"])
+
     def _warm_and_capture(self):
         from .. import _lib
         with torch.cuda.stream(self.stream):
             for slot in self.slots:
                 for _ in range(2):  # fills the packed-weight cache, cuDNN plans, allocator pools
                     before = sum(_lib.LAUNCHES.values())
-                    slot["dets"].copy_(self._step(slot["x"]))
+                    self._frame(slot)
                     self.launches_per_step = sum(_lib.LAUNCHES.values()) - before   # our kernels in one warm frame
             self.stream.synchronize()
             if self.use_graph:
                 for slot in self.slots:
                     g = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(g, stream=self.stream):
-                        slot["dets"].copy_(self._step(slot["x"]))
+                        self._frame(slot)
                     slot["graph"] = g
         self.stream.synchronize()
 
@@ -114,7 +129,7 @@ class PolydetEngine:
         if slot["graph"] is not None:
             slot["graph"].replay()
         else:
-            slot["dets"].copy_(self._step(slot["x"]))
+            self._frame(slot)
 
     # ------------------------------------------------------------------------------------------
     def set_resident_frames(self, frames):
