@@ -90,7 +90,7 @@ def test_vs_reference_golden(name, store_width):
 
 
 @pytest.mark.parametrize("B,K,N,W,H,wild", [(1, 100, 32, 256, 128, False), (3, 40, 32, 203, 97, True), (2, 64, 16, 517, 64, True),
-                                            (1, 256, 8, 96, 33, True), (2, 17, 64, 64, 200, True), (1, 5, 3, 9, 9, True), (2, 30, 32, 1040, 48, True)])
+                                            (1, 256, 8, 96, 33, True), (2, 17, 64, 64, 200, True), (1, 5, 3, 9, 9, True), (2, 30, 32, 1040, 48, True), (1, 250, 64, 160, 64, True)])
 def test_vs_oracle(B, K, N, W, H, wild, store_width):
     import centerpoly_b200 as cp
     dets = np.stack([scene(100 * B + b, K, N, W, H, wild) for b in range(B)])
