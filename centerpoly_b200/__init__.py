@@ -9,3 +9,4 @@ from .raster import CITYSCAPES_CLASSES, RasterResult, rasterise_instances  # noq
 from .post_process import batch_inverse_affine, group_by_class, inverse_affine, polydet_post_process  # noqa: F401
 
 __version__ = "0.1.0"
+from .poly_loss import IOU_STATUS, PolyLoss, poly_iou_loss  # noqa: F401

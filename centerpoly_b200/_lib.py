@@ -23,7 +23,7 @@ EXPORTED_SYMBOLS = (
     "cpoly_dcn_packed_weight_bytes", "cpoly_dcn_pack_weights", "cpoly_dcn_forward_workspace_bytes", "cpoly_dcn_forward",
     "cpoly_idaup_upsample_forward",
     "cpoly_dcn_backward_workspace_bytes", "cpoly_dcn_backward", "cpoly_decode_workspace_bytes", "cpoly_decode",
-    "cpoly_rasterise_workspace_bytes", "cpoly_rasterise",
+    "cpoly_rasterise_workspace_bytes", "cpoly_rasterise", "cpoly_poly_iou_forward", "cpoly_poly_iou_backward",
 )
 
 
@@ -67,9 +67,15 @@ class RasterArgs(Structure):
         ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
 
 
+class PolyIouArgs(Structure):
+    _fields_ = [(n, c_int32) for n in ("B", "M", "N", "H", "W", "dtype")] + [
+        ("poly", Tensor4), ("ind", c_void_p), ("mask", c_void_p), ("target", c_void_p), ("iou", c_void_p),
+        ("dpred", c_void_p), ("status", c_void_p), ("stats", c_void_p), ("grad_loss", c_void_p), ("grad_poly", Tensor4)]
+
+
 _lib = None
 # kernels launched by the shims since import (our kernels only; bench.py reports it as gpu_launches)
-LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "decode": 0, "rasterise": 0}
+LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "decode": 0, "rasterise": 0, "poly_iou": 0}
 
 
 def lib():
@@ -108,7 +114,11 @@ def lib():
         L.cpoly_rasterise_workspace_bytes.argtypes = [c_int32] * 2
         L.cpoly_rasterise.restype = c_int32
         L.cpoly_rasterise.argtypes = [POINTER(RasterArgs), c_void_p]
-        if L.cpoly_abi_version() != 4:
+        L.cpoly_poly_iou_forward.restype = c_int32
+        L.cpoly_poly_iou_forward.argtypes = [POINTER(PolyIouArgs), c_void_p]
+        L.cpoly_poly_iou_backward.restype = c_int32
+        L.cpoly_poly_iou_backward.argtypes = [POINTER(PolyIouArgs), c_void_p]
+        if L.cpoly_abi_version() != 5:
             raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
         _lib = L
     return _lib

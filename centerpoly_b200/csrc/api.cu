@@ -190,4 +190,28 @@ int cpoly_idaup_upsample_forward(const cpoly_upsample_args* a, cpoly_stream_t st
   return idaup_upsample_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+static int poly_iou_check(const cpoly_poly_iou_args* a) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->M >= 1 && a->H > 0 && a->W > 0, CPOLY_EINVAL, "bad poly-IoU dims");
+  CPOLY_REQUIRE(a->N >= 2 && a->N <= 64, CPOLY_EINVAL, "N (vertices) must be in [2, 64], got %d", a->N);
+  CPOLY_REQUIRE((int64_t)a->B * a->M < (1 << 28), CPOLY_EINVAL, "too many object slots");
+  CPOLY_REQUIRE(a->ind && a->mask && a->dpred && a->stats, CPOLY_EINVAL, "NULL pointer");
+  return CPOLY_OK;
+}
+
+int cpoly_poly_iou_forward(const cpoly_poly_iou_args* a, cpoly_stream_t stream) {
+  if (int rc = poly_iou_check(a)) return rc;
+  CPOLY_REQUIRE(a->dtype == CPOLY_F32 || a->dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", a->dtype);
+  CPOLY_REQUIRE(a->poly.ptr && a->target && a->iou && a->status, CPOLY_EINVAL, "NULL pointer");
+  if (a->B == 0) return CPOLY_OK;
+  return poly_iou_forward_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int cpoly_poly_iou_backward(const cpoly_poly_iou_args* a, cpoly_stream_t stream) {
+  if (int rc = poly_iou_check(a)) return rc;
+  CPOLY_REQUIRE(a->grad_loss && a->grad_poly.ptr, CPOLY_EINVAL, "NULL pointer");
+  if (a->B == 0) return CPOLY_OK;
+  return poly_iou_backward_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

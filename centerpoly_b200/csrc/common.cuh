@@ -135,4 +135,6 @@ size_t decode_workspace_bytes(int B, int C, int H, int W, int K);
 int decode_launch(const cpoly_decode_args& a, cudaStream_t stream);
 size_t raster_workspace_bytes(int B, int K);
 int raster_launch(const cpoly_raster_args& a, cudaStream_t stream);
+int poly_iou_forward_launch(const cpoly_poly_iou_args& a, cudaStream_t stream);
+int poly_iou_backward_launch(const cpoly_poly_iou_args& a, cudaStream_t stream);
 }  // namespace cpoly

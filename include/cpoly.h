@@ -23,6 +23,10 @@
  *                           heat_is_logit=1) the `hm.sigmoid_()` of src/lib/detectors/polydet.py:28.
  *   cpoly_rasterise      <- the mask construction inside `format_and_write_to_cityscapes`,
  *                           src/lib/datasets/dataset/cityscapes.py:226-279 (PIL ImageDraw + `bresenham` + numpy).
+ *   cpoly_poly_iou_forward / _backward <- the polygon-IoU arm of `PolyLoss.forward`, src/lib/models/losses.py:870-888,
+ *                           :909-910 (`WeilPolygonClipper` :373-628, `area` :25-41), including the
+ *                           `_transpose_and_gather_feat` of :855 and, in backward, what autograd does with the
+ *                           reference's per-object graph.
  *
  * Ownership: the caller allocates every input, output and workspace in device memory and passes raw
  * device pointers; the library allocates nothing, keeps no global state and never synchronises the
@@ -46,7 +50,7 @@
 extern "C" {
 #endif
 
-#define CPOLY_ABI_VERSION 4
+#define CPOLY_ABI_VERSION 5
 
 /* element types */
 #define CPOLY_F32 0
@@ -228,6 +232,35 @@ typedef struct {
 
 size_t cpoly_rasterise_workspace_bytes(int32_t B, int32_t K);
 int cpoly_rasterise(const cpoly_raster_args* args, cpoly_stream_t stream);
+
+/* --------------------------------------------------------------------------- polygon-IoU loss */
+
+/* per-object status (`status` below); anything but OK contributes IoU 0 and no gradient */
+#define CPOLY_IOU_OK 0
+#define CPOLY_IOU_NO_OUTBOUND 1 /* in-bound but no out-bound crossings: the reference raises IndexError (losses.py:590) */
+#define CPOLY_IOU_RUNAWAY 2     /* the reference's walk does not terminate (more than 8N vertices / in-bound list exhausted) */
+#define CPOLY_IOU_TOO_MANY 3    /* more than 4N in-bound or out-bound crossings */
+#define CPOLY_IOU_NONFINITE 4   /* NaN / Inf in the prediction or target row */
+
+typedef struct {
+  int32_t B, M, N;        /* images, object slots per image (max_objs), vertices per polygon (2 <= N <= 64) */
+  int32_t H, W;           /* head-map size */
+  int32_t dtype;          /* element type of `poly`: CPOLY_F32 | CPOLY_BF16 */
+  cpoly_tensor4 poly;     /* (B,2N,H,W) polar poly head: channel 2v = r_v, 2v+1 = theta_v (any strides) */
+  const int64_t* ind;     /* (B,M) flat cell index y*W+x of each object (batch['ind']) */
+  const uint8_t* mask;    /* (B,M) batch['reg_mask'] != 0 */
+  const float* target;    /* (B,M,2N) batch['poly'], polar, angles increasing */
+  float* iou;             /* (B,M)   out: intersection / (union + 1e-6) per object, 0 where masked out */
+  float* dpred;           /* (B,M,2N) out: d iou / d prediction row (in head-channel order) */
+  int32_t* status;        /* (B,M)   out: CPOLY_IOU_* */
+  float* stats;           /* (4)     out: {loss = 1 - sum iou/(n+1e-6), -1/(n+1e-6), n = sum mask, objects with status != 0} */
+  /* backward only */
+  const float* grad_loss; /* (1) upstream gradient of the scalar loss, on the device */
+  cpoly_tensor4 grad_poly;/* (B,2N,H,W) fp32, zero-initialised by the caller; receives += grad_loss * d loss / d poly */
+} cpoly_poly_iou_args;
+
+int cpoly_poly_iou_forward(const cpoly_poly_iou_args* args, cpoly_stream_t stream);
+int cpoly_poly_iou_backward(const cpoly_poly_iou_args* args, cpoly_stream_t stream);
 
 #ifdef __cplusplus
 }
