@@ -11,8 +11,10 @@ ranks like ``loss.mean()`` over replicas (base_trainer.py:95).
 
 Loss: focal loss on the heat map (src/lib/models/losses.py:146-171 ``_neg_loss``) + masked L1 on the
 poly / pseudo_depth / reg heads gathered at the ground-truth centres (``RegL1Loss`` :817-830 via
-``_transpose_and_gather_feat``).  The polygon-IoU term of the reference (``WeilPolygonClipper``, host Python at
-~80 ms per object) is SURVEY §8(f)-1, a "next" row, and is not part of this step.
+``_transpose_and_gather_feat``) = ``polydet_l1_loss``.  With ``rep='polar'`` targets, ``polydet_l1_iou_loss`` adds the
+reference's polygon-IoU term (``PolyLoss`` with ``poly_loss='l1+iou'``, losses.py:870-945; ``WeilPolygonClipper``,
+host Python at ~80 ms per object in the reference) through ``centerpoly_b200.poly_loss`` — the configuration
+BASELINE.json configs[3] names ("L1 + polygon IoU loss").
 """
 from __future__ import annotations
 
@@ -56,7 +58,22 @@ def polydet_l1_loss(out, batch, w_hm=1.0, w_poly=1.0, w_depth=0.1, w_off=1.0):
     return loss
 
 
-def synthetic_batch(batch, height, width, n_cls=8, n_vtx=32, max_objs=128, n_obj=20, device="cpu", seed=0):
+def polydet_l1_iou_loss(out, batch, w_hm=1.0, w_poly=1.0, w_depth=0.1, w_off=1.0):
+    """PolydetLoss.forward (src/lib/trains/polydet.py:38-162) with poly_loss='l1+iou', rep='polar': the poly term is
+    the GPU ``PolyLoss`` mirror (IoU arm on our kernel, polar L1 + (1 - cos) angle arm as losses.py:927-936)."""
+    from ..poly_loss import PolyLoss
+
+    class _Opt:
+        poly_loss, rep, poly_order = "l1+iou", "polar", False
+    hm = torch.clamp(out["hm"].float().sigmoid(), min=1e-4, max=1 - 1e-4)
+    loss = w_hm * focal_loss(hm, batch["hm"])
+    loss = loss + w_poly * PolyLoss(_Opt())(out["poly"], batch["reg_mask"], batch["ind"], batch["poly"])
+    loss = loss + w_depth * reg_l1(out["pseudo_depth"], batch["reg_mask"], batch["ind"], batch["pseudo_depth"])
+    loss = loss + w_off * reg_l1(out["reg"], batch["reg_mask"], batch["ind"], batch["reg"])
+    return loss
+
+
+def synthetic_batch(batch, height, width, n_cls=8, n_vtx=32, max_objs=128, n_obj=20, device="cpu", seed=0, rep="cartesian"):
     """Targets shaped like PolydetDataset.__getitem__ (src/lib/datasets/sample/polydet.py:138-150,425-449)."""
     g = torch.Generator().manual_seed(seed)
     h, w = height // 4, width // 4
@@ -79,8 +96,12 @@ def synthetic_batch(batch, height, width, n_cls=8, n_vtx=32, max_objs=128, n_obj
             reg_mask[b, k] = 1
             ang = torch.linspace(0, 2 * 3.14159, n_vtx + 1)[:-1]
             r = 4.0 + 10.0 * torch.rand(n_vtx, generator=g)
-            poly[b, k, 0::2] = r * torch.cos(ang)
-            poly[b, k, 1::2] = r * torch.sin(ang)
+            if rep == "polar":           # (r, theta) pairs, theta in [0, 2 pi) increasing (sample/polydet.py:250-263)
+                poly[b, k, 0::2] = r
+                poly[b, k, 1::2] = ang + 0.5 * 6.28318 / n_vtx * float(torch.rand(1, generator=g))
+            else:
+                poly[b, k, 0::2] = r * torch.cos(ang)
+                poly[b, k, 1::2] = r * torch.sin(ang)
             depth[b, k, 0] = float(torch.rand(1, generator=g))
             reg[b, k] = torch.rand(2, generator=g)
     out = dict(input=x, hm=hm, ind=ind, reg_mask=reg_mask, poly=poly, pseudo_depth=depth, reg=reg)

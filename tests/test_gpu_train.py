@@ -22,3 +22,21 @@ def test_training_steps_reduce_the_loss(dtype):
     for n, p in net.named_parameters():
         if ".conv.weight" in n or "conv_offset_mask" in n:
             assert p.grad is not None and torch.isfinite(p.grad).all(), n
+
+
+def test_training_with_polygon_iou_loss():
+    """configs[3] names "L1 + polygon IoU": polar targets, PolyLoss l1+iou with the IoU arm on cpoly_poly_iou_*."""
+    from centerpoly_b200 import _lib
+    from centerpoly_b200.harness.dla34 import PolydetDLA34, calibrate_random_init
+    from centerpoly_b200.harness.train import DataParallelTrainer, polydet_l1_iou_loss, synthetic_batch
+    torch.manual_seed(317)
+    net = PolydetDLA34().cuda().to(memory_format=torch.channels_last)
+    calibrate_random_init(net, 64, 128)
+    trainer = DataParallelTrainer(net, lr=5e-4, dtype=torch.bfloat16, loss_fn=polydet_l1_iou_loss)
+    batch = synthetic_batch(2, 128, 256, n_obj=6, device="cuda", seed=3, rep="polar")
+    batch["input"] = batch["input"].contiguous(memory_format=torch.channels_last)
+    before = _lib.LAUNCHES["poly_iou"]
+    losses = [float(trainer.step(batch)) for _ in range(12)]
+    assert _lib.LAUNCHES["poly_iou"] == before + 12 * 3          # forward (2 kernels) + backward (1) every step
+    assert all(l == l and abs(l) < 1e6 for l in losses), losses
+    assert min(losses[-3:]) < losses[0], losses

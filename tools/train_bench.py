@@ -17,6 +17,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def _launches(key):
+    from centerpoly_b200 import _lib
+    return _lib.LAUNCHES.get(key, 0)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=16)
@@ -26,6 +31,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--dcn-path", default="auto", choices=["auto", "simt"])
+    ap.add_argument("--poly-loss", default="l1", choices=["l1", "l1+iou"],
+                    help="l1: cartesian targets, masked L1; l1+iou: polar targets, the reference's PolyLoss l1+iou (IoU arm on the GPU kernel)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -35,14 +42,16 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     import centerpoly_b200 as cp
     from centerpoly_b200.harness.dla34 import PolydetDLA34, calibrate_random_init
-    from centerpoly_b200.harness.train import DataParallelTrainer, synthetic_batch
+    from centerpoly_b200.harness.train import DataParallelTrainer, polydet_l1_iou_loss, polydet_l1_loss, synthetic_batch
     cp.set_dcn_path(args.dcn_path)
     torch.backends.cudnn.benchmark = True
     torch.manual_seed(317)                                   # same initial weights on every rank
     net = PolydetDLA34().cuda().to(memory_format=torch.channels_last)
     calibrate_random_init(net, 128, 256)
-    trainer = DataParallelTrainer(net, lr=2e-4, dtype=torch.bfloat16 if args.dtype == "bf16" else None)
-    batch = synthetic_batch(args.batch, args.height, args.width, device="cuda", seed=1000 + rank)
+    iou = args.poly_loss == "l1+iou"
+    trainer = DataParallelTrainer(net, lr=2e-4, dtype=torch.bfloat16 if args.dtype == "bf16" else None,
+                                  loss_fn=polydet_l1_iou_loss if iou else polydet_l1_loss)
+    batch = synthetic_batch(args.batch, args.height, args.width, device="cuda", seed=1000 + rank, rep="polar" if iou else "cartesian")
     batch["input"] = batch["input"].contiguous(memory_format=torch.channels_last)
 
     def barrier():
@@ -67,7 +76,8 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t)
     if rank == 0:
-        print(json.dumps(dict(metric="polydet dla_34 training images/s (1024x512 crops, focal + L1, Adam, data-parallel)",
+        print(json.dumps(dict(metric=f"polydet dla_34 training images/s (1024x512 crops, focal + {'L1 + polygon IoU (polar)' if iou else 'L1'}, Adam, data-parallel)",
+                              poly_loss=args.poly_loss, poly_iou_launches=_launches("poly_iou"),
                               value=world * args.batch * args.steps / (ms / 1000.0), unit="images/s", n_gpus=world,
                               ms_per_step=ms / args.steps, batch_per_gpu=args.batch, dtype=args.dtype, dcn_path=args.dcn_path,
                               loss_first=losses[0], loss_last=losses[-1], scaling="weak", data="synthetic")), flush=True)
