@@ -24,6 +24,7 @@ EXPORTED_SYMBOLS = (
     "cpoly_idaup_upsample_forward",
     "cpoly_dcn_backward_workspace_bytes", "cpoly_dcn_backward", "cpoly_decode_workspace_bytes", "cpoly_decode",
     "cpoly_rasterise_workspace_bytes", "cpoly_rasterise", "cpoly_poly_iou_forward", "cpoly_poly_iou_backward",
+    "cpoly_stem_pack_weights", "cpoly_stem_conv7x7_forward", "cpoly_maxpool2x2_nhwc_forward",
 )
 
 
@@ -73,9 +74,18 @@ class PolyIouArgs(Structure):
         ("dpred", c_void_p), ("status", c_void_p), ("stats", c_void_p), ("grad_loss", c_void_p), ("grad_poly", Tensor4)]
 
 
+class StemArgs(Structure):
+    _fields_ = [(n, c_int32) for n in ("B", "H", "W", "in_dtype", "out_dtype", "relu")] + [
+        ("x", Tensor4), ("weight_packed", c_void_p), ("bias", c_void_p), ("y", c_void_p)]
+
+
+class MaxPoolArgs(Structure):
+    _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "dtype", "reserved0")] + [("x", c_void_p), ("y", c_void_p)]
+
+
 _lib = None
 # kernels launched by the shims since import (our kernels only; bench.py reports it as gpu_launches)
-LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "decode": 0, "rasterise": 0, "poly_iou": 0}
+LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "decode": 0, "rasterise": 0, "poly_iou": 0, "stem": 0, "maxpool": 0}
 
 
 def lib():
@@ -118,7 +128,13 @@ def lib():
         L.cpoly_poly_iou_forward.argtypes = [POINTER(PolyIouArgs), c_void_p]
         L.cpoly_poly_iou_backward.restype = c_int32
         L.cpoly_poly_iou_backward.argtypes = [POINTER(PolyIouArgs), c_void_p]
-        if L.cpoly_abi_version() != 5:
+        L.cpoly_stem_pack_weights.restype = c_int32
+        L.cpoly_stem_pack_weights.argtypes = [c_void_p, c_int32, c_void_p, c_void_p]
+        L.cpoly_stem_conv7x7_forward.restype = c_int32
+        L.cpoly_stem_conv7x7_forward.argtypes = [POINTER(StemArgs), c_void_p]
+        L.cpoly_maxpool2x2_nhwc_forward.restype = c_int32
+        L.cpoly_maxpool2x2_nhwc_forward.argtypes = [POINTER(MaxPoolArgs), c_void_p]
+        if L.cpoly_abi_version() != 6:
             raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
         _lib = L
     return _lib

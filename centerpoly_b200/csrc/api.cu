@@ -214,4 +214,30 @@ int cpoly_poly_iou_backward(const cpoly_poly_iou_args* a, cpoly_stream_t stream)
   return poly_iou_backward_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int cpoly_stem_pack_weights(const void* weight, int32_t weight_dtype, void* packed, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(weight && packed, CPOLY_EINVAL, "NULL pointer");
+  CPOLY_REQUIRE(weight_dtype == CPOLY_F32 || weight_dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", weight_dtype);
+  return stem_pack_weights_launch(weight, weight_dtype, packed, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int cpoly_stem_conv7x7_forward(const cpoly_stem_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->B <= 65535 && a->H > 0 && a->W > 0, CPOLY_EINVAL, "bad stem dims");
+  CPOLY_REQUIRE((a->in_dtype == CPOLY_F32 || a->in_dtype == CPOLY_BF16) && (a->out_dtype == CPOLY_F32 || a->out_dtype == CPOLY_BF16),
+                CPOLY_EINVAL, "unsupported dtype");
+  CPOLY_REQUIRE(a->x.ptr && a->weight_packed && a->y, CPOLY_EINVAL, "NULL pointer");
+  CPOLY_REQUIRE((reinterpret_cast<uintptr_t>(a->y) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->weight_packed) & 3) == 0, CPOLY_EINVAL, "y must be 16-byte aligned");
+  if (a->B == 0) return CPOLY_OK;
+  return stem_conv_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int cpoly_maxpool2x2_nhwc_forward(const cpoly_maxpool_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->C > 0 && a->H >= 2 && a->W >= 2, CPOLY_EINVAL, "bad max-pool dims");
+  CPOLY_REQUIRE(a->dtype == CPOLY_F32 || a->dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", a->dtype);
+  CPOLY_REQUIRE((a->C * (a->dtype == CPOLY_BF16 ? 2 : 4)) % 16 == 0, CPOLY_EUNSUPPORTED, "C * element size must be a multiple of 16 bytes");
+  CPOLY_REQUIRE(a->x && a->y && (reinterpret_cast<uintptr_t>(a->x) & 15) == 0 && (reinterpret_cast<uintptr_t>(a->y) & 15) == 0, CPOLY_EINVAL, "x / y must be 16-byte aligned");
+  return maxpool2x2_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

@@ -137,4 +137,7 @@ size_t raster_workspace_bytes(int B, int K);
 int raster_launch(const cpoly_raster_args& a, cudaStream_t stream);
 int poly_iou_forward_launch(const cpoly_poly_iou_args& a, cudaStream_t stream);
 int poly_iou_backward_launch(const cpoly_poly_iou_args& a, cudaStream_t stream);
+int stem_pack_weights_launch(const void* w, int w_dtype, void* out, cudaStream_t stream);
+int stem_conv_launch(const cpoly_stem_args& a, cudaStream_t stream);
+int maxpool2x2_launch(const cpoly_maxpool_args& a, cudaStream_t stream);
 }  // namespace cpoly

@@ -222,6 +222,43 @@ def pad_stem_input_channels(model: nn.Module, multiple: int = 8) -> int:
     return 3
 
 
+def fuse_stem(model: nn.Module) -> int:
+    """Conv2d(3,16,7,1,3) (BN folded) -> ReLU of ``DLA.base_layer`` (pose_dla_dcn.py:231-236) as ONE kernel of ours
+    (centerpoly_b200/backbone.py).  bf16 models only: the kernel multiplies in bf16 (fp32 accumulation), which is what
+    a bf16 model does to that convolution anyway.  Returns the number of rewritten sites."""
+    from .backbone import StemConv7x7, stem_eligible
+    n = 0
+    for m in model.modules():
+        if not isinstance(m, nn.Sequential):
+            continue
+        keys = list(m._modules.keys())
+        for i, a in enumerate(keys):
+            c = m._modules[a]
+            if not (stem_eligible(c) and c.weight.is_cuda and c.weight.dtype == torch.bfloat16):
+                continue
+            j = i + 1
+            while j < len(keys) and isinstance(m._modules[keys[j]], nn.Identity):
+                j += 1
+            if j < len(keys) and isinstance(m._modules[keys[j]], nn.ReLU):
+                m._modules[a] = StemConv7x7(c, relu=True)
+                m._modules[keys[j]] = nn.Identity()
+                n += 1
+    return n
+
+
+def fuse_maxpool(model: nn.Module) -> int:
+    """nn.MaxPool2d(2, stride=2) (Tree.downsample / project, pose_dla_dcn.py:201,262) -> our NHWC kernel."""
+    from .backbone import MaxPool2x2
+    n = 0
+    for parent in model.modules():
+        for name, c in list(parent._modules.items()):
+            if (type(c) is nn.MaxPool2d and c.kernel_size in (2, (2, 2)) and c.stride in (2, (2, 2)) and c.padding in (0, (0, 0)) and
+                    c.dilation in (1, (1, 1)) and not c.ceil_mode and not c.return_indices):
+                parent._modules[name] = MaxPool2x2()
+                n += 1
+    return n
+
+
 def optimize_for_inference(model: nn.Module, dtype: torch.dtype | None = None) -> dict:
     """Apply every rewrite; the model must be in eval mode and on its CUDA device (load the checkpoint first: the
     folded BatchNorm parameters leave the state_dict).  ``dtype`` (e.g. torch.bfloat16) casts the model after the
@@ -232,5 +269,8 @@ def optimize_for_inference(model: nn.Module, dtype: torch.dtype | None = None) -
         stats = dict(deform_convs=fuse_deform_convs(model), upsamplers=fuse_idaup(model), conv_bn=fold_conv_bn(model))
         if dtype is not None:
             model.to(dtype)
+        p = next(model.parameters())
+        stats["stem"] = fuse_stem(model) if p.is_cuda else 0
+        stats["maxpool"] = fuse_maxpool(model) if p.is_cuda and p.dtype in (torch.bfloat16, torch.float32) else 0
         stats["cudnn_fused"] = fuse_backbone_cudnn(model)
     return stats

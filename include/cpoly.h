@@ -27,6 +27,9 @@
  *                           :909-910 (`WeilPolygonClipper` :373-628, `area` :25-41), including the
  *                           `_transpose_and_gather_feat` of :855 and, in backward, what autograd does with the
  *                           reference's per-object graph.
+ *   cpoly_stem_conv7x7_forward (+ cpoly_stem_pack_weights) <- `DLA.base_layer` = Conv2d(3,16,7,1,3) + BatchNorm2d + ReLU,
+ *                           src/lib/models/networks/pose_dla_dcn.py:231-236,289 (BN folded by the caller, eval mode).
+ *   cpoly_maxpool2x2_nhwc_forward <- `Tree.downsample` / `project` = nn.MaxPool2d(2, stride=2), pose_dla_dcn.py:201,207,262.
  *
  * Ownership: the caller allocates every input, output and workspace in device memory and passes raw
  * device pointers; the library allocates nothing, keeps no global state and never synchronises the
@@ -50,7 +53,7 @@
 extern "C" {
 #endif
 
-#define CPOLY_ABI_VERSION 5
+#define CPOLY_ABI_VERSION 6
 
 /* element types */
 #define CPOLY_F32 0
@@ -261,6 +264,35 @@ typedef struct {
 
 int cpoly_poly_iou_forward(const cpoly_poly_iou_args* args, cpoly_stream_t stream);
 int cpoly_poly_iou_backward(const cpoly_poly_iou_args* args, cpoly_stream_t stream);
+
+/* ------------------------------------------------------------------- backbone stem and max-pool */
+
+#define CPOLY_STEM_PACKED_BYTES (16 * 224 * 2)
+
+typedef struct {
+  int32_t B, H, W;
+  int32_t in_dtype;   /* element type of x: CPOLY_F32 | CPOLY_BF16 (rounded to bf16 on load, like autocast) */
+  int32_t out_dtype;  /* element type of y */
+  int32_t relu;
+  cpoly_tensor4 x;    /* (B,3,H,W), any strides */
+  const void* weight_packed; /* CPOLY_STEM_PACKED_BYTES from cpoly_stem_pack_weights */
+  const float* bias;  /* (16) fp32 (folded BatchNorm shift) or NULL */
+  void* y;            /* (B,16,H,W) channels_last contiguous (NHWC physical) */
+} cpoly_stem_args;
+
+/* weight: (16,3,7,7) contiguous, fp32 or bf16 -> [16][224] bf16, k = ky*32 + kx*4 + c */
+int cpoly_stem_pack_weights(const void* weight, int32_t weight_dtype, void* packed, cpoly_stream_t stream);
+int cpoly_stem_conv7x7_forward(const cpoly_stem_args* args, cpoly_stream_t stream);
+
+typedef struct {
+  int32_t B, C, H, W; /* input (B,C,H,W) channels_last contiguous; output (B,C,H/2,W/2) channels_last contiguous */
+  int32_t dtype;      /* C * sizeof(element) must be a multiple of 16 */
+  int32_t reserved0;
+  const void* x;
+  void* y;
+} cpoly_maxpool_args;
+
+int cpoly_maxpool2x2_nhwc_forward(const cpoly_maxpool_args* args, cpoly_stream_t stream);
 
 #ifdef __cplusplus
 }
