@@ -42,6 +42,19 @@ def install_decode() -> None:
             mod.polydet_decode = polydet_decode
 
 
+def install_poly_loss() -> None:
+    """Rebind ``PolyLoss`` where the reference's trainer looks it up (``from models.losses import ... PolyLoss``,
+    src/lib/trains/polydet.py:10-12; constructed at :32).  Call it BEFORE ``PolydetLoss`` is instantiated.  Importing
+    ``models.losses`` needs the reference's own dependencies (matplotlib, seaborn at losses.py:18-19)."""
+    from .poly_loss import PolyLoss
+    import importlib
+
+    importlib.import_module("models.losses").PolyLoss = PolyLoss
+    mod = sys.modules.get("trains.polydet")
+    if mod is not None and hasattr(mod, "PolyLoss"):
+        mod.PolyLoss = PolyLoss
+
+
 def install(reference_src_lib: str | None = None) -> None:
     install_dcn_overlay(reference_src_lib)
     if reference_src_lib:

@@ -26,7 +26,9 @@ def test_struct_layouts_match_header(tmp_path):
     import subprocess
     from centerpoly_b200 import _lib
     names = {"cpoly_tensor4": _lib.Tensor4, "cpoly_dcn_fwd_args": _lib.DcnFwdArgs, "cpoly_dcn_bwd_args": _lib.DcnBwdArgs,
-             "cpoly_upsample_args": _lib.UpsampleArgs, "cpoly_decode_args": _lib.DecodeArgs}
+             "cpoly_upsample_args": _lib.UpsampleArgs, "cpoly_decode_args": _lib.DecodeArgs,
+             "cpoly_raster_args": _lib.RasterArgs, "cpoly_poly_iou_args": _lib.PolyIouArgs, "cpoly_stem_args": _lib.StemArgs,
+             "cpoly_maxpool_args": _lib.MaxPoolArgs}
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include "cpoly.h"\nint main(void){' +
                    "".join(f'printf("{n} %zu\\n", sizeof({n}));' for n in names) + "return 0;}\n")
