@@ -22,7 +22,8 @@ namespace {
 
 constexpr int ST = 32;              // output tile: ST x ST pixels
 constexpr int WIN_H = ST + 6;       // rows y-3 .. y+ST+2
-constexpr int WIN_W = ST + 8;       // cols x-3 .. x+ST+4 (kx = 7 has zero weights but is read)
+constexpr int WIN_W = ST + 12;      // cols x-4 .. x+ST+7: starts on a 16-byte boundary of an fp32 NHWC row (kx = 7 has zero weights but is read)
+constexpr int WIN_X0 = 4;           // window column of the tile's first output column
 constexpr int STEM_K = 224, STEM_N = 16;
 
 __device__ __forceinline__ void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
@@ -43,16 +44,41 @@ __global__ void __launch_bounds__(256) stem_conv7x7_kernel(cpoly_tensor4 x, int 
   __shared__ __align__(16) __nv_bfloat16 wsm[STEM_N][STEM_K + 8];   // +8: rows land on different banks
   const int b = blockIdx.z, ty0 = blockIdx.y * ST, tx0 = blockIdx.x * ST;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int e = tid; e < STEM_N * STEM_K; e += 256) wsm[e / STEM_K][e % STEM_K] = wpk[e];
-  // frame window -> bf16, zero outside the image (the conv's zero padding) and in the 4th channel
-  for (int e = tid; e < WIN_H * WIN_W * 3; e += 256) {
-    const int r = e / (WIN_W * 3), xc = e - r * (WIN_W * 3), cx = xc / 3, c = xc - cx * 3;
-    const int yy = ty0 - 3 + r, xx = tx0 - 3 + cx;
-    float v = 0.0f;
-    if (yy >= 0 && yy < H && xx >= 0 && xx < W) v = ld_dyn(x.ptr, (int64_t)b * x.sb + (int64_t)c * x.sc + (int64_t)yy * x.sh + (int64_t)xx * x.sw, in_dtype);
-    win[r][cx][c] = __float2bfloat16_rn(v);
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(wpk);                    // 16 rows x 28 uint4
+    for (int e = tid; e < STEM_N * (STEM_K / 8); e += 256)
+      *reinterpret_cast<uint4*>(&wsm[e / (STEM_K / 8)][(e % (STEM_K / 8)) * 8]) = __ldg(src + e);
   }
+  // frame window -> bf16, zero outside the image (the conv's zero padding) and in the 4th channel
   for (int e = tid; e < WIN_H * WIN_W; e += 256) win[e / WIN_W][e % WIN_W][3] = __float2bfloat16_rn(0.0f);
+  const int wx0 = tx0 - WIN_X0;
+  const bool fast = in_dtype == CPOLY_F32 && x.sc == 1 && x.sw == 3 && (x.sh & 3) == 0 && (x.sb & 3) == 0 && wx0 >= 0 && wx0 + WIN_W <= W &&
+                    (reinterpret_cast<uintptr_t>(x.ptr) & 15) == 0;
+  if (fast) {
+    // fp32 channels_last frame, interior columns: a window row is WIN_W*3 = 132 contiguous floats = 33 aligned float4
+    constexpr int V = WIN_W * 3 / 4;
+    const float* xb = reinterpret_cast<const float*>(x.ptr) + (int64_t)b * x.sb + (int64_t)wx0 * 3;
+    for (int e = tid; e < WIN_H * V; e += 256) {
+      const int r = e / V, j = e - r * V;
+      const int yy = ty0 - 3 + r;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (yy >= 0 && yy < H) v = __ldg(reinterpret_cast<const float4*>(xb + (int64_t)yy * x.sh) + j);
+      const float f[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int fl = 4 * j + q, px = fl / 3;
+        win[r][px][fl - 3 * px] = __float2bfloat16_rn(f[q]);
+      }
+    }
+  } else {
+    for (int e = tid; e < WIN_H * WIN_W * 3; e += 256) {
+      const int r = e / (WIN_W * 3), xc = e - r * (WIN_W * 3), cx = xc / 3, c = xc - cx * 3;
+      const int yy = ty0 - 3 + r, xx = wx0 + cx;
+      float v = 0.0f;
+      if (yy >= 0 && yy < H && xx >= 0 && xx < W) v = ld_dyn(x.ptr, (int64_t)b * x.sb + (int64_t)c * x.sc + (int64_t)yy * x.sh + (int64_t)xx * x.sw, in_dtype);
+      win[r][cx][c] = __float2bfloat16_rn(v);
+    }
+  }
   __syncthreads();
 
   const int g = lane >> 2, t = lane & 3;
@@ -80,7 +106,7 @@ __global__ void __launch_bounds__(256) stem_conv7x7_kernel(cpoly_tensor4 x, int 
     for (int ks = 0; ks < 14; ++ks) {
       const int ky = ks >> 1, half = ks & 1;
       // k = half*16 + 2t (+8): offset in bf16 elements from the window pixel (row+ky, col0+g) channel 0
-      const __nv_bfloat16* p0 = &win[row + ky][col0 + g][0] + half * 16 + 2 * t;
+      const __nv_bfloat16* p0 = &win[row + ky][col0 + g + WIN_X0 - 3][0] + half * 16 + 2 * t;
       uint32_t a[4];
       a[0] = *reinterpret_cast<const uint32_t*>(p0);
       a[1] = *reinterpret_cast<const uint32_t*>(p0 + 8 * 4);

@@ -430,15 +430,17 @@ __global__ void __launch_bounds__(DNT) decode_threshold_kernel(DecodeParams p) {
 // Only the items whose best peak reaches the image's threshold bin are re-scanned (about K + one bin's worth of peaks
 // per image lie there), so this pass touches a few percent of the heat map instead of all of it again.
 template <typename T>
-__global__ void __launch_bounds__(DNT, 3) decode_collect_kernel(DecodeParams p) {
+__global__ void __launch_bounds__(DNT, 3) decode_collect_kernel(DecodeParams p, int ipw) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t total = (int64_t)p.nb * p.items_per_image;
-  // a warp looks at 32 consecutive items at once (one per lane: coalesced reads of item_max) and re-scans the few
-  // whose best peak reaches their image's threshold bin
-  for (int64_t base = ((int64_t)blockIdx.x * DWARPS + warp) * 32; base < total; base += (int64_t)gridDim.x * DWARPS * 32) {
+  // a warp looks at `ipw` (<= 32) consecutive items at once (one per lane: coalesced reads of item_max) and re-scans
+  // the few whose best peak reaches their image's threshold bin.  ipw shrinks with the batch so that a single frame
+  // (1024 items) still spreads over ~1000 warps: the re-scans of one warp are serial, and a flat heat map (bf16
+  // logits of an untrained network) can qualify most items.
+  for (int64_t base = ((int64_t)blockIdx.x * DWARPS + warp) * ipw; base < total; base += (int64_t)gridDim.x * DWARPS * ipw) {
     const int64_t mine = base + lane;
     bool need = false;
-    if (mine < total) {
+    if (lane < ipw && mine < total) {
       const int lb = (int)(mine / p.items_per_image);
       const float mx = __uint_as_float(__ldcg(p.item_max + (int64_t)p.b0 * p.items_per_image + mine));
       need = mx > 0.f && score_bin(mx) >= __ldcg(p.tbin + p.b0 + lb);
@@ -721,10 +723,13 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
     if (bf) decode_threshold_kernel<__nv_bfloat16><<<(unsigned)a.B, DNT, 0, stream>>>(p);
     else decode_threshold_kernel<float><<<(unsigned)a.B, DNT, 0, stream>>>(p);
     if (int rc = check_launch("decode_threshold_kernel")) return rc;
-    int64_t cctas = (items + 32 * DWARPS - 1) / (32 * DWARPS);
+    const int64_t warps_wanted = (int64_t)3 * sms * DWARPS;
+    int ipw = (int)((items + warps_wanted - 1) / warps_wanted);
+    ipw = ipw < 1 ? 1 : (ipw > 32 ? 32 : ipw);
+    int64_t cctas = (items + (int64_t)ipw * DWARPS - 1) / ((int64_t)ipw * DWARPS);
     if (cctas > 3 * sms) cctas = 3 * sms;
-    if (bf) decode_collect_kernel<__nv_bfloat16><<<(unsigned)cctas, DNT, 0, stream>>>(p);
-    else decode_collect_kernel<float><<<(unsigned)cctas, DNT, 0, stream>>>(p);
+    if (bf) decode_collect_kernel<__nv_bfloat16><<<(unsigned)cctas, DNT, 0, stream>>>(p, ipw);
+    else decode_collect_kernel<float><<<(unsigned)cctas, DNT, 0, stream>>>(p, ipw);
     if (int rc = check_launch("decode_collect_kernel")) return rc;
   }
   if (bf) decode_select_kernel<__nv_bfloat16><<<(unsigned)a.B, DNT, 0, stream>>>(p);
