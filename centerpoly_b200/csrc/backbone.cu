@@ -94,27 +94,37 @@ __global__ void __launch_bounds__(256) stem_conv7x7_kernel(cpoly_tensor4 x, int 
   const float bz0 = bias ? bias[2 * t] : 0.f, bz1 = bias ? bias[2 * t + 1] : 0.f;
   const float bz8 = bias ? bias[8 + 2 * t] : 0.f, bz9 = bias ? bias[9 + 2 * t] : 0.f;
 
-  // warp w owns rows 4w .. 4w+3 of the tile; an m16 tile = 16 consecutive pixels of one row
-  for (int mt = 0; mt < 8; ++mt) {
-    const int row = warp * 4 + (mt >> 1), col0 = (mt & 1) * 16;
-    float acc[2][4];
+  // warp w owns rows 4w .. 4w+3 of the tile; an m16 tile = 16 consecutive pixels of one row.  Two rows are in
+  // flight at once (4 independent accumulator chains per warp: the MMA chain latency, not issue, is the limit)
+  for (int mp = 0; mp < 4; ++mp) {
+    const int col0 = (mp & 1) * 16, rbase = warp * 4 + (mp >> 1) * 2;
+    float accs[2][2][4];
 #pragma unroll
-    for (int nh = 0; nh < 2; ++nh)
+    for (int u = 0; u < 2; ++u)
 #pragma unroll
-      for (int e = 0; e < 4; ++e) acc[nh][e] = 0.0f;
+      for (int nh = 0; nh < 2; ++nh)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) accs[u][nh][e] = 0.0f;
 #pragma unroll
     for (int ks = 0; ks < 14; ++ks) {
       const int ky = ks >> 1, half = ks & 1;
-      // k = half*16 + 2t (+8): offset in bf16 elements from the window pixel (row+ky, col0+g) channel 0
-      const __nv_bfloat16* p0 = &win[row + ky][col0 + g + WIN_X0 - 3][0] + half * 16 + 2 * t;
-      uint32_t a[4];
-      a[0] = *reinterpret_cast<const uint32_t*>(p0);
-      a[1] = *reinterpret_cast<const uint32_t*>(p0 + 8 * 4);
-      a[2] = *reinterpret_cast<const uint32_t*>(p0 + 8);
-      a[3] = *reinterpret_cast<const uint32_t*>(p0 + 8 * 4 + 8);
-      mma_bf16(acc[0], a, bf[ks][0][0], bf[ks][0][1]);
-      mma_bf16(acc[1], a, bf[ks][1][0], bf[ks][1][1]);
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        // k = half*16 + 2t (+8): offset in bf16 elements from the window pixel (row+ky, col0+g) channel 0
+        const __nv_bfloat16* p0 = &win[rbase + u + ky][col0 + g + WIN_X0 - 3][0] + half * 16 + 2 * t;
+        uint32_t a[4];
+        a[0] = *reinterpret_cast<const uint32_t*>(p0);
+        a[1] = *reinterpret_cast<const uint32_t*>(p0 + 8 * 4);
+        a[2] = *reinterpret_cast<const uint32_t*>(p0 + 8);
+        a[3] = *reinterpret_cast<const uint32_t*>(p0 + 8 * 4 + 8);
+        mma_bf16(accs[u][0], a, bf[ks][0][0], bf[ks][0][1]);
+        mma_bf16(accs[u][1], a, bf[ks][1][0], bf[ks][1][1]);
+      }
     }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+    const int row = rbase + u;
+    const float (&acc)[2][4] = accs[u];
     // epilogue: bias, ReLU; lane (g,t) holds channels {2t,2t+1} and {8+2t,9+2t} of pixels g and g+8
     float v[2][4];   // [pixel g | g+8][ch 2t, 2t+1, 8+2t, 9+2t]
     v[0][0] = acc[0][0] + bz0; v[0][1] = acc[0][1] + bz1; v[0][2] = acc[1][0] + bz8; v[0][3] = acc[1][1] + bz9;
@@ -145,6 +155,7 @@ __global__ void __launch_bounds__(256) stem_conv7x7_kernel(cpoly_tensor4 x, int 
           *reinterpret_cast<float2*>(o + 8 + 2 * t) = make_float2(v[i][2], v[i][3]);
         }
       }
+    }
     }
   }
 }
