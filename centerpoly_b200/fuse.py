@@ -222,6 +222,54 @@ def pad_stem_input_channels(model: nn.Module, multiple: int = 8) -> int:
     return 3
 
 
+class _Conv1x1Gemm(nn.Module):
+    """A biased 1x1 Conv2d on a channels_last tensor as ONE cuBLASLt GEMM with the bias in its epilogue
+    (``F.conv2d`` runs cuDNN + a separate bias-add kernel here).  Output channels are padded to a multiple of 8 so the
+    bf16 rows stay 16-byte aligned; the result is returned as a (B,Cout,H,W) view of that buffer (the decode reads any
+    strides).  Keeps ``conv`` as a sub-module: same state_dict keys; the padded copies are version-keyed caches."""
+
+    def __init__(self, conv: nn.Conv2d):
+        super().__init__()
+        self.conv = conv
+        self._cache = None
+
+    def _wb(self):
+        w, b = self.conv.weight, self.conv.bias
+        key = (w._version, w.data_ptr(), w.dtype, w.device, b._version, b.data_ptr())
+        if self._cache is None or self._cache[0] != key:
+            co, ci = w.shape[0], w.shape[1]
+            cp = (co + 7) // 8 * 8
+            wt = torch.zeros((ci, cp), dtype=w.dtype, device=w.device)
+            wt[:, :co] = w.detach().reshape(co, ci).t()
+            bp = torch.zeros((cp,), dtype=w.dtype, device=w.device)
+            bp[:co] = b.detach()
+            self._cache = (key, wt, bp)
+        return self._cache[1], self._cache[2]
+
+    def forward(self, x):
+        if not (x.is_cuda and x.is_contiguous(memory_format=torch.channels_last)) or torch.is_grad_enabled():
+            return self.conv(x)
+        wt, bp = self._wb()
+        B, C, H, W = x.shape
+        y = torch.addmm(bp, x.permute(0, 2, 3, 1).reshape(B * H * W, C), wt)
+        return y.view(B, H, W, -1).permute(0, 3, 1, 2)[:, :self.conv.out_channels]
+
+
+def fuse_head_1x1(model: nn.Module) -> int:
+    """The closing 1x1 convolutions of the heads (pose_dla_dcn.py:445-468: Conv3x3 -> ReLU -> Conv1x1 with bias)."""
+    n = 0
+    for m in model.modules():
+        if not isinstance(m, nn.Sequential) or len(m) < 2:
+            continue
+        keys = list(m._modules.keys())
+        c = m._modules[keys[-1]]
+        if (type(c) is nn.Conv2d and c.kernel_size == (1, 1) and c.stride == (1, 1) and c.padding == (0, 0) and c.groups == 1 and
+                c.bias is not None and c.weight.is_cuda and c.in_channels % 8 == 0):
+            m._modules[keys[-1]] = _Conv1x1Gemm(c)
+            n += 1
+    return n
+
+
 def fuse_stem(model: nn.Module) -> int:
     """Conv2d(3,16,7,1,3) (BN folded) -> ReLU of ``DLA.base_layer`` (pose_dla_dcn.py:231-236) as ONE kernel of ours
     (centerpoly_b200/backbone.py).  bf16 models only: the kernel multiplies in bf16 (fp32 accumulation), which is what
@@ -273,4 +321,5 @@ def optimize_for_inference(model: nn.Module, dtype: torch.dtype | None = None) -
         stats["stem"] = fuse_stem(model) if p.is_cuda else 0
         stats["maxpool"] = fuse_maxpool(model) if p.is_cuda and p.dtype in (torch.bfloat16, torch.float32) else 0
         stats["cudnn_fused"] = fuse_backbone_cudnn(model)
+        stats["head_gemm"] = fuse_head_1x1(model) if p.is_cuda and p.dtype == torch.bfloat16 else 0
     return stats

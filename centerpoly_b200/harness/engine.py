@@ -46,6 +46,7 @@ class PolydetEngine:
             # (fuse.pad_stem_input_channels exists, but on this cuDNN the 8-channel bf16 stem is 2x SLOWER than the
             #  3-channel one - tools/stem_probe.py: 853 us vs 412 us - so the stem keeps its 3 input channels)
         self.optimize = optimize
+        self._stem_direct = bool(self.fusion and self.fusion.get("stem"))
         self.net = net
         self.n_dcn_per_frame = sum(1 for m in net.modules() if hasattr(m, "conv_offset_mask"))
         if optimize:
@@ -89,10 +90,11 @@ class PolydetEngine:
     def _step(self, x):
         """One frame: network -> sigmoid -> decode (the body of PolydetDetector.process)."""
         with torch.no_grad(), self._autocast():
-            if self.optimize:
-                # fp32 frame -> persistent (B,8,H,W) network input (channels 3..7 stay zero): one conversion kernel
+            if self.optimize and not self._stem_direct:
+                # fp32 frame -> persistent network input in the model dtype: one conversion kernel
                 self._xin[:, :3].copy_(x)
                 x = self._xin
+            # (with our stem kernel the fp32 channels_last frame is read directly and rounded to bf16 on load)
             out = self.net(x)[-1]
             if self.optimize:   # the sigmoid of detectors/polydet.py:28 is fused into the decode kernel
                 return cdecode.polydet_decode_from_logits(out["hm"], out["poly"], out["pseudo_depth"], reg=out.get("reg"),

@@ -63,3 +63,18 @@ def test_engine_uses_the_kernels():
     from centerpoly_b200.harness.engine import PolydetEngine
     eng = PolydetEngine(height=128, width=256, dtype="bf16")
     assert eng.fusion["stem"] == 1 and eng.fusion["maxpool"] >= 4, eng.fusion
+
+
+@pytest.mark.parametrize("cout", [1, 2, 8, 64])
+def test_head_1x1_gemm_matches_conv(cout):
+    from centerpoly_b200.fuse import _Conv1x1Gemm
+    torch.manual_seed(cout)
+    conv = torch.nn.Conv2d(256, cout, 1, bias=True).cuda().bfloat16()
+    x = torch.randn(2, 256, 24, 40, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    m = _Conv1x1Gemm(conv)
+    with torch.no_grad():
+        y = m(x)
+        want = F.conv2d(x.float(), conv.weight.float(), conv.bias.float())
+    assert tuple(y.shape) == (2, cout, 24, 40) and y.dtype == torch.bfloat16
+    gate(y.float().cpu().numpy(), want.cpu().numpy(), 1e-2, "1x1 head as GEMM")
+    assert list(m.state_dict().keys()) == ["conv.weight", "conv.bias"]
