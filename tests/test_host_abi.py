@@ -102,3 +102,22 @@ def test_overlay_resolves_reference_import():
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr[-2000:]
     assert "ok 16" in out.stdout
+
+
+def test_poly_loss_mirror_rejects_what_it_does_not_build():
+    """Host-side contract of the PolyLoss mirror (no GPU needed): unsupported options raise at construction, CPU
+    tensors raise instead of falling back."""
+    import pytest
+    import torch
+    from centerpoly_b200.poly_loss import PolyLoss, poly_iou_loss
+
+    class Opt:
+        poly_loss, rep, poly_order = "iou", "polar", False
+    PolyLoss(Opt())
+    for attr, val in (("poly_order", True), ("poly_loss", "relu"), ("rep", "cartesian")):
+        o = type("O", (), dict(poly_loss="iou", rep="polar", poly_order=False))
+        setattr(o, attr, val)
+        with pytest.raises(NotImplementedError):
+            PolyLoss(o)
+    with pytest.raises(RuntimeError):
+        poly_iou_loss(torch.zeros(1, 16, 4, 4), torch.ones(1, 2), torch.zeros(1, 2, dtype=torch.int64), torch.zeros(1, 2, 16))
