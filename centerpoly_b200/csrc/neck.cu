@@ -7,6 +7,8 @@
 //
 // With kernel 2f and stride f exactly two input rows / columns contribute: iy1 = (oy + pad) / f with
 // ky = (oy + pad) % f, and iy0 = iy1 - 1 with ky + f.  HBM bound: algorithmic bytes = s * B*C*(H*W + [2] * Ho*Wo).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace cpoly {
@@ -51,6 +53,19 @@ template <> struct Vec<__nv_bfloat16, 8> {
     *reinterpret_cast<uint4*>(p) = q;
   }
 };
+
+template <typename T> __device__ __forceinline__ void unpack16(const uint4 q, float* v);
+template <> __device__ __forceinline__ void unpack16<float>(const uint4 q, float* v) {
+  v[0] = __uint_as_float(q.x); v[1] = __uint_as_float(q.y); v[2] = __uint_as_float(q.z); v[3] = __uint_as_float(q.w);
+}
+template <> __device__ __forceinline__ void unpack16<__nv_bfloat16>(const uint4 q, float* v) {
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    v[2 * j] = __uint_as_float(w[j] << 16);
+    v[2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+  }
+}
 
 // channels_last fast path: one thread per (output pixel, VEC-channel piece); pieces of a pixel are adjacent
 // threads, so loads and stores are 16-byte vectors over contiguous channels.
@@ -108,6 +123,81 @@ __global__ void __launch_bounds__(256) upsample_nhwc_kernel(UpParams p) {
   }
 }
 
+// channels_last, tap-major weights: one thread per (2x2 output quad, VEC-channel piece).  A quad whose origin has
+// the parity of pad shares its 2x2 input neighbourhood (f is even, so (o + pad) and (o + pad + 1) never straddle a
+// multiple of f): 4 input loads, one unpack and one set of index arithmetic serve 4 outputs - the one-pixel kernel
+// above is bound by instruction issue (57 % issue slots busy, 10 % of DRAM), not by bytes.
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256) upsample_nhwc_quad_kernel(UpParams p) {
+  const int pieces = p.C / VEC;
+  const int K = 2 * p.f, pad = p.f / 2, par = pad & 1;
+  const int qh = p.Ho / 2 + par, qw = p.Wo / 2 + par;          // Ho, Wo are even (f is)
+  const int64_t total = (int64_t)p.B * qh * qw * pieces;
+  const T* xg = reinterpret_cast<const T*>(p.x.ptr);
+  const T* sg = reinterpret_cast<const T*>(p.skip.ptr);
+  T* yg = reinterpret_cast<T*>(p.y.ptr);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int piece = (int)(i % pieces);
+    int t = (int)(i / pieces);
+    const int qx = t % qw; t /= qw;
+    const int qy = t % qh;
+    const int b = t / qh;
+    const int c0 = piece * VEC;
+    const int oy0 = 2 * qy - par, ox0 = 2 * qx - par;
+    const int iy1 = (oy0 + pad) / p.f, ky0 = (oy0 + pad) - iy1 * p.f;      // oy0 + pad >= 0
+    const int ix1 = (ox0 + pad) / p.f, kx0 = (ox0 + pad) - ix1 * p.f;
+    // every load of the quad is issued before anything is used: 8 x 16 bytes in flight per thread (with one output
+    // pixel and a grid-stride loop the kernel sat at 1.4 TB/s, bound by memory latency, not by bytes or issue)
+    uint4 xr[2][2], sr[2][2];
+    bool ok[2][2], oko[2][2];
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const int iy = iy1 - dy, ix = ix1 - dx;
+        ok[dy][dx] = iy >= 0 && iy < p.H && ix >= 0 && ix < p.W;
+        xr[dy][dx] = make_uint4(0u, 0u, 0u, 0u);
+        if (ok[dy][dx]) xr[dy][dx] = __ldg(reinterpret_cast<const uint4*>(xg + (int64_t)b * p.x.sb + (int64_t)iy * p.x.sh + (int64_t)ix * p.x.sw + c0));
+        const int oy = oy0 + dy, ox = ox0 + dx;
+        oko[dy][dx] = oy >= 0 && oy < p.Ho && ox >= 0 && ox < p.Wo;
+        sr[dy][dx] = make_uint4(0u, 0u, 0u, 0u);
+        if (sg && oko[dy][dx]) sr[dy][dx] = __ldg(reinterpret_cast<const uint4*>(sg + (int64_t)b * p.skip.sb + (int64_t)oy * p.skip.sh + (int64_t)ox * p.skip.sw + c0));
+      }
+    float v[2][2][VEC];
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) unpack16<T>(xr[dy][dx], v[dy][dx]);
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        if (!oko[r][q]) continue;
+        const int oy = oy0 + r, ox = ox0 + q;
+        float acc[VEC];
+        unpack16<T>(sr[r][q], acc);            // zeros when there is no skip tensor
+        // same tap order as the one-pixel kernel (dy, dx ascending): identical fp32 results
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx) {
+            if (!ok[dy][dx]) continue;
+            const float4* wp = reinterpret_cast<const float4*>(p.w + (int64_t)((ky0 + r + dy * p.f) * K + kx0 + q + dx * p.f) * p.C + c0);
+#pragma unroll
+            for (int j = 0; j < VEC / 4; ++j) {
+              const float4 w4 = __ldg(wp + j);
+              acc[4 * j] = fmaf(v[dy][dx][4 * j], w4.x, acc[4 * j]);
+              acc[4 * j + 1] = fmaf(v[dy][dx][4 * j + 1], w4.y, acc[4 * j + 1]);
+              acc[4 * j + 2] = fmaf(v[dy][dx][4 * j + 2], w4.z, acc[4 * j + 2]);
+              acc[4 * j + 3] = fmaf(v[dy][dx][4 * j + 3], w4.w, acc[4 * j + 3]);
+            }
+          }
+        Vec<T, VEC>::store(yg + (int64_t)b * p.y.sb + (int64_t)oy * p.y.sh + (int64_t)ox * p.y.sw + c0, acc);
+      }
+    }
+  }
+}
+
 // any strides / channel counts: one thread per output element
 template <typename T>
 __global__ void __launch_bounds__(256) upsample_generic_kernel(UpParams p) {
@@ -155,7 +245,14 @@ int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream) {
   const bool fast = a.C % vec == 0 && vec_ok(a.x, vec) && vec_ok(a.skip, vec) && vec_ok(a.y, vec);
   const int64_t total = (int64_t)a.B * p.Ho * p.Wo * (fast ? a.C / vec : a.C);
   const unsigned blocks = (unsigned)((total + 255) / 256 < 148 * 16 ? (total + 255) / 256 : 148 * 16);
-  if (fast) {
+  static const bool quad_on = [] { const char* e = getenv("CPOLY_UPSAMPLE_QUAD"); return !(e && e[0] == '0'); }();
+  if (quad_on && fast && a.weight_tap_major && a.f % 2 == 0 && (int64_t)a.B * (p.Ho / 2 + 1) * (p.Wo / 2 + 1) * (a.C / vec) < 0x7fffffffLL) {
+    const int par = (a.f / 2) & 1;
+    const int64_t quads = (int64_t)a.B * (p.Ho / 2 + par) * (p.Wo / 2 + par) * (a.C / vec);
+    const unsigned qblocks = (unsigned)((quads + 255) / 256);   // one quad per thread: every load of a wave in flight at once
+    if (bf) upsample_nhwc_quad_kernel<__nv_bfloat16, 8><<<qblocks, 256, 0, stream>>>(p);
+    else upsample_nhwc_quad_kernel<float, 4><<<qblocks, 256, 0, stream>>>(p);
+  } else if (fast) {
     if (bf) upsample_nhwc_kernel<__nv_bfloat16, 8><<<blocks, 256, 0, stream>>>(p);
     else upsample_nhwc_kernel<float, 4><<<blocks, 256, 0, stream>>>(p);
   } else {

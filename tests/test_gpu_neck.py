@@ -34,6 +34,13 @@ def test_idaup_upsample_vs_conv_transpose(f, dtype, layout):
     gate(got.float().cpu().numpy(), want.numpy(), tol, "up")
     got2 = idaup_upsample(xd, w.cuda(), f, sd)
     gate(got2.float().cpu().numpy(), (want + skip.double()).numpy(), tol, "up+skip")
+    # tap-major weights (what the IDAUpsample module passes): on channels_last this is the 2x2-quad kernel, which must
+    # give the same fp32 sums in the same order as the one-pixel kernel
+    wt = w.reshape(C, -1).t().contiguous().cuda()
+    got3 = idaup_upsample(xd, wt, f, sd, tap_major=True)
+    assert torch.equal(got3, got2)
+    got4 = idaup_upsample(xd, wt, f, tap_major=True)
+    assert torch.equal(got4, got)
 
 
 def test_idaup_upsample_odd_channels_generic_path():
