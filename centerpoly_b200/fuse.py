@@ -256,17 +256,18 @@ class _Conv1x1Gemm(nn.Module):
 
 
 def fuse_head_1x1(model: nn.Module) -> int:
-    """The closing 1x1 convolutions of the heads (pose_dla_dcn.py:445-468: Conv3x3 -> ReLU -> Conv1x1 with bias)."""
+    """Biased 1x1 convolutions inside ``nn.Sequential`` containers: the closing convolutions of the heads
+    (pose_dla_dcn.py:445-468: Conv3x3 -> ReLU -> Conv1x1 with bias) and, after BN folding, the ``project`` branches of
+    the DLA trees (:203-207: Conv1x1 -> BatchNorm2d).  F.conv2d runs these as cuDNN + a separate bias-add kernel."""
     n = 0
     for m in model.modules():
-        if not isinstance(m, nn.Sequential) or len(m) < 2:
+        if not isinstance(m, nn.Sequential):
             continue
-        keys = list(m._modules.keys())
-        c = m._modules[keys[-1]]
-        if (type(c) is nn.Conv2d and c.kernel_size == (1, 1) and c.stride == (1, 1) and c.padding == (0, 0) and c.groups == 1 and
-                c.bias is not None and c.weight.is_cuda and c.in_channels % 8 == 0):
-            m._modules[keys[-1]] = _Conv1x1Gemm(c)
-            n += 1
+        for key, c in list(m._modules.items()):
+            if (type(c) is nn.Conv2d and c.kernel_size == (1, 1) and c.stride == (1, 1) and c.padding == (0, 0) and c.groups == 1 and
+                    c.bias is not None and c.weight.is_cuda and c.in_channels % 8 == 0):
+                m._modules[key] = _Conv1x1Gemm(c)
+                n += 1
     return n
 
 
