@@ -21,7 +21,7 @@ PATH_AUTO, PATH_SIMT, PATH_TCGEN05 = 0, 1, 2
 EXPORTED_SYMBOLS = (
     "cpoly_abi_version", "cpoly_last_error", "cpoly_device_supports_tcgen05", "cpoly_dcn_tcgen05_eligible",
     "cpoly_dcn_packed_weight_bytes", "cpoly_dcn_pack_weights", "cpoly_dcn_forward_workspace_bytes", "cpoly_dcn_forward",
-    "cpoly_idaup_upsample_forward",
+    "cpoly_idaup_upsample_forward", "cpoly_idaup_upsample_backward",
     "cpoly_dcn_backward_workspace_bytes", "cpoly_dcn_backward", "cpoly_decode_workspace_bytes", "cpoly_decode",
     "cpoly_rasterise_workspace_bytes", "cpoly_rasterise", "cpoly_poly_iou_forward", "cpoly_poly_iou_backward",
     "cpoly_stem_pack_weights", "cpoly_stem_conv7x7_forward", "cpoly_maxpool2x2_nhwc_forward",
@@ -83,9 +83,14 @@ class MaxPoolArgs(Structure):
     _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "dtype", "reserved0")] + [("x", c_void_p), ("y", c_void_p)]
 
 
+class UpsampleBwdArgs(Structure):
+    _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "f", "dtype")] + [
+        ("x", Tensor4), ("gy", Tensor4), ("weight", c_void_p), ("gx", Tensor4), ("gweight", c_void_p)]
+
+
 _lib = None
 # kernels launched by the shims since import (our kernels only; bench.py reports it as gpu_launches)
-LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "decode": 0, "rasterise": 0, "poly_iou": 0, "stem": 0, "maxpool": 0}
+LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "upsample_bwd": 0, "decode": 0, "rasterise": 0, "poly_iou": 0, "stem": 0, "maxpool": 0}
 
 
 def lib():
@@ -134,7 +139,9 @@ def lib():
         L.cpoly_stem_conv7x7_forward.argtypes = [POINTER(StemArgs), c_void_p]
         L.cpoly_maxpool2x2_nhwc_forward.restype = c_int32
         L.cpoly_maxpool2x2_nhwc_forward.argtypes = [POINTER(MaxPoolArgs), c_void_p]
-        if L.cpoly_abi_version() != 6:
+        L.cpoly_idaup_upsample_backward.restype = c_int32
+        L.cpoly_idaup_upsample_backward.argtypes = [POINTER(UpsampleBwdArgs), c_void_p]
+        if L.cpoly_abi_version() != 7:
             raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
         _lib = L
     return _lib

@@ -240,4 +240,13 @@ int cpoly_maxpool2x2_nhwc_forward(const cpoly_maxpool_args* a, cpoly_stream_t st
   return maxpool2x2_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int cpoly_idaup_upsample_backward(const cpoly_upsample_bwd_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->C > 0 && a->H > 0 && a->W > 0 && a->f >= 2, CPOLY_EINVAL, "bad upsample dims");
+  CPOLY_REQUIRE(a->dtype == CPOLY_F32 || a->dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", a->dtype);
+  CPOLY_REQUIRE(a->x.ptr && a->gy.ptr && a->weight, CPOLY_EINVAL, "NULL pointer");
+  if (a->B == 0) return CPOLY_OK;
+  return idaup_upsample_backward_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

@@ -131,6 +131,7 @@ bool dcn_tc_dgrad_eligible(const cpoly_dcn_bwd_args& a);
 size_t dcn_tc_dgrad_workspace(const cpoly_dcn_bwd_args& a);
 int dcn_dgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream);
+int idaup_upsample_backward_launch(const cpoly_upsample_bwd_args& a, cudaStream_t stream);
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K);
 int decode_launch(const cpoly_decode_args& a, cudaStream_t stream);
 size_t raster_workspace_bytes(int B, int K);

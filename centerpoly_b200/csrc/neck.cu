@@ -198,6 +198,120 @@ __global__ void __launch_bounds__(256) upsample_nhwc_quad_kernel(UpParams p) {
   }
 }
 
+// ---- backward of the up-sampler (training: the reference's nn.ConvTranspose2d autograd; cuDNN runs the depthwise
+// weight gradient as `wgrad2d_grouped_direct_kernel` at ~1 ms per call and the data gradient as `dgrad2d_c1_k1_nhwc` at
+// ~0.5 ms: 17 % of the configs[3] training step).  channels_last, tap-major fp32 weights.
+// grad_x[b,c,iy,ix] = sum_{ky,kx} w[c,ky,kx] * gy[b,c, iy*f + ky - pad, ix*f + kx - pad]: one thread per (input pixel, piece)
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256) upsample_bwd_input_kernel(UpParams p, cpoly_tensor4 gy, cpoly_tensor4 gx) {
+  const int pieces = p.C / VEC;
+  const int64_t total = (int64_t)p.B * p.H * p.W * pieces;
+  const int K = 2 * p.f, pad = p.f / 2;
+  const T* gyp = reinterpret_cast<const T*>(gy.ptr);
+  T* gxp = reinterpret_cast<T*>(gx.ptr);
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int piece = (int)(i % pieces);
+  int t = (int)(i / pieces);
+  const int ix = t % p.W; t /= p.W;
+  const int iy = t % p.H;
+  const int b = t / p.H;
+  const int c0 = piece * VEC;
+  float acc[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) acc[j] = 0.f;
+  for (int ky = 0; ky < K; ++ky) {
+    const int oy = iy * p.f + ky - pad;
+    if (oy < 0 || oy >= p.Ho) continue;
+    for (int kx = 0; kx < K; ++kx) {
+      const int ox = ix * p.f + kx - pad;
+      if (ox < 0 || ox >= p.Wo) continue;
+      float g[VEC];
+      Vec<T, VEC>::load(gyp + (int64_t)b * gy.sb + (int64_t)oy * gy.sh + (int64_t)ox * gy.sw + c0, g);
+      const float4* wp = reinterpret_cast<const float4*>(p.w + (int64_t)(ky * K + kx) * p.C + c0);
+#pragma unroll
+      for (int j = 0; j < VEC / 4; ++j) {
+        const float4 w4 = __ldg(wp + j);
+        acc[4 * j] = fmaf(g[4 * j], w4.x, acc[4 * j]);
+        acc[4 * j + 1] = fmaf(g[4 * j + 1], w4.y, acc[4 * j + 1]);
+        acc[4 * j + 2] = fmaf(g[4 * j + 2], w4.z, acc[4 * j + 2]);
+        acc[4 * j + 3] = fmaf(g[4 * j + 3], w4.w, acc[4 * j + 3]);
+      }
+    }
+  }
+  Vec<T, VEC>::store(gxp + (int64_t)b * gx.sb + (int64_t)iy * gx.sh + (int64_t)ix * gx.sw + c0, acc);
+}
+
+// grad_w[(ky,kx), c] += sum over outputs of one phase (oy % f, ox % f): the 4 contributing taps are fixed per phase, so a
+// thread keeps 4 x VEC partial sums in registers over its share of the phase's pixels, then warp-shuffle + atomicAdd.
+// blockIdx.y = phase, blockIdx.x = pixel chunk; thread = (pixel lane, piece).  fp32 atomics: summation order varies
+// between runs at the 1e-7 level (as in cuDNN's own grouped weight gradient).
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256) upsample_bwd_weight_kernel(UpParams p, cpoly_tensor4 gy, float* __restrict__ gw, int px_per_block) {
+  const int pieces = p.C / VEC;                   // 8, 16 or 32 (power of two <= 32)
+  const int K = 2 * p.f, pad = p.f / 2;
+  const int py = blockIdx.y / p.f, pxp = blockIdx.y - py * p.f;
+  const int piece = threadIdx.x % pieces, plane = threadIdx.x / pieces, nlanes = 256 / pieces;
+  const int c0 = piece * VEC;
+  const int uy = (py + pad) / p.f, ky1 = (py + pad) - uy * p.f;     // iy1 = m + uy
+  const int ux = (pxp + pad) / p.f, kx1 = (pxp + pad) - ux * p.f;
+  const T* xg = reinterpret_cast<const T*>(p.x.ptr);
+  const T* gyp = reinterpret_cast<const T*>(gy.ptr);
+  const int64_t npix = (int64_t)p.B * p.H * p.W;                    // phase pixels (m, n) per image = H x W
+  const int64_t beg = (int64_t)blockIdx.x * px_per_block, end = beg + px_per_block < npix ? beg + px_per_block : npix;
+  float acc[2][2][VEC];
+#pragma unroll
+  for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+    for (int dx = 0; dx < 2; ++dx)
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) acc[dy][dx][j] = 0.f;
+  for (int64_t q = beg + plane; q < end; q += nlanes) {
+    int t = (int)q;
+    const int n = t % p.W; t /= p.W;
+    const int m = t % p.H;
+    const int b = t / p.H;
+    const int oy = m * p.f + py, ox = n * p.f + pxp;
+    float g[VEC];
+    Vec<T, VEC>::load(gyp + (int64_t)b * gy.sb + (int64_t)oy * gy.sh + (int64_t)ox * gy.sw + c0, g);
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy) {
+      const int iy = m + uy - dy;
+      if (iy < 0 || iy >= p.H) continue;
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const int ix = n + ux - dx;
+        if (ix < 0 || ix >= p.W) continue;
+        float v[VEC];
+        Vec<T, VEC>::load(xg + (int64_t)b * p.x.sb + (int64_t)iy * p.x.sh + (int64_t)ix * p.x.sw + c0, v);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) acc[dy][dx][j] = fmaf(v[j], g[j], acc[dy][dx][j]);
+      }
+    }
+  }
+  // lanes with the same piece inside a warp: lane, lane + pieces, ... -> xor-reduce over the multiples of `pieces`
+#pragma unroll
+  for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+    for (int dx = 0; dx < 2; ++dx)
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        float a = acc[dy][dx][j];
+        for (int o = pieces; o < 32; o <<= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        acc[dy][dx][j] = a;
+      }
+  if ((threadIdx.x & 31) < pieces) {
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        float* dst = gw + (int64_t)((ky1 + dy * p.f) * K + kx1 + dx * p.f) * p.C + c0;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) atomicAdd(dst + j, acc[dy][dx][j]);
+      }
+  }
+}
+
 // any strides / channel counts: one thread per output element
 template <typename T>
 __global__ void __launch_bounds__(256) upsample_generic_kernel(UpParams p) {
@@ -260,6 +374,38 @@ int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream) {
     else upsample_generic_kernel<float><<<blocks, 256, 0, stream>>>(p);
   }
   return check_launch("idaup_upsample_kernel");
+}
+
+int idaup_upsample_backward_launch(const cpoly_upsample_bwd_args& a, cudaStream_t stream) {
+  UpParams p;
+  p.B = a.B; p.C = a.C; p.H = a.H; p.W = a.W; p.f = a.f; p.Ho = a.H * a.f; p.Wo = a.W * a.f;
+  p.x = a.x; p.skip = cpoly_tensor4{nullptr, 0, 0, 0, 0}; p.y = cpoly_tensor4{nullptr, 0, 0, 0, 0}; p.w = a.weight; p.w_tapmajor = 1;
+  const bool bf = a.dtype == CPOLY_BF16;
+  const int vec = bf ? 8 : 4;
+  const int pieces = a.C / vec;
+  const bool ok = a.C % vec == 0 && pieces >= 1 && pieces <= 32 && (pieces & (pieces - 1)) == 0 && vec_ok(a.x, vec) && vec_ok(a.gy, vec) &&
+                  vec_ok(a.gx, vec) && a.f % 2 == 0 && (int64_t)a.B * p.Ho * p.Wo * pieces < 0x7fffffffLL;
+  if (!ok) {
+    set_error("idaup_upsample_backward needs channels_last tensors with C/%d a power of two <= 32 and an even f", vec);
+    return CPOLY_EUNSUPPORTED;
+  }
+  if (a.gx.ptr) {
+    const int64_t total = (int64_t)a.B * a.H * a.W * pieces;
+    const unsigned blocks = (unsigned)((total + 255) / 256);
+    if (bf) upsample_bwd_input_kernel<__nv_bfloat16, 8><<<blocks, 256, 0, stream>>>(p, a.gy, a.gx);
+    else upsample_bwd_input_kernel<float, 4><<<blocks, 256, 0, stream>>>(p, a.gy, a.gx);
+    if (int rc = check_launch("upsample_bwd_input_kernel")) return rc;
+  }
+  if (a.gweight) {
+    const int64_t npix = (int64_t)a.B * a.H * a.W;
+    const int nlanes = 256 / pieces;
+    int px_per_block = nlanes * 16;                     // 16 pixels per thread
+    const dim3 grid((unsigned)((npix + px_per_block - 1) / px_per_block), (unsigned)(a.f * a.f));
+    if (bf) upsample_bwd_weight_kernel<__nv_bfloat16, 8><<<grid, 256, 0, stream>>>(p, a.gy, a.gweight, px_per_block);
+    else upsample_bwd_weight_kernel<float, 4><<<grid, 256, 0, stream>>>(p, a.gy, a.gweight, px_per_block);
+    if (int rc = check_launch("upsample_bwd_weight_kernel")) return rc;
+  }
+  return CPOLY_OK;
 }
 
 }  // namespace cpoly

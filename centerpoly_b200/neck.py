@@ -3,7 +3,9 @@ groups=o, bias=False)`` (src/lib/models/networks/pose_dla_dcn.py:372-375, applie
 CUDA kernel, optionally fused with the skip add ``layers[i] + layers[i-1]`` of :387.
 
 ``IDAUpsample`` keeps the parameter name and shape of the module it replaces (``weight`` (C,1,2f,2f)), so
-``state_dict`` keys do not change.  Inference only (no autograd): training keeps the reference's ConvTranspose2d.
+``state_dict`` keys do not change.  ``IDAUpsample`` is the inference module (optional fused skip add, no autograd);
+``IDAUpsampleTrain`` is the training drop-in: same forward kernel plus ``cpoly_idaup_upsample_backward`` for the data
+and weight gradients (cuDNN's grouped-deconvolution kernels cost 15 ms of the 86 ms configs[3] step).
 """
 from __future__ import annotations
 
@@ -14,7 +16,9 @@ from torch import nn
 
 from . import _lib
 
-__all__ = ["idaup_upsample", "IDAUpsample"]
+from torch.autograd.function import once_differentiable
+
+__all__ = ["idaup_upsample", "IDAUpsample", "IDAUpsampleTrain", "use_training_upsamplers"]
 
 
 def idaup_upsample(x: torch.Tensor, weight: torch.Tensor, f: int, skip: torch.Tensor | None = None,
@@ -67,3 +71,77 @@ class IDAUpsample(nn.Module):
         if self._wt is None or self._wt[0] != tag:   # derived (2f*2f, C) fp32 copy of the (tiny) weights
             self._wt = (tag, w.detach().float().reshape(w.shape[0], -1).t().contiguous())
         return idaup_upsample(x, self._wt[1], self.f, skip, tap_major=True)
+
+
+class _UpsampleFn(torch.autograd.Function):
+    """y = conv_transpose2d(x, weight, stride=f, padding=f//2, groups=C) with both gradients on our kernels."""
+
+    @staticmethod
+    def forward(ctx, x, weight, f):
+        wt = weight.detach().float().reshape(weight.shape[0], -1).t().contiguous()      # (4f^2, C) fp32
+        y = idaup_upsample(x, wt, f, None, tap_major=True)
+        ctx.save_for_backward(x, wt)
+        ctx.f, ctx.wshape, ctx.wdtype = f, tuple(weight.shape), weight.dtype
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, gy):
+        x, wt = ctx.saved_tensors
+        f = ctx.f
+        dev = x.device
+        B, C, H, W = x.shape
+        gy = gy.to(x.dtype).contiguous(memory_format=torch.channels_last)
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        with torch.cuda.device(dev):
+            gx = torch.empty_like(x, memory_format=torch.channels_last) if need_x else None
+            gwt = torch.zeros_like(wt) if need_w else None
+            a = _lib.UpsampleBwdArgs()
+            a.B, a.C, a.H, a.W, a.f, a.dtype = B, C, H, W, f, _lib.dtype_code(x)
+            a.x, a.gy, a.gx = _lib.t4(x), _lib.t4(gy), _lib.t4(gx)
+            a.weight = wt.data_ptr()
+            a.gweight = gwt.data_ptr() if need_w else None
+            _lib.check(_lib.lib().cpoly_idaup_upsample_backward(byref(a), _lib.stream_ptr(dev)), "cpoly_idaup_upsample_backward")
+            _lib.LAUNCHES["upsample_bwd"] += int(need_x) + int(need_w)
+        gw = gwt.t().reshape(ctx.wshape).to(ctx.wdtype) if need_w else None
+        return gx, gw, None
+
+
+class IDAUpsampleTrain(nn.Module):
+    """Training drop-in for IDAUp's ``up_i``: keeps the ``nn.ConvTranspose2d`` as the sub-module ``deconv`` is NOT done -
+    the parameter is re-registered under the same name ``weight`` so checkpoints and optimizers see no difference."""
+
+    def __init__(self, deconv: nn.ConvTranspose2d):
+        super().__init__()
+        s = deconv.stride[0]
+        ok = (deconv.groups == deconv.in_channels == deconv.out_channels and deconv.bias is None and
+              deconv.kernel_size == (2 * s, 2 * s) and deconv.stride == (s, s) and deconv.padding == (s // 2, s // 2) and
+              deconv.output_padding == (0, 0) and deconv.dilation == (1, 1) and s >= 2 and s % 2 == 0)
+        if not ok:
+            raise RuntimeError(f"IDAUpsampleTrain: {deconv} is not the depthwise 2f/f/f//2 deconvolution of IDAUp")
+        self.f = s
+        self.weight = deconv.weight
+
+    def forward(self, x):
+        if torch.is_autocast_enabled():
+            x = x.to(torch.get_autocast_dtype("cuda"))
+        C = x.shape[1]
+        vec = 8 if x.dtype == torch.bfloat16 else 4
+        pieces = C // vec
+        if not (x.is_cuda and x.dtype in (torch.bfloat16, torch.float32) and C % vec == 0 and pieces <= 32 and pieces & (pieces - 1) == 0):
+            return torch.nn.functional.conv_transpose2d(x, self.weight.to(x.dtype), None, self.f, self.f // 2, 0, C)
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        return _UpsampleFn.apply(x, self.weight, self.f)
+
+
+def use_training_upsamplers(model: nn.Module) -> int:
+    """Swap every IDAUp ``up_i`` (depthwise ConvTranspose2d 2f/f/f//2, pose_dla_dcn.py:372-375) for ``IDAUpsampleTrain``."""
+    n = 0
+    for parent in model.modules():
+        for name, c in list(parent._modules.items()):
+            if (type(c) is nn.ConvTranspose2d and c.groups == c.in_channels == c.out_channels and c.bias is None and
+                    c.kernel_size == (2 * c.stride[0],) * 2 and c.padding == (c.stride[0] // 2,) * 2 and c.stride[0] % 2 == 0):
+                parent._modules[name] = IDAUpsampleTrain(c)
+                n += 1
+    return n

@@ -53,7 +53,7 @@
 extern "C" {
 #endif
 
-#define CPOLY_ABI_VERSION 6
+#define CPOLY_ABI_VERSION 7
 
 /* element types */
 #define CPOLY_F32 0
@@ -169,6 +169,20 @@ typedef struct {
 } cpoly_upsample_args;
 
 int cpoly_idaup_upsample_forward(const cpoly_upsample_args* args, cpoly_stream_t stream);
+
+/* Backward of the same depthwise transposed convolution (what autograd does with nn.ConvTranspose2d in
+ * IDAUp during training, src/lib/models/networks/pose_dla_dcn.py:372-375,385; driven by base_trainer.py:97-98).
+ * channels_last tensors only; weight / gweight are the tap-major (4f^2, C) fp32 form. */
+typedef struct {
+  int32_t B, C, H, W, f, dtype;
+  cpoly_tensor4 x;        /* (B,C,H,W) forward input                                   */
+  cpoly_tensor4 gy;       /* (B,C,H*f,W*f) gradient of the output                      */
+  const float* weight;    /* (4f^2, C) fp32                                            */
+  cpoly_tensor4 gx;       /* (B,C,H,W) out, or ptr NULL                                */
+  float* gweight;         /* (4f^2, C) fp32, ZERO-INITIALISED by the caller, or NULL   */
+} cpoly_upsample_bwd_args;
+
+int cpoly_idaup_upsample_backward(const cpoly_upsample_bwd_args* args, cpoly_stream_t stream);
 
 /* --------------------------------------------------------------------------------------- decode */
 

@@ -118,3 +118,37 @@ def test_rewrites_are_exact_per_module():
             gate(got[k].cpu().numpy(), want[k].cpu().numpy(), 0.25, k)
     with pytest.raises(RuntimeError):
         opt(img.requires_grad_(True))
+
+
+@pytest.mark.parametrize("f", [2, 4, 8])
+@pytest.mark.parametrize("dtype,C", [(torch.float32, 64), (torch.bfloat16, 64), (torch.bfloat16, 128)], ids=["fp32c64", "bf16c64", "bf16c128"])
+def test_idaup_upsample_backward_vs_conv_transpose(f, dtype, C):
+    """Data and weight gradients of the depthwise transposed convolution against torch's CPU autograd in float64."""
+    from centerpoly_b200.neck import IDAUpsampleTrain
+    g = torch.Generator().manual_seed(20 + f)
+    B, H, W = 2, 9, 13
+    x = torch.randn(B, C, H, W, generator=g)
+    w = torch.randn(C, 1, 2 * f, 2 * f, generator=g) * 0.3
+    gy = torch.randn(B, C, H * f, W * f, generator=g)
+    if dtype == torch.bfloat16:
+        x, gy = x.bfloat16().float(), gy.bfloat16().float()
+    xr, wr = x.double().requires_grad_(True), w.double().requires_grad_(True)
+    F.conv_transpose2d(xr, wr, stride=f, padding=f // 2, groups=C).backward(gy.double())
+    deconv = torch.nn.ConvTranspose2d(C, C, 2 * f, stride=f, padding=f // 2, groups=C, bias=False)
+    with torch.no_grad():
+        deconv.weight.copy_(w)
+    m = IDAUpsampleTrain(deconv.cuda())
+    xd = x.cuda().to(dtype).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y = m(xd)
+    y.backward(gy.cuda().to(dtype))
+    tol = 1e-2 if dtype == torch.bfloat16 else 1e-5
+    gate(xd.grad.float().cpu().numpy(), xr.grad.numpy(), tol, "grad_x")
+    gate(m.weight.grad.float().cpu().numpy(), wr.grad.numpy(), 1e-4 if dtype == torch.float32 else 1e-3, "grad_w")
+    assert list(m.state_dict().keys()) == ["weight"]
+    # frozen weight: only the data gradient is produced
+    m.weight.requires_grad_(False)
+    m.weight.grad = None
+    xd.grad = None
+    m(xd).backward(gy.cuda().to(dtype))
+    assert m.weight.grad is None
+    gate(xd.grad.float().cpu().numpy(), xr.grad.numpy(), tol, "grad_x (frozen weight)")

@@ -18,7 +18,7 @@ def test_library_exports_every_declared_symbol():
     L = ctypes.CDLL(_lib.LIB_PATH)
     for sym in declared:
         assert hasattr(L, sym), sym
-    assert _lib.lib().cpoly_abi_version() == 6
+    assert _lib.lib().cpoly_abi_version() == 7
 
 
 def test_struct_layouts_match_header(tmp_path):
@@ -28,7 +28,7 @@ def test_struct_layouts_match_header(tmp_path):
     names = {"cpoly_tensor4": _lib.Tensor4, "cpoly_dcn_fwd_args": _lib.DcnFwdArgs, "cpoly_dcn_bwd_args": _lib.DcnBwdArgs,
              "cpoly_upsample_args": _lib.UpsampleArgs, "cpoly_decode_args": _lib.DecodeArgs,
              "cpoly_raster_args": _lib.RasterArgs, "cpoly_poly_iou_args": _lib.PolyIouArgs, "cpoly_stem_args": _lib.StemArgs,
-             "cpoly_maxpool_args": _lib.MaxPoolArgs}
+             "cpoly_maxpool_args": _lib.MaxPoolArgs, "cpoly_upsample_bwd_args": _lib.UpsampleBwdArgs}
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include "cpoly.h"\nint main(void){' +
                    "".join(f'printf("{n} %zu\\n", sizeof({n}));' for n in names) + "return 0;}\n")

@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--dcn-path", default="auto", choices=["auto", "simt"])
     ap.add_argument("--poly-loss", default="l1", choices=["l1", "l1+iou"],
                     help="l1: cartesian targets, masked L1; l1+iou: polar targets, the reference's PolyLoss l1+iou (IoU arm on the GPU kernel)")
+    ap.add_argument("--cudnn-upsample", action="store_true", help="keep nn.ConvTranspose2d for the IDAUp up-samplers (cuDNN grouped kernels)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -48,6 +49,10 @@ def main():
     torch.manual_seed(317)                                   # same initial weights on every rank
     net = PolydetDLA34().cuda().to(memory_format=torch.channels_last)
     calibrate_random_init(net, 128, 256)
+    n_up = 0
+    if not args.cudnn_upsample:
+        from centerpoly_b200.neck import use_training_upsamplers
+        n_up = use_training_upsamplers(net)     # IDAUp up_i: forward + both gradients on our kernels
     iou = args.poly_loss == "l1+iou"
     trainer = DataParallelTrainer(net, lr=2e-4, dtype=torch.bfloat16 if args.dtype == "bf16" else None,
                                   loss_fn=polydet_l1_iou_loss if iou else polydet_l1_loss)
@@ -77,7 +82,7 @@ def main():
         ms = float(t)
     if rank == 0:
         print(json.dumps(dict(metric=f"polydet dla_34 training images/s (1024x512 crops, focal + {'L1 + polygon IoU (polar)' if iou else 'L1'}, Adam, data-parallel)",
-                              poly_loss=args.poly_loss, poly_iou_launches=_launches("poly_iou"),
+                              poly_loss=args.poly_loss, poly_iou_launches=_launches("poly_iou"), upsamplers_on_our_kernels=n_up,
                               value=world * args.batch * args.steps / (ms / 1000.0), unit="images/s", n_gpus=world,
                               ms_per_step=ms / args.steps, batch_per_gpu=args.batch, dtype=args.dtype, dcn_path=args.dcn_path,
                               loss_first=losses[0], loss_last=losses[-1], scaling="weak", data="synthetic")), flush=True)
