@@ -121,3 +121,20 @@ def test_poly_loss_mirror_rejects_what_it_does_not_build():
             PolyLoss(o)
     with pytest.raises(RuntimeError):
         poly_iou_loss(torch.zeros(1, 16, 4, 4), torch.ones(1, 2), torch.zeros(1, 2, dtype=torch.int64), torch.zeros(1, 2, 16))
+
+
+def test_training_upsampler_swap_keeps_the_state_dict():
+    """use_training_upsamplers (host logic, no GPU): same keys and tensors before and after; non-CUDA input takes
+    torch's conv_transpose2d with the same parameter."""
+    import torch
+    from centerpoly_b200.harness.dla34 import PolydetDLA34
+    from centerpoly_b200.neck import IDAUpsampleTrain, use_training_upsamplers
+    net = PolydetDLA34()
+    before = {k: v.clone() for k, v in net.state_dict().items()}
+    assert use_training_upsamplers(net) == 8
+    after = net.state_dict()
+    assert list(after.keys()) == list(before.keys()) and all(torch.equal(after[k], before[k]) for k in before)
+    up = next(m for m in net.modules() if isinstance(m, IDAUpsampleTrain))
+    x = torch.randn(1, up.weight.shape[0], 5, 7)
+    want = torch.nn.functional.conv_transpose2d(x, up.weight, None, up.f, up.f // 2, 0, up.weight.shape[0])
+    assert torch.equal(up(x), want)
