@@ -196,7 +196,9 @@ class DataParallelTrainer:
         self.model = model
         self.dtype = dtype
         self.loss_fn = loss_fn
-        self.opt = torch.optim.Adam(model.parameters(), lr)          # src/main.py:44
+        params = list(model.parameters())
+        # src/main.py:44 builds torch.optim.Adam(model.parameters(), opt.lr); same update rule, single multi-tensor launch on CUDA
+        self.opt = torch.optim.Adam(params, lr, fused=bool(params) and all(p.is_cuda for p in params))
         self.reducer = BucketedAllReduce(list(model.parameters()), bucket_bytes)
 
     def step(self, batch):
