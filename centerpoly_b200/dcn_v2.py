@@ -23,7 +23,7 @@ from torch.nn.modules.utils import _pair
 
 from . import _lib
 
-__all__ = ["DCN", "DCNv2", "dcn_v2_conv", "_DCNv2", "set_dcn_path"]
+__all__ = ["DCN", "DCNv2", "dcn_v2_conv", "_DCNv2", "set_dcn_path", "invalidate_packed_weights"]
 
 _FORCED_PATH = _lib.PATH_AUTO
 
@@ -32,6 +32,17 @@ def set_dcn_path(path: str) -> None:
     """'auto' (default), 'simt' or 'tcgen05' — used by tests and profiling to pin a kernel family."""
     global _FORCED_PATH
     _FORCED_PATH = {"auto": _lib.PATH_AUTO, "simt": _lib.PATH_SIMT, "tcgen05": _lib.PATH_TCGEN05}[path]
+
+
+def _tc_allowed(x) -> bool:
+    """The tcgen05 path multiplies fp32 tensors as TF32 (10-bit mantissa, gated at 1e-3 by the tests).  Like every
+    PyTorch convolution it therefore follows ``torch.backends.cudnn.allow_tf32`` (default True): with the flag off,
+    fp32 tensors take the IEEE-fp32 CUDA-core kernels.  bf16 tensors are unaffected."""
+    if _FORCED_PATH == _lib.PATH_SIMT:
+        return False
+    if _FORCED_PATH == _lib.PATH_TCGEN05:
+        return True
+    return x.dtype != torch.float32 or torch.backends.cudnn.allow_tf32
 
 
 def _out_hw(H, W, k, s, p, d):
@@ -43,9 +54,13 @@ class _PackedWeights:
     """Derived, non-persistent cache of the tap-major / swizzled weight images (never in state_dict).
     The image hangs off the weight tensor OBJECT (a plain Python attribute, so it dies with the parameter and can
     never be confused with another tensor that later reuses the same address); it is rebuilt when the parameter's
-    version counter, storage address, device or shape moves (optimizer step, load_state_dict, .to(), .bfloat16())."""
+    version counter, storage address, device or shape moves (load_state_dict, .to(), .bfloat16(), in-place ops).
+    The version counter is NOT trusted while training: ``torch._fused_adam_`` (and any ``.data``-style update: EMA,
+    apex optimizers) changes the values without bumping it, so every forward that will be differentiated w.r.t. the
+    weight (``fresh=True``) re-packs (9*Cin*Cout elements, negligible next to the layer) and the cache serves
+    no-grad inference only.  ``invalidate_packed_weights`` drops it by hand after an out-of-band update."""
 
-    def get(self, weight: torch.Tensor, dtype_code: int):
+    def get(self, weight: torch.Tensor, dtype_code: int, fresh: bool = False):
         Cout, Cin, kh, kw = weight.shape
         L = _lib.lib()
         nbytes = L.cpoly_dcn_packed_weight_bytes(Cin, Cout, kh, kw, dtype_code)
@@ -60,7 +75,7 @@ class _PackedWeights:
             except Exception:      # tensor subclass without a __dict__: pack every call
                 pass
         hit = cache.get(dtype_code)
-        if hit is not None and hit[0] == tag:
+        if hit is not None and hit[0] == tag and not fresh:
             return hit[1]
         w32 = weight.detach()
         if w32.dtype != torch.float32 or not w32.is_contiguous():
@@ -76,6 +91,22 @@ class _PackedWeights:
 _GLOBAL_PACK_CACHE = _PackedWeights()
 
 
+def invalidate_packed_weights(obj) -> int:
+    """Drop the derived weight images of a tensor, a DCN module or a whole model (after a ``.data`` / fused-optimizer
+    update made outside autograd's version counting while the model is used for no-grad inference)."""
+    tensors = [obj] if isinstance(obj, torch.Tensor) else [p for p in obj.parameters()]
+    n = 0
+    for t in tensors:
+        if getattr(t, "_cpoly_packed", None):
+            t._cpoly_packed.clear()
+            n += 1
+    if isinstance(obj, nn.Module):
+        for m in obj.modules():
+            if hasattr(m, "_om_cache"):
+                m._om_cache = None
+    return n
+
+
 def _fwd_args(x, offset, mask, weight32, bias32, stride, padding, dilation, dg, mask_is_logit, packed, y,
               wshape=None, out_scale=None, relu=False, om_bias=None):
     a = _lib.DcnFwdArgs()
@@ -88,7 +119,7 @@ def _fwd_args(x, offset, mask, weight32, bias32, stride, padding, dilation, dg, 
     a.dtype = _lib.dtype_code(x)
     a.om_dtype = _lib.dtype_code(offset)
     a.mask_is_logit = int(mask_is_logit)
-    a.path = _FORCED_PATH
+    a.path = _FORCED_PATH if _tc_allowed(x) else _lib.PATH_SIMT
     a.x, a.offset, a.mask = _lib.t4(x), _lib.t4(offset), _lib.t4(mask)
     a.weight = weight32.data_ptr() if weight32 is not None else None
     a.bias = bias32.data_ptr() if bias32 is not None else None
@@ -128,13 +159,13 @@ def _check_shapes(x, offset, mask, weight, stride, padding, dilation, dg):
 
 
 def _forward_impl(x, offset, mask, weight, bias, stride, padding, dilation, dg, mask_is_logit, out_scale=None, relu=False,
-                  om_bias=None):
+                  om_bias=None, fresh_pack=False):
     """y = act(out_scale * dcn(x) + bias); out_scale/relu are the optional fused DeformConv epilogue."""
     dev = _lib.require_cuda(x, offset, mask, weight, bias)
     Ho, Wo = _check_shapes(x, offset, mask, weight, stride, padding, dilation, dg)
     L = _lib.lib()
     with torch.cuda.device(dev):
-        packed = _GLOBAL_PACK_CACHE.get(weight, _lib.dtype_code(x)) if _FORCED_PATH != _lib.PATH_SIMT else None
+        packed = _GLOBAL_PACK_CACHE.get(weight, _lib.dtype_code(x), fresh_pack) if _tc_allowed(x) else None
         if packed is not None and not x.is_contiguous(memory_format=torch.channels_last):
             # the tensor-core path reads NHWC; run the model channels_last to make this a no-op
             x = x.contiguous(memory_format=torch.channels_last)
@@ -197,7 +228,7 @@ class _DCNv2(Function):
         ctx.stride, ctx.padding, ctx.dilation = _pair(stride), _pair(padding), _pair(dilation)
         ctx.deformable_groups = deformable_groups
         y, x_used = _forward_impl(input, offset, mask, weight, bias, ctx.stride, ctx.padding, ctx.dilation,
-                                  deformable_groups, mask_is_logit=False)
+                                  deformable_groups, mask_is_logit=False, fresh_pack=ctx.needs_input_grad[3])
         ctx.save_for_backward(x_used, offset, mask, weight, bias)
         return y
 
@@ -222,7 +253,7 @@ class _DCNFused(Function):
         ctx.deformable_groups = deformable_groups
         n_off = om.shape[1] // 3 * 2
         y, x_used = _forward_impl(input, om[:, :n_off], om[:, n_off:], weight, bias, stride, padding, dilation,
-                                  deformable_groups, mask_is_logit=True)
+                                  deformable_groups, mask_is_logit=True, fresh_pack=ctx.needs_input_grad[2])
         ctx.save_for_backward(x_used, om, weight, bias)
         return y
 

@@ -111,14 +111,24 @@ def synthetic_batch(batch, height, width, n_cls=8, n_vtx=32, max_objs=128, n_obj
 # ------------------------------------------------------------------------------------------------ gradient exchange
 class BucketedAllReduce:
     """Flat gradient buckets filled in reverse parameter order (= roughly the order backward produces them) and
-    all-reduced asynchronously as soon as they are complete.  ``finish()`` waits, averages and scatters the
-    buckets back into ``p.grad``."""
+    all-reduced asynchronously as soon as they are complete.
+
+    Data movement per step and parameter: ONE copy, gradient -> its slice of the flat bucket, issued on the side stream
+    from the post-accumulate hook; ``p.grad`` is then re-pointed at that slice, the all-reduce averages in place
+    (``ReduceOp.AVG`` on NCCL; sum + one scale of the flat bucket on gloo), and the optimizer reads the bucket directly -
+    there is no copy back and no per-parameter multiply.  With one rank nothing is registered at all."""
 
     def __init__(self, params, bucket_bytes=25 << 20, group=None):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.params = [p for p in params if p.requires_grad]
         self.buckets = []     # dict(flat, views[(param, view)], pending, work)
+        self.stream = None
+        self._hooks = []
+        self.launch_events = []   # (bucket index, CUDA event recorded when its all-reduce was enqueued): overlap evidence
+        self.last_launch_events = []
+        if self.world == 1:
+            return
         cur, cur_bytes = [], 0
         for p in reversed(self.params):
             cur.append(p)
@@ -133,6 +143,7 @@ class BucketedAllReduce:
             for p, _ in b["views"]:
                 self._where[p] = bi
         self.stream = torch.cuda.Stream() if self.params and self.params[0].is_cuda else None
+        self._avg = dist.ReduceOp.AVG if dist.get_backend(group) == "nccl" else None
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
 
     def _close(self, plist):
@@ -151,22 +162,35 @@ class BucketedAllReduce:
             self._launch(b)
 
     def _launch(self, b):
-        """Copy the bucket's gradients into its flat buffer and start the all-reduce on the side stream."""
+        """Move the bucket's gradients into its flat buffer and start the all-reduce on the side stream."""
         import contextlib
         if self.stream is not None:
             self.stream.wait_stream(torch.cuda.current_stream())
         with (torch.cuda.stream(self.stream) if self.stream is not None else contextlib.nullcontext()):
             for p, v in b["views"]:
-                if p.grad is not None:
-                    v.copy_(p.grad)
-                else:
+                if p.grad is None:
                     v.zero_()      # frozen / unused parameter: contributes zeros, keeps the buckets aligned across ranks
-            if self.world > 1:
+                elif p.grad.data_ptr() != v.data_ptr():
+                    g = p.grad
+                    v.copy_(g)
+                    if g.dtype == v.dtype:
+                        if g.is_cuda and self.stream is not None:
+                            g.record_stream(self.stream)   # its memory must not be recycled before the side-stream copy ran
+                        p.grad = v  # the optimizer reads the (averaged) bucket slice; the producer's tensor is released
+            if self._avg is not None:
+                b["work"] = dist.all_reduce(b["flat"], op=self._avg, group=self.group, async_op=True)
+            else:
                 b["work"] = dist.all_reduce(b["flat"], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            if self.stream is not None:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record(self.stream)
+                self.launch_events.append((self.buckets.index(b), ev))
         b["launched"] = True
 
     def finish(self):
-        """Call after backward: flush incomplete buckets, wait, write the averaged gradients back into p.grad."""
+        """Call after backward: flush incomplete buckets, wait; p.grad then holds the rank-averaged gradient."""
+        if self.world == 1:
+            return
         for b in self.buckets:
             if not b.get("launched"):
                 self._launch(b)
@@ -175,18 +199,32 @@ class BucketedAllReduce:
                 b["work"].wait()
         if self.stream is not None:
             torch.cuda.current_stream().wait_stream(self.stream)
-        if self.world > 1:
-            inv = 1.0 / self.world
-            for b in self.buckets:
-                for p, v in b["views"]:
-                    if p.grad is not None:
-                        torch.mul(v, inv, out=p.grad)
         for b in self.buckets:
+            if self._avg is None:
+                b["flat"].mul_(1.0 / self.world)
+            for p, v in b["views"]:
+                if p.grad is not None and p.grad.data_ptr() != v.data_ptr():
+                    p.grad.copy_(v)        # gradient kept in another dtype: one cast back
             b["pending"], b["work"], b["launched"] = b["n"], None, False
+        self.last_launch_events, self.launch_events = self.launch_events, []
 
     def remove(self):
         for h in self._hooks:
             h.remove()
+
+
+def broadcast_module_state(model: nn.Module, src: int = 0, group=None) -> int:
+    """What nn.DataParallel.replicate does every step (src/lib/models/data_parallel.py:70-75): every rank starts from
+    rank ``src``'s parameters AND buffers (BN running statistics), so a rank-dependent init, a different seed or a
+    checkpoint loaded on one rank cannot make the replicas diverge silently.  Returns the number of tensors sent."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return 0
+    n = 0
+    with torch.no_grad():
+        for t in list(model.parameters()) + list(model.buffers()):
+            dist.broadcast(t.data, src=src, group=group)
+            n += 1
+    return n
 
 
 class DataParallelTrainer:
@@ -196,10 +234,24 @@ class DataParallelTrainer:
         self.model = model
         self.dtype = dtype
         self.loss_fn = loss_fn
+        broadcast_module_state(model)      # replicas start identical (reference: nn.DataParallel re-broadcasts GPU 0's)
         params = list(model.parameters())
         # src/main.py:44 builds torch.optim.Adam(model.parameters(), opt.lr); same update rule, single multi-tensor launch on CUDA
         self.opt = torch.optim.Adam(params, lr, fused=bool(params) and all(p.is_cuda for p in params))
         self.reducer = BucketedAllReduce(list(model.parameters()), bucket_bytes)
+        self.timing = False          # set True to record the events `exchange_ms()` reads
+        self._ev = None
+
+    def exchange_ms(self):
+        """(exposed, span) of the last step's gradient exchange in ms, CUDA events, after a synchronize():
+        exposed = time the main stream waited for the all-reduces after backward had finished (what the step pays);
+        span    = first all-reduce enqueued -> exchange complete (what NCCL was busy for, mostly under backward)."""
+        if self._ev is None:
+            return None
+        bwd_end, done = self._ev
+        evs = self.reducer.last_launch_events
+        span = evs[0][1].elapsed_time(done) if evs else 0.0
+        return bwd_end.elapsed_time(done), span
 
     def step(self, batch):
         self.model.train()
@@ -212,6 +264,13 @@ class DataParallelTrainer:
             out = self.model(x)[-1]
         loss = self.loss_fn(out, batch)
         loss.backward()
+        if self.timing and loss.is_cuda:
+            bwd_end = torch.cuda.Event(enable_timing=True)
+            bwd_end.record()
         self.reducer.finish()
+        if self.timing and loss.is_cuda:
+            done = torch.cuda.Event(enable_timing=True)
+            done.record()
+            self._ev = (bwd_end, done)
         self.opt.step()
         return loss.detach()

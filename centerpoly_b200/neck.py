@@ -129,7 +129,9 @@ class IDAUpsampleTrain(nn.Module):
         vec = 8 if x.dtype == torch.bfloat16 else 4
         pieces = C // vec
         if not (x.is_cuda and x.dtype in (torch.bfloat16, torch.float32) and C % vec == 0 and pieces <= 32 and pieces & (pieces - 1) == 0):
-            return torch.nn.functional.conv_transpose2d(x, self.weight.to(x.dtype), None, self.f, self.f // 2, 0, C)
+            # no CPU / PyTorch fallback in the product (north_star): same behaviour as every other entry point
+            raise RuntimeError(f"IDAUpsampleTrain: needs a CUDA bf16/fp32 tensor whose channel count is {vec} x a power of two "
+                               f"<= {32 * vec} (got {tuple(x.shape)}, {x.dtype}, {x.device}); keep nn.ConvTranspose2d for other inputs")
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         return _UpsampleFn.apply(x, self.weight, self.f)

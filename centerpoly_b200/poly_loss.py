@@ -7,8 +7,13 @@ analytic gradient, one warp per object, the ``_transpose_and_gather_feat`` (:855
     crit = PolyLoss(opt)                                   # opt.poly_loss, opt.rep, opt.poly_order as in opts.py:72,166-169
     loss = crit(output['poly'], batch['reg_mask'], batch['ind'], batch['poly'])
 
-Not built (raise): ``poly_order`` (the reference mutates a view of the prediction in place, :893-906),
-``poly_loss='relu'`` / 'bce', and the IoU arm for ``rep='cartesian'`` (the reference's ``area`` hard-codes POLAR = True).
+``poly_order`` (:891-906, ``opt.poly_order``): ``poly_order_loss`` below; like the reference, ``forward`` then returns
+``(loss, loss_order)``.  Not built (raise): ``poly_loss='relu'`` / 'bce', and the IoU arm for ``rep='cartesian'`` (the
+reference's ``area`` hard-codes POLAR = True).
+
+Objects whose clip the reference cannot finish (``IOU_STATUS`` != 0: it raises IndexError or never returns) contribute
+IoU 0 and no gradient but still count in the denominator; ``PolyLoss.last_status`` keeps the per-object status tensor
+on the device (no sync), and ``opt.poly_strict = True`` (or ``poly_iou_loss(..., strict=True)``) raises like the reference.
 """
 from __future__ import annotations
 
@@ -20,7 +25,7 @@ from torch.autograd.function import once_differentiable
 
 from . import _lib
 
-__all__ = ["poly_iou_loss", "PolyLoss", "IOU_STATUS"]
+__all__ = ["poly_iou_loss", "poly_order_loss", "PolyLoss", "IOU_STATUS"]
 
 IOU_STATUS = {0: "ok", 1: "no out-bound crossing (reference raises IndexError)", 2: "walk does not terminate in the reference",
               3: "more than 4N crossings", 4: "non-finite row"}
@@ -80,12 +85,41 @@ class _PolyIoU(torch.autograd.Function):
         return gmap.to(ctx.in_dtype), None, None, None
 
 
-def poly_iou_loss(output, mask, ind, target, return_details: bool = False):
+def poly_iou_loss(output, mask, ind, target, return_details: bool = False, strict: bool = False):
     """The IoU arm of ``PolyLoss.forward``: ``output`` (B,2N,H,W) polar poly head (fp32 / bf16, NCHW or channels_last),
     ``mask`` (B,M), ``ind`` (B,M) int64, ``target`` (B,M,2N).  Returns the scalar loss (differentiable w.r.t.
-    ``output``), and with ``return_details`` also the per-object IoU and status (see ``IOU_STATUS``)."""
+    ``output``), and with ``return_details`` also the per-object IoU and status (see ``IOU_STATUS``).  ``strict``:
+    raise when an object's clip fails where the reference raises / hangs (costs one device->host sync)."""
     loss, iou, status = _PolyIoU.apply(output, mask, ind, target)
+    if strict:
+        bad = status[status != 0]
+        if bad.numel():
+            kinds = {IOU_STATUS.get(int(k), str(int(k))): int((bad == k).sum()) for k in bad.unique()}
+            raise RuntimeError(f"poly_iou_loss: {bad.numel()} object(s) could not be clipped (the reference fails on them too): {kinds}")
     return (loss, iou, status) if return_details else loss
+
+
+def poly_order_loss(pred, mask):
+    """The order arm of the reference's ``PolyLoss.forward`` (losses.py:891-906, 908), vectorised on the tensors' device.
+
+    Per selected object, over its N predicted angles ``a`` (``pred[..., 1::2]``), in vertex order:
+      * once an angle > 0 has been seen, every later negative angle gets ``+ 2*3.14`` - IN PLACE on a view of the
+        gathered prediction in the reference, so the regression arm that follows sees the shifted angles too;
+      * ``loss_order += sum_{j=0}^{N-2} sum_{k=j}^{N-1} max(a_j - a_k, 0)``; finally ``/ (10 * mask.sum() + 1e-4)``.
+    Returns ``(pred_shifted, loss_order)``; ``pred_shifted`` is a new tensor (same gradient as the in-place add)."""
+    a = pred[..., 1::2]
+    sel = (mask != 0).unsqueeze(-1)
+    seen_pos = torch.cumsum((a > 0).to(torch.int32), dim=-1) > 0          # inclusive == exclusive where a_j < 0
+    shift = ((a < 0) & seen_pos & sel).to(pred.dtype) * pred.new_tensor(2 * 3.14)
+    a = a + shift
+    N = a.shape[-1]
+    d = a.unsqueeze(-1) - a.unsqueeze(-2)                                  # [.., j, k] = a_j - a_k
+    jj = torch.arange(N, device=pred.device)
+    pair = (jj.unsqueeze(1) <= jj.unsqueeze(0)) & (jj.unsqueeze(1) < N - 1)   # k >= j, j <= N-2 (range((2N-1)//2))
+    order = (torch.relu(d) * pair * sel.unsqueeze(-1)).sum()
+    order = order / (10 * mask.sum() + 1e-4)
+    shifted = torch.stack((pred[..., 0::2], a), dim=-1).flatten(-2)
+    return shifted, order
 
 
 def _gather(feat, ind):
@@ -100,8 +134,7 @@ class PolyLoss(nn.Module):
     def __init__(self, opt):
         super().__init__()
         self.opt = opt
-        if getattr(opt, "poly_order", False):
-            raise NotImplementedError("poly_order: the reference's order loss mutates the prediction view in place (losses.py:893-906)")
+        self.last_status = None
         if opt.poly_loss not in ("l1", "iou", "l1+iou"):
             raise NotImplementedError(f"poly_loss={opt.poly_loss!r} (built: l1, iou, l1+iou)")
         if opt.poly_loss != "l1" and opt.rep not in ("polar", "polar_fixed"):
@@ -110,10 +143,16 @@ class PolyLoss(nn.Module):
     def forward(self, output, mask, ind, target, freq_mask=None, peak=None, hm=None):
         opt = self.opt
         loss = 0.0
-        if opt.poly_loss in ("iou", "l1+iou"):
-            loss = poly_iou_loss(output, mask, ind, target)
+        if opt.poly_loss in ("iou", "l1+iou"):                      # per object BEFORE its angles are shifted (:870-888)
+            loss, _, self.last_status = poly_iou_loss(output, mask, ind, target, return_details=True,
+                                                      strict=bool(getattr(opt, "poly_strict", False)))
+        order = None
+        pred = None
+        if getattr(opt, "poly_order", False):                       # :891-906
+            pred, order = poly_order_loss(_gather(output.float(), ind), mask)
         if opt.poly_loss in ("l1", "l1+iou"):                       # :911-945
-            pred = _gather(output.float(), ind)
+            if pred is None:
+                pred = _gather(output.float(), ind)
             m = mask.unsqueeze(2).expand_as(pred).float()
             if opt.rep == "cartesian":
                 reg = torch.nn.functional.l1_loss(pred * m, target * m, reduction="sum")
@@ -126,4 +165,6 @@ class PolyLoss(nn.Module):
                 elif opt.rep != "polar_fixed":
                     reg = 0.0 * reg                                  # any other rep string: no regression arm in the reference
             loss = loss + reg / (m.sum() + 1e-6)
+        if order is not None:
+            return loss, order                                      # :951-954
         return loss

@@ -21,14 +21,19 @@ def _net():
 
 def _worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
-    from centerpoly_b200.harness.train import BucketedAllReduce
+    from centerpoly_b200.harness.train import BucketedAllReduce, broadcast_module_state
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     torch.manual_seed(0)
     x = torch.randn(4, 3, 8, 8)
     y = torch.randn(4, 5)
     net = _net()
-    net(x)  # materialise the lazy layer identically on every rank
+    net(x)  # materialise the lazy layer on every rank
+    if rank == 1:   # a rank-dependent init / a checkpoint loaded on one rank only: the broadcast must repair it
+        with torch.no_grad():
+            for p in net.parameters():
+                p.add_(1.0)
+    assert broadcast_module_state(net) == len(list(net.parameters()))
     red = BucketedAllReduce(list(net.parameters()), bucket_bytes=2048)   # several small buckets
     assert len(red.buckets) > 1
     for step in range(2):                                               # buckets must re-arm between steps
@@ -37,7 +42,8 @@ def _worker(rank, world, port, q):
         loss = ((net(xs) - ys) ** 2).mean()
         loss.backward()
         red.finish()
-    q.put((rank, [p.grad.clone() for p in net.parameters()]))
+    assert all(p.grad.data_ptr() == v.data_ptr() for b in red.buckets for p, v in b["views"])   # no copy back: grad IS the bucket slice
+    q.put((rank, [p.grad.clone().numpy() for p in net.parameters()]))   # by value: the worker may exit before the parent reads
     dist.barrier()
     dist.destroy_process_group()
 
@@ -61,8 +67,8 @@ def test_bucketed_allreduce_matches_full_batch_gradients():
     # mean over ranks of per-rank mean losses == mean over the full batch (equal shard sizes)
     ((net(x) - y) ** 2).mean().backward()
     for g0, g1, p in zip(got[0], got[1], net.parameters()):
-        torch.testing.assert_close(g0, g1, rtol=0, atol=0)
-        torch.testing.assert_close(g0, p.grad, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(torch.from_numpy(g0), torch.from_numpy(g1), rtol=0, atol=0)
+        torch.testing.assert_close(torch.from_numpy(g0), p.grad, rtol=1e-5, atol=1e-6)
 
 
 def test_single_process_is_a_no_op():

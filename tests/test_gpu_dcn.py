@@ -153,13 +153,14 @@ def test_full_size_zero_offset_identity_and_linearity():
         gate(lhs.double().cpu().numpy(), rhs.double().cpu().numpy(), 2e-3, "linearity")
 
 
-def test_module_matches_torchvision_module():
+def test_module_matches_torchvision_module(monkeypatch):
     """DCN module (fused sigmoid/chunk path) vs the torchvision-backed oracle module, same state_dict."""
     import centerpoly_b200 as cp
     from oracle.tv_dcn import TVDCN
     # cuDNN's default TF32 convolution would perturb the OFFSETS (conv_offset_mask output) by ~1e-3 relative and
-    # move the sampling points; pin the offset conv to IEEE fp32 so this test isolates the DCN kernels.
-    torch.backends.cudnn.allow_tf32 = False
+    # move the sampling points; with the flag off both the offset conv and (by the same flag, dcn_v2._tc_allowed)
+    # our DCN run in IEEE fp32.
+    monkeypatch.setattr(torch.backends.cudnn, "allow_tf32", False)
     torch.manual_seed(3)
     ref = TVDCN(64, 64, (3, 3), 1, 1)
     torch.nn.init.normal_(ref.conv_offset_mask.weight, std=0.05)

@@ -81,14 +81,14 @@ def _neck_inputs(seed=0):
     return [mk(64, 32, 64), mk(128, 16, 32), mk(256, 8, 16)]
 
 
-def test_rewrites_are_exact_per_module():
+def test_rewrites_are_exact_per_module(monkeypatch):
     """Every rewrite of optimize_for_inference against the module it replaces, on identical inputs.  (The
     whole random-init network amplifies a 1e-6 perturbation to ~1e-2 through its 16 data-dependent samplers -
     tools/fusion_debug.py - so the module is the level at which exactness can be gated.)"""
     import copy
     from centerpoly_b200 import fuse
     from centerpoly_b200.harness.dla34 import PolydetDLA34, calibrate_random_init
-    torch.backends.cudnn.allow_tf32 = False
+    monkeypatch.setattr(torch.backends.cudnn, "allow_tf32", False)   # IEEE fp32 on both sides (convs and DCN)
     torch.manual_seed(317)
     net = PolydetDLA34().cuda().to(memory_format=torch.channels_last)
     calibrate_random_init(net, 128, 256)

@@ -114,7 +114,8 @@ def test_poly_loss_mirror_rejects_what_it_does_not_build():
     class Opt:
         poly_loss, rep, poly_order = "iou", "polar", False
     PolyLoss(Opt())
-    for attr, val in (("poly_order", True), ("poly_loss", "relu"), ("rep", "cartesian")):
+    PolyLoss(type("O", (), dict(poly_loss="iou", rep="polar", poly_order=True)))      # order arm is built (tests/test_polyorder.py)
+    for attr, val in (("poly_loss", "relu"), ("poly_loss", "bce"), ("rep", "cartesian")):
         o = type("O", (), dict(poly_loss="iou", rep="polar", poly_order=False))
         setattr(o, attr, val)
         with pytest.raises(NotImplementedError):
@@ -124,8 +125,8 @@ def test_poly_loss_mirror_rejects_what_it_does_not_build():
 
 
 def test_training_upsampler_swap_keeps_the_state_dict():
-    """use_training_upsamplers (host logic, no GPU): same keys and tensors before and after; non-CUDA input takes
-    torch's conv_transpose2d with the same parameter."""
+    """use_training_upsamplers (host logic, no GPU): same keys and tensors before and after; a non-CUDA input raises
+    like every other entry point (no PyTorch fallback in the product)."""
     import torch
     from centerpoly_b200.harness.dla34 import PolydetDLA34
     from centerpoly_b200.neck import IDAUpsampleTrain, use_training_upsamplers
@@ -135,6 +136,5 @@ def test_training_upsampler_swap_keeps_the_state_dict():
     after = net.state_dict()
     assert list(after.keys()) == list(before.keys()) and all(torch.equal(after[k], before[k]) for k in before)
     up = next(m for m in net.modules() if isinstance(m, IDAUpsampleTrain))
-    x = torch.randn(1, up.weight.shape[0], 5, 7)
-    want = torch.nn.functional.conv_transpose2d(x, up.weight, None, up.f, up.f // 2, 0, up.weight.shape[0])
-    assert torch.equal(up(x), want)
+    with pytest.raises(RuntimeError):
+        up(torch.randn(1, up.weight.shape[0], 5, 7))
