@@ -1,11 +1,21 @@
 #!/usr/bin/env python
-"""bench.py — BASELINE.json metric: 2048x1024 frames/s of polydet dla_34 inference (configs[1]) per B200.
+"""bench.py — BASELINE.json metric: 2048x1024 frames/s of polydet dla_34 inference (configs[1]) per B200, plus, in the
+same JSON line, the rest of the measurement contract:
 
-    python bench.py --gpus N --steps K --warmup W [--dtype bf16|fp32] [--impl reference]
+    python bench.py --gpus N --steps K --warmup W [--dtype bf16|fp32] [--impl reference] [--skip fp32,sweep,train,idd,cpu]
 
-A step = one pass of the hot path over one synthetic 2048x1024 frame: DLA-34 network (16 DCNv2 layers through
-libcpoly.so) -> sigmoid -> fused polydet_decode (+ the back-mapping of polydet_post_process), replayed from a CUDA graph.  Prints ONE JSON line (rank 0).
-See DESIGN.md "Measurement" for how every field is produced.
+  value / e2e   configs[1] bf16: one synthetic 2048x1024 frame per step, DLA-34 network (16 DCNv2 layers through
+                libcpoly.so) -> sigmoid -> fused polydet_decode (+ polydet_post_process back-mapping), CUDA graph replay
+  sustained     the same loop for >= 2 s with >= 20 NVML clock samples (the K-step figure is a burst figure)
+  roofline      dominant kernel (dcn_fwd_tc_kernel, 64->64 @256x512) timed live against the measured HBM / tensor peaks
+  fp32          configs[1] in fp32 (TF32 tensor cores)
+  dcn_sweep     configs[2]: DCNv2 fwd+bwd TFLOP/s vs tensor peak and GB/s vs HBM peak per IDAUp shape, B in {1,4,16}
+  train         configs[3]: data-parallel training step (16 crops of 1024x512 per GPU, focal + L1 + polygon IoU, Adam),
+                images/s over all ranks, NCCL gradient all-reduce: exposed and total time per step
+  idd_polar     configs[4]: polar-vertex inference, 8 IDD-shape 1920x1080 (padded 1952x1088) images per GPU, end to end
+  cpu_baseline  the path's CPU implementation on the host cores (N = 1 only)
+
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for how every field is produced.
 """
 import argparse
 import json
@@ -22,21 +32,24 @@ sys.path.insert(0, ROOT)
 METRIC = "2048x1024 frames/s (polydet dla_34 inference, hot path = 16 DCNv2 layers + sigmoid + polydet_decode)"
 H, W = 1024, 2048
 K_DET, N_VTX, N_CLS = 100, 32, 8
+SWEEP_SHAPES = [(64, 64, 256, 512), (128, 64, 128, 256), (128, 128, 128, 256), (256, 64, 64, 128),
+                (256, 128, 64, 128), (256, 256, 64, 128), (512, 256, 32, 64)]       # SURVEY A.1 / configs[2]
 
 
 def read_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return dict(hbm_gbs=d["hbm_gbs"], bf16_tflops=d["bf16_tflops"], source="measured")
-    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, source="fallback")
+        return dict(hbm_gbs=d["hbm_gbs"], bf16_tflops=d["bf16_tflops"], bf16_tflops_sustained=d.get("bf16_tflops_sustained"),
+                    source="measured")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_tflops_sustained=1400.0, source="fallback")
 
 
 class ClockSampler:
-    """Samples SM clock + throttle reasons DURING the timed region (NVML, 50 ms period)."""
+    """Samples SM clock + throttle reasons DURING a timed region (NVML, 5 ms period)."""
 
-    def __init__(self, index):
-        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+    def __init__(self, index, period=0.005):
+        self.index, self.samples, self.reasons, self.max_mhz, self.period = index, [], set(), None, period
         self._stop = threading.Event()
         self._thread = None
 
@@ -74,7 +87,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.05)
+            self._stop.wait(self.period)
 
     def stop(self):
         self._stop.set()
@@ -97,9 +110,15 @@ def physical_gpu_index(local_rank):
 
 # ------------------------------------------------------------------------------------------ CPU arm
 class CpuArm:
-    """The path's CPU implementation on the host: the same DLA-34 network with torchvision's CPU deform_conv2d (the
-    stand-in BASELINE.json names for the missing DCNv2 CPU build) + the numpy decode oracle.  Bench infrastructure only.
-    The network is built and calibrated ONCE, outside every timed region."""
+    """The path's CPU implementation on the host: centerpoly_b200/harness/dla34.py (a state_dict-compatible mirror of the
+    reference's DLASeg, pinned to it bit-exactly by tests/test_harness_vs_reference.py; /root/reference does not exist on
+    the GPU box) with torchvision's CPU deform_conv2d behind the DCN module API (the stand-in BASELINE.json names for
+    the missing DCNv2 CPU build) + the numpy decode and post-process oracles.  Bench infrastructure only.  The network
+    is built and calibrated ONCE, outside every timed region."""
+
+    KIND = "port"
+    WHAT = ("harness/dla34.py (mirror of the reference's DLASeg, bit-exact vs it in tests/test_harness_vs_reference.py) with "
+            "torchvision CPU deform_conv2d behind the DCN API + numpy polydet_decode and polydet_post_process oracles")
 
     def __init__(self, threads):
         import torch
@@ -131,36 +150,48 @@ class CpuArm:
 
 
 def run_reference(args):
-    """--impl reference: the path's CPU implementation on the host cores (rank 0 only)."""
+    """--impl reference: the path's CPU implementation on the host cores (rank 0 only), on the SAME config as the GPU
+    arm: every step is one full 2048x1024 frame, ms_per_step is measured, nothing is extrapolated."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
     threads = os.cpu_count() or 1
-    # bounded sample: a crop whose pixel count is 1/frac of the 2048x1024 frame (conv cost is linear in pixels)
-    frac, (h, w) = 4, (512, 1024)
     arm = CpuArm(threads)
-    t_probe = arm.frame_seconds(h, w)
-    if t_probe * (args.steps + args.warmup) > 240:
-        frac, (h, w) = 16, (256, 512)
+    frac, (h, w) = 1, (H, W)
+    t_probe = arm.frame_seconds(h, w)                      # also the first warm-up step
+    if t_probe * (args.steps + args.warmup) > 1500:        # a box with very few host cores: bounded crop, stated below
+        frac, (h, w) = 4, (H // 2, W // 2)
+        arm.frame_seconds(h, w)
     for _ in range(max(0, args.warmup - 1)):
         arm.frame_seconds(h, w)
     dt = 0.0
     for _ in range(args.steps):
         dt += arm.frame_seconds(h, w)
     fps = args.steps / frac / dt
-    sample = f"{args.steps} steps, each one {w}x{h} crop = 1/{frac} of a 2048x1024 frame (cost linear in pixels); torchvision CPU deform_conv2d + numpy decode and post-process oracles"
+    sample = (f"{args.steps} steps, each one full {W}x{H} frame" if frac == 1 else
+              f"{args.steps} steps, each one {w}x{h} crop = 1/{frac} of a frame (cost linear in pixels; too few host cores for full frames)")
+    sample += "; " + CpuArm.WHAT
     line = dict(impl="reference", metric=METRIC, value=fps, unit="frames/s", n_gpus=args.gpus, steps=args.steps,
                 warmup=args.warmup, ms_per_step=1000.0 * dt / args.steps * frac, higher_is_better=True, scaling="weak",
                 vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload="configs[1]: polydet dla_34 inference, batch 1, synthetic 2048x1024", K=K_DET,
-                            classes=N_CLS, vertices=N_VTX),
-                cpu_baseline=dict(value=fps, unit="frames/s", cores=threads, kind="port", sample=sample),
+                config=dict(workload="configs[1]: polydet dla_34 inference, batch 1, synthetic 2048x1024 Cityscapes-shape", K=K_DET,
+                            classes=N_CLS, vertices=N_VTX, frame_fraction_per_step=1.0 / frac),
+                cpu_baseline=dict(value=fps, unit="frames/s", cores=threads, kind=CpuArm.KIND, sample=sample),
                 e2e=dict(value=fps, unit="frames/s", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line), flush=True)
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
+def measured_traffic(kernel, dtype):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from this round's `ncu --set full` capture
+    (profiles/r02_traffic.json, written by tools/ncu_summary.py from the committed raw page); None if not captured."""
+    p = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    try:
+        return json.load(open(p)).get(f"{kernel}:{dtype}")
+    except Exception:
+        return None
+
+
 def dominant_kernel_roofline(torch, dtype, steps, peaks):
     """The dominant kernel: dcn_fwd_tc_kernel on the 64->64 @ 256x512 stride-4 node layers (5 launches per frame,
     the largest DCN time share).  5*steps back-to-back launches through the C ABI on the bench stream between two
@@ -185,7 +216,7 @@ def dominant_kernel_roofline(torch, dtype, steps, peaks):
     for i in range(2 * nbuf):
         call(i)
     torch.cuda.synchronize()
-    n = 5 * steps
+    n = max(50, 5 * steps)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for i in range(n):
@@ -196,16 +227,230 @@ def dominant_kernel_roofline(torch, dtype, steps, peaks):
     alg_bytes = es * h * w * (Cin + 27 + Cout)          # s*B*H*W*(Cin+27+Cout)
     flops = 2.0 * Cout * Cin * 9 * h * w
     achieved = alg_bytes / ms / 1e6
-    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of this launch in the committed `ncu --set full` capture
-    # (profiles/r01d_dcn_fwd_tc_64x64_raw.txt; bf16 only).  Below the algorithmic bytes because the 16.8 MB output
-    # is still in the write-back L2 when the kernel ends.
-    traffic = 23.98e6 if dtype == "bf16" else None
+    tpeak = peaks["bf16_tflops"] * (1.0 if dtype == "bf16" else 0.5)
     return dict(bound="hbm", kernel="dcn_fwd_tc_kernel", layer="64->64 @256x512 (5 of 16 DCN layers/frame)",
-                achieved=achieved, peak=peaks["hbm_gbs"], unit="GB/s", frac=achieved / peaks["hbm_gbs"], traffic=traffic,
-                note="gather-bound: the sampler pulls 4*9*H*W*Cin*s = 604 MB through the L1 path per launch (DESIGN.md 3.1)",
-                peak_source=peaks["source"], us_per_launch=1000.0 * ms, algorithmic_bytes=alg_bytes,
-                tensor=dict(achieved=flops / ms / 1e9, peak=peaks["bf16_tflops"] * (1.0 if dtype == "bf16" else 0.5),
-                            unit="TFLOP/s", frac=flops / ms / 1e9 / (peaks["bf16_tflops"] * (1.0 if dtype == "bf16" else 0.5))))
+                achieved=achieved, peak=peaks["hbm_gbs"], unit="GB/s", frac=achieved / peaks["hbm_gbs"],
+                traffic=measured_traffic("dcn_fwd_tc_kernel", dtype),
+                note="gather-bound: the sampler pulls 4*9*H*W*Cin*s = 604 MB through the L1/LSU path per launch (DESIGN.md 3.1); "
+                     "traffic = dram bytes of this launch in profiles/r02_* (ncu --set full), null if not captured this round",
+                peak_source=peaks["source"], us_per_launch=1000.0 * ms, algorithmic_bytes=alg_bytes, launches_timed=n,
+                tensor=dict(achieved=flops / ms / 1e9, peak=tpeak, unit="TFLOP/s", frac=flops / ms / 1e9 / tpeak))
+
+
+def time_calls(torch, fn, iters, flush):
+    """median CUDA-event time (ms) of fn() over `iters` runs, L2 flushed (256 MB memset) before every run."""
+    for _ in range(2):
+        fn()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(iters):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    ts = sorted(a.elapsed_time(b) for a, b in evs)
+    return ts[len(ts) // 2]
+
+
+def dcn_layer_sweep(torch, peaks, batches=(1, 4, 16), iters=5):
+    """BASELINE.json configs[2] + the metric's second half: DCNv2 forward + backward (all five gradients) per IDAUp
+    shape class through the C ABI, bf16.  FLOPs(fwd+bwd) = 3 * 2*Cout*Cin*9*H*W*B (dgrad + wgrad GEMMs; sampling not
+    counted); bytes = s*B*H*W*((Cin+27+Cout) + (2*Cin+54+Cout)).  Sustained tensor peak (long runs)."""
+    import centerpoly_b200 as cp
+    from centerpoly_b200 import dcn_v2 as D
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    tpeak = peaks["bf16_tflops"]
+    rows = []
+    for B in batches:
+        for (Cin, Cout, h, w) in SWEEP_SHAPES:
+            g = torch.Generator(device="cuda").manual_seed(317 + Cin + B)
+            x = torch.randn(B, Cin, h, w, device="cuda", generator=g).bfloat16().contiguous(memory_format=torch.channels_last)
+            om = torch.randn(B, 27, h, w, device="cuda", generator=g)
+            om[:, :18] *= 2.0
+            om = om.bfloat16().contiguous(memory_format=torch.channels_last)
+            gout = torch.randn(B, Cout, h, w, device="cuda", generator=g).bfloat16().contiguous(memory_format=torch.channels_last)
+            m = cp.DCN(Cin, Cout, (3, 3), 1, 1).cuda()
+            wgt, bias = m.weight.detach(), m.bias.detach()
+            off, msk = om[:, :18], om[:, 18:]
+            fwd = lambda: D._forward_impl(x, off, msk, wgt, bias, (1, 1), (1, 1), (1, 1), 1, True)
+            bwd = lambda: D._backward_impl(x, off, msk, wgt, gout, (1, 1), (1, 1), (1, 1), 1, True, (True,) * 5)
+            t_f = time_calls(torch, fwd, iters, flush)
+            t_b = time_calls(torch, bwd, iters, flush)
+            flops = 3 * 2.0 * Cout * Cin * 9 * h * w * B
+            byts = 2 * B * h * w * ((Cin + 27 + Cout) + (2 * Cin + 54 + Cout))
+            t = t_f + t_b
+            rows.append(dict(shape=f"{Cin}->{Cout}@{h}x{w}", B=B, fwd_ms=round(t_f, 4), bwd_ms=round(t_b, 4),
+                             tflops=round(flops / t / 1e9, 1), frac_tensor=round(flops / t / 1e9 / tpeak, 4),
+                             gbs=round(byts / t / 1e6, 1), frac_hbm=round(byts / t / 1e6 / peaks["hbm_gbs"], 4)))
+            del x, om, gout
+    best = max(rows, key=lambda r: r["tflops"])
+    return dict(metric="DCNv2 fwd+bwd TFLOP/s vs tensor peak (configs[2])", dtype="bf16", peak_tflops=tpeak, peak_hbm_gbs=peaks["hbm_gbs"],
+                timing="median of %d, CUDA events, L2 flushed before every call" % iters, best=best, rows=rows)
+
+
+def train_step_bench(torch, dist, world, rank, steps=5, warmup=3, batch=16):
+    """BASELINE.json configs[3]: data-parallel polydet training step, 16 crops of 1024x512 per GPU, bf16 autocast, focal +
+    polar L1 + polygon IoU loss (PolydetLoss l1+iou), Adam; the one exchange step is the bucketed NCCL gradient all-reduce."""
+    from centerpoly_b200.harness.dla34 import PolydetDLA34, calibrate_random_init
+    from centerpoly_b200.harness.train import DataParallelTrainer, polydet_l1_iou_loss, synthetic_batch
+    from centerpoly_b200.neck import use_training_upsamplers
+    torch.backends.cudnn.benchmark = True
+    torch.manual_seed(317)
+    net = PolydetDLA34().cuda().to(memory_format=torch.channels_last)
+    calibrate_random_init(net, 128, 256)
+    use_training_upsamplers(net)
+    trainer = DataParallelTrainer(net, lr=2e-4, dtype=torch.bfloat16, loss_fn=polydet_l1_iou_loss)
+    data = synthetic_batch(batch, 512, 1024, device="cuda", seed=1000 + rank, rep="polar")
+    data["input"] = data["input"].contiguous(memory_format=torch.channels_last)
+    first = None
+    for _ in range(warmup):
+        loss = trainer.step(data)
+        first = float(loss) if first is None else first
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    trainer.timing = True
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    exch = []
+    for _ in range(steps):
+        loss = trainer.step(data)
+        exch.append(trainer._ev)
+    b.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b)
+    exposed = span = None
+    if world > 1:
+        evs = trainer.reducer.last_launch_events
+        exposed = float(np.median([e[0].elapsed_time(e[1]) for e in exch]))
+        span = evs[0][1].elapsed_time(exch[-1][1]) if evs else None
+        t = torch.tensor([ms, exposed], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, exposed = t.tolist()
+    n_param = sum(p.numel() for p in net.parameters())
+    out = dict(workload="configs[3]: polydet dla_34 training step, 1024x512 crops, 16/GPU, focal + polar L1 + polygon IoU, Adam (fused), bf16 autocast",
+               value=world * batch * steps / (ms / 1000.0), unit="images/s", n_gpus=world, ms_per_step=ms / steps, steps=steps,
+               batch_per_gpu=batch, loss_first=first, loss_last=float(loss), scaling="weak",
+               allreduce=dict(backend="nccl" if world > 1 else None, bytes_per_step=4 * n_param if world > 1 else 0,
+                              buckets=len(trainer.reducer.buckets), exposed_ms_per_step=exposed, span_ms_last_step=span,
+                              note="exposed = main stream waiting for the bucketed all-reduces after backward ended (CUDA events, median over steps, max over ranks); "
+                                   "span = first bucket enqueued -> exchange complete (runs under the rest of backward)"))
+    trainer.reducer.remove()
+    del trainer, net, data
+    torch.cuda.empty_cache()
+    return out
+
+
+def idd_polar_bench(torch, dist, world, rank, local_rank, steps=5, warmup=3, per_gpu=8):
+    """BASELINE.json configs[4]: polar-vertex polydet inference on IDD-shape frames (1920x1080 padded to 1952x1088,
+    SURVEY 8), 9 classes, rep='polar', 64 images sharded 8 per GPU; resident and end-to-end (pinned host batch in,
+    detections out, every step)."""
+    from centerpoly_b200.harness.engine import PolydetEngine
+    h, w = 1088, 1952
+    eng = PolydetEngine(h, w, batch=per_gpu, dtype="bf16", K=K_DET, rep="polar", heads={"hm": 9, "poly": 2 * N_VTX, "pseudo_depth": 1, "reg": 2},
+                        device=f"cuda:{local_rank}", n_slots=2)
+    g = torch.Generator().manual_seed(2000 + rank)
+    host = [torch.randn(per_gpu, 3, h, w, generator=g).contiguous(memory_format=torch.channels_last).pin_memory() for _ in range(2)]
+    eng.set_resident_frames([f.cuda(non_blocking=True) for f in host])
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(warmup):
+        eng.infer_resident(i)
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(eng.stream)
+    for i in range(steps):
+        eng.infer_resident(i)
+    b.record(eng.stream)
+    barrier()
+    ms = a.elapsed_time(b)
+    eng.infer_host_stream(host, warmup)
+    barrier()
+    t0 = time.perf_counter()
+    eng.infer_host_stream(host, steps)
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1000.0
+    if world > 1:
+        t = torch.tensor([ms, e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_ms = t.tolist()
+    out = dict(workload="configs[4]: polar-vertex polydet inference, IDD-shape 1920x1080 (padded 1952x1088), 9 classes, %d images/GPU" % per_gpu,
+               value=world * per_gpu * steps / (ms / 1000.0), unit="images/s", n_gpus=world, global_batch=world * per_gpu,
+               ms_per_step=ms / steps, steps=steps, rep="polar", scaling="weak",
+               e2e=dict(value=world * per_gpu * steps / (e2e_ms / 1000.0), unit="images/s", ms_per_step=e2e_ms / steps,
+                        h2d_bytes_per_step=eng.h2d_bytes_per_step, d2h_bytes_per_step=eng.d2h_bytes_per_step))
+    del eng, host
+    torch.cuda.empty_cache()
+    return out
+
+
+def infer_bench(torch, dist, args, world, rank, local_rank, dtype, sustained_seconds=0.0):
+    """configs[1]: frames/s resident (CUDA events on the engine stream) and end to end (pinned host frame in, detections out)."""
+    from centerpoly_b200.harness.engine import PolydetEngine
+    eng = PolydetEngine(H, W, batch=1, dtype=dtype, K=K_DET, device=f"cuda:{local_rank}", n_slots=4)
+    # per-image sharding: every rank owns its own frames (weak scaling, no data-path collective)
+    g = torch.Generator().manual_seed(1000 + rank)
+    host_frames = [torch.randn(1, 3, H, W, generator=g).contiguous(memory_format=torch.channels_last).pin_memory() for _ in range(4)]
+    eng.set_resident_frames([f.cuda(non_blocking=True) for f in host_frames])
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(n):
+        sampler = ClockSampler(physical_gpu_index(local_rank)).start()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(eng.stream)
+        for i in range(n):
+            eng.infer_resident(i)
+        b.record(eng.stream)
+        barrier()
+        return a.elapsed_time(b), sampler.stop()
+
+    for i in range(max(3, args.warmup)):
+        eng.infer_resident(i)
+    barrier()
+    ms_total, clocks = timed(args.steps)
+    # ---- end to end: pinned host frame in, detections out, every step
+    eng.infer_host_stream(host_frames, max(3, args.warmup))
+    barrier()
+    t0 = time.perf_counter()
+    eng.infer_host_stream(host_frames, args.steps)
+    torch.cuda.synchronize()
+    e2e_ms_total = (time.perf_counter() - t0) * 1000.0
+    sus = None
+    if sustained_seconds > 0:
+        n = max(args.steps, int(sustained_seconds * 1000.0 / (ms_total / args.steps)) + 1)
+        barrier()
+        ms_s, clocks_s = timed(n)
+        if world > 1:
+            t = torch.tensor([ms_s], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_s = float(t)
+        sus = dict(value=world * n / (ms_s / 1000.0), unit="frames/s", steps=n, seconds=ms_s / 1000.0, ms_per_step=ms_s / n, clocks=clocks_s)
+    if world > 1:
+        t = torch.tensor([ms_total, e2e_ms_total], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, e2e_ms_total = t.tolist()
+    res = dict(value=world * args.steps / (ms_total / 1000.0), ms_per_step=ms_total / args.steps,
+               e2e=dict(value=world * args.steps / (e2e_ms_total / 1000.0), unit="frames/s", h2d_bytes_per_step=eng.h2d_bytes_per_step,
+                        d2h_bytes_per_step=eng.d2h_bytes_per_step, ms_per_step=e2e_ms_total / args.steps),
+               clocks=clocks, sustained=sus, launches_per_step=eng.launches_per_step)
+    del eng, host_frames
+    torch.cuda.empty_cache()
+    return res
 
 
 def run_ours(args):
@@ -219,74 +464,56 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    from centerpoly_b200.harness.engine import PolydetEngine
+    skip = set(s for s in args.skip.split(",") if s)
     peaks = read_peaks()
-    eng = PolydetEngine(H, W, batch=1, dtype=args.dtype, K=K_DET, device=f"cuda:{local_rank}", n_slots=4)
-    # per-image sharding: every rank owns its own frames (weak scaling, no data-path collective)
-    g = torch.Generator().manual_seed(1000 + rank)
-    host_frames = [torch.randn(1, 3, H, W, generator=g).contiguous(memory_format=torch.channels_last).pin_memory() for _ in range(4)]
-    eng.set_resident_frames([f.cuda(non_blocking=True) for f in host_frames])
-    torch.cuda.synchronize()
+    extra, errors = {}, {}
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    def section(name, fn):
+        """Secondary workloads never take the headline down: a failure is reported in the line instead."""
+        if name in skip:
+            return
+        try:
+            extra[name] = fn()
+        except Exception as e:      # noqa: BLE001
+            errors[name] = f"{type(e).__name__}: {e}"[:300]
+            if world > 1:
+                raise
 
-    # ---- device-resident throughput
-    for i in range(max(3, args.warmup)):
-        eng.infer_resident(i)
-    barrier()
-    sampler = ClockSampler(physical_gpu_index(local_rank)).start()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with torch.cuda.stream(eng.stream):
-        a.record(eng.stream)
-    for i in range(args.steps):
-        eng.infer_resident(i)
-    with torch.cuda.stream(eng.stream):
-        b.record(eng.stream)
-    barrier()
-    clocks = sampler.stop()
-    ms_total = a.elapsed_time(b)
-    # ---- end to end: pinned host frame in, detections out, every step
-    eng.infer_host_stream(host_frames, max(3, args.warmup))
-    barrier()
-    t0 = time.perf_counter()
-    eng.infer_host_stream(host_frames, args.steps)
-    torch.cuda.synchronize()
-    e2e_ms_total = (time.perf_counter() - t0) * 1000.0
-    if world > 1:
-        t = torch.tensor([ms_total, e2e_ms_total], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total, e2e_ms_total = t.tolist()
-    value = world * args.steps / (ms_total / 1000.0)
-    e2e_value = world * args.steps / (e2e_ms_total / 1000.0)
+    main = infer_bench(torch, dist, args, world, rank, local_rank, args.dtype, sustained_seconds=0.0 if "sustained" in skip else 2.0)
+    if args.dtype == "bf16":
+        section("fp32", lambda: {k: v for k, v in infer_bench(torch, dist, args, world, rank, local_rank, "fp32").items()
+                                 if k in ("value", "ms_per_step", "e2e")} | dict(unit="frames/s", dtype="f32 (TF32 tensor cores)", n_gpus=world))
+    section("train", lambda: train_step_bench(torch, dist, world, rank))
+    section("idd_polar", lambda: idd_polar_bench(torch, dist, world, rank, local_rank))
     if rank == 0:
         roof = dominant_kernel_roofline(torch, args.dtype, args.steps, peaks)
+        section("dcn_sweep", lambda: dcn_layer_sweep(torch, peaks))
         cpu = None
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and "cpu" not in skip:
             threads = os.cpu_count() or 1
             arm = CpuArm(threads)
             arm.frame_seconds(256, 512)   # warm-up (thread pool, allocator)
-            t_cpu = arm.frame_seconds(512, 1024)
-            cpu = dict(value=1.0 / (4.0 * t_cpu), unit="frames/s", cores=threads, kind="port",
-                       sample="one 1024x512 crop (1/4 of the 2048x1024 frame, cost linear in pixels) through the same DLA-34 "
-                              "network with torchvision CPU deform_conv2d + numpy decode and post-process oracles; %.2f s" % t_cpu)
-        # our kernels per frame, counted by the shims on a warm eager frame: 16 dcn_fwd_tc_kernel (+ a combine kernel
-        # on the tap-split layers) + 8 upsample_nhwc_kernel + 3 decode kernels
-        launches_per_step = eng.launches_per_step
-        line = dict(metric=METRIC, value=value, unit="frames/s", n_gpus=world, steps=args.steps, warmup=max(3, args.warmup),
-                    ms_per_step=ms_total / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
+            t_cpu = arm.frame_seconds(H, W)
+            cpu = dict(value=1.0 / t_cpu, unit="frames/s", cores=threads, kind=CpuArm.KIND,
+                       sample="one full 2048x1024 frame, %.2f s; %s" % (t_cpu, CpuArm.WHAT))
+        line = dict(metric=METRIC, value=main["value"], unit="frames/s", n_gpus=world, steps=args.steps, warmup=max(3, args.warmup),
+                    ms_per_step=main["ms_per_step"], higher_is_better=True, scaling="weak", vs_baseline=None,
                     dtype=("bf16" if args.dtype == "bf16" else "f32"), data="synthetic",
                     config=dict(workload="configs[1]: polydet dla_34 inference, batch 1, synthetic 2048x1024 Cityscapes-shape",
                                 global_batch=world, K=K_DET, classes=N_CLS, vertices=N_VTX, parallelism=f"per-image x{world}",
                                 init="random weights, BN-calibrated (SURVEY A.5)", cuda_graph=True,
                                 l2="4 distinct frames rotate; one step writes/reads > 1 GB of activations (L2 is 126 MB), so nothing survives between steps"),
-                    e2e=dict(value=e2e_value, unit="frames/s", h2d_bytes_per_step=eng.h2d_bytes_per_step,
-                             d2h_bytes_per_step=eng.d2h_bytes_per_step, ms_per_step=e2e_ms_total / args.steps),
-                    gpu_launches=launches_per_step * args.steps, clocks=clocks, roofline=roof)
+                    e2e=main["e2e"],
+                    # our kernels per frame, counted by the shims on a warm eager frame (DCN + combine, up-sampler, stem,
+                    # max-pool, decode kernels) x the timed steps
+                    gpu_launches=main["launches_per_step"] * args.steps, clocks=main["clocks"], roofline=roof)
+        if main["sustained"] is not None:
+            line["sustained"] = main["sustained"]
         if cpu is not None:
             line["cpu_baseline"] = cpu
+        line.update(extra)
+        if errors:
+            line["errors"] = errors
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -300,8 +527,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--skip", default="", help="comma list of fp32,train,idd_polar,dcn_sweep,cpu,sustained (development shortcut)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    if args.no_cpu_baseline:
+        args.skip += ",cpu"
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -3,10 +3,10 @@ the DCNv2 modulated deformable convolution of the DLA-34 neck (forward + backwar
 ``polydet_decode``.  Host code is Python/PyTorch for memory and streams only; the arithmetic lives in
 ``libcpoly.so`` (hand-written CUDA behind the C ABI of ``include/cpoly.h``).
 """
-from .dcn_v2 import DCN, DCNv2, _DCNv2, dcn_v2_conv, set_dcn_path  # noqa: F401
+from .dcn_v2 import DCN, DCNv2, _DCNv2, dcn_v2_conv, invalidate_packed_weights, set_dcn_path  # noqa: F401
 from .decode import polydet_decode, polydet_decode_from_logits  # noqa: F401
 from .raster import CITYSCAPES_CLASSES, RasterResult, rasterise_instances  # noqa: F401
 from .post_process import batch_inverse_affine, group_by_class, inverse_affine, polydet_post_process  # noqa: F401
 
 __version__ = "0.1.0"
-from .poly_loss import IOU_STATUS, PolyLoss, poly_iou_loss  # noqa: F401
+from .poly_loss import IOU_STATUS, PolyLoss, poly_iou_loss, poly_order_loss  # noqa: F401

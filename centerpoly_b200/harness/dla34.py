@@ -224,14 +224,14 @@ def dcn_modules(net: nn.Module):
     return [m for m in net.modules() if hasattr(m, "conv_offset_mask")]
 
 
-def calibrate_random_init(net: nn.Module, height: int, width: int, seed: int = 317, device="cpu") -> nn.Module:
+def calibrate_random_init(net: nn.Module, height: int, width: int, seed: int = 317, device="cpu", offset_std: float = 0.05) -> nn.Module:
     """SURVEY §A.5 recipe: random weights stay random, but (a) the DCN offset convs get small random weights so
     the offsets are non-trivial and (b) one train-mode forward with BN momentum 1.0 makes the running statistics
     consistent with the activations, so the heat map is tie-free instead of degenerate."""
     g = torch.Generator().manual_seed(seed)
     for m in dcn_modules(net):
         with torch.no_grad():
-            m.conv_offset_mask.weight.copy_(torch.randn(m.conv_offset_mask.weight.shape, generator=g) * 0.05)
+            m.conv_offset_mask.weight.copy_(torch.randn(m.conv_offset_mask.weight.shape, generator=g) * offset_std)
             m.conv_offset_mask.bias.copy_(torch.randn(m.conv_offset_mask.bias.shape, generator=g) * 1.0)
     bns = [m for m in net.modules() if isinstance(m, nn.BatchNorm2d)]
     for m in bns:

@@ -25,7 +25,7 @@ HEADS = {"hm": 8, "poly": 64, "pseudo_depth": 1, "reg": 2}
 class PolydetEngine:
     def __init__(self, height=1024, width=2048, batch=1, dtype="bf16", K=100, rep="cartesian", heads=None,
                  device="cuda:0", seed=317, calibrate=True, use_graph=True, n_slots=2, optimize=True, post_process=True,
-                 rasterise=False, thresh=0.05):
+                 rasterise=False, thresh=0.05, net=None):
         self.device = torch.device(device)
         self.dtype = dtype
         self.K, self.rep = K, rep
@@ -33,9 +33,12 @@ class PolydetEngine:
         self.shape = (batch, 3, height, width)
         torch.manual_seed(seed)
         torch.backends.cudnn.benchmark = True     # as the reference does (src/main.py:32): let cuDNN time its algorithms
-        net = PolydetDLA34(self.heads).to(self.device).to(memory_format=torch.channels_last)
-        if calibrate:
-            calibrate_random_init(net, height, width, seed=seed)
+        if net is None:
+            net = PolydetDLA34(self.heads).to(self.device).to(memory_format=torch.channels_last)
+            if calibrate:
+                calibrate_random_init(net, height, width, seed=seed)
+        else:       # a caller-built network (same module tree, e.g. loaded from a checkpoint); it is rewritten in place below
+            net = net.to(self.device).to(memory_format=torch.channels_last)
         net = net.eval()
         self.fusion = None
         self.in_channels = 3

@@ -115,12 +115,88 @@ def test_backward_vs_oracle(shape, dtype):
         gate(got[name], want[name], tol, name)
 
 
-def test_backward_is_deterministic_for_weights():
-    case = make_dcn_case(7, 2, 64, 64, 12, 20)
-    a = run_ours(case, "auto", channels_last=True)
-    b = run_ours(case, "auto", channels_last=True)
-    for name in ("y", "goffset", "gmask", "gw", "gb"):
-        np.testing.assert_array_equal(a[name], b[name], err_msg=name)
+@pytest.mark.parametrize("shape", [(2, 64, 64, 12, 20), (1, 128, 64, 40, 56), (1, 64, 64, 70, 90)], ids=lambda s: "x".join(map(str, s)))
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32], ids=["bf16", "fp32"])
+def test_backward_is_bitwise_deterministic(shape, dtype):
+    """Every output of the backward, grad_input included, is bit-identical from run to run: the col2im is a
+    gather over a sorted contribution list (csrc/dcn_col2im.cu), there is no floating-point atomic on the path."""
+    case = make_dcn_case(7, *shape, dtype=dtype)
+    a = run_ours(case, "auto", dtype=dtype, channels_last=True)
+    for _ in range(2):
+        b = run_ours(case, "auto", dtype=dtype, channels_last=True)
+        for name in ("y", "gx", "goffset", "gmask", "gw", "gb"):
+            np.testing.assert_array_equal(a[name], b[name], err_msg=name)
+
+
+FULL_GOLDEN = sorted(glob.glob(os.path.join(GOLDEN, "dcnfull_*.npz")))
+
+
+def _take(t, flat):
+    B, C, H, W = t.shape
+    return t.permute(0, 2, 3, 1).reshape(B * H * W, C)[flat]
+
+
+@pytest.mark.parametrize("path", FULL_GOLDEN, ids=lambda p: os.path.basename(p)[:-4])
+def test_full_size_vs_torchvision_golden(path):
+    """BASELINE.json configs[2] shapes at FULL size (64->64 @256x512, 128->128 @128x256; B = 1 and 4), random offsets
+    with 5 % far taps: forward + all five gradients against torchvision.deform_conv2d float64 (fixtures made by
+    tests/golden/make_dcn_fullsize_golden.py: expected values at 2048 seeded pixels, gw / gb in full, norms of the full
+    tensors).  Inputs are regenerated from the stored seed.  bf16-rounded inputs are run in bf16 (1e-2) and fp32
+    (1e-3) mode, fp32 inputs in fp32 mode.  The full tensors are additionally cross-checked against the generic
+    CUDA-core path, which sees every pixel."""
+    g = np.load(path)
+    B, Cin, Cout, H, W = (int(v) for v in g["shape"])
+    rounding = torch.bfloat16 if str(g["rounding"]) == "bfloat16" else torch.float32
+    case = make_dcn_case(int(g["seed"]), B, Cin, Cout, H, W, dtype=rounding)
+    flat = torch.from_numpy(g["positions"])
+    modes = [torch.float32] if rounding == torch.float32 else [torch.bfloat16, torch.float32]
+    ref_full = None
+    for dtype in modes:
+        tol = 1e-2 if dtype == torch.bfloat16 else 1e-3
+        got = run_ours(case, "tcgen05", dtype=dtype, channels_last=True)
+        for name in ("y", "gx", "goffset", "gmask"):
+            want = g[name].astype(np.float64)
+            have = _take(torch.from_numpy(got[name]), flat).numpy().astype(np.float64)
+            err_max = np.abs(have - want).max() / float(g[name + "_max"])
+            err_l2 = np.linalg.norm(have - want) / np.linalg.norm(want)
+            assert err_max <= tol and err_l2 <= tol, f"{name} [{dtype}]: max-rel {err_max:.3e}, l2-rel {err_l2:.3e} > {tol}"
+            l2 = np.linalg.norm(got[name].astype(np.float64))
+            assert abs(l2 - float(g[name + "_l2"])) <= tol * float(g[name + "_l2"]), f"{name} [{dtype}]: full-tensor norm"
+        gate(got["gw"], g["gw"], tol, "gw")
+        gate(got["gb"], g["gb"], tol, "gb")
+        if dtype == torch.float32 and B == 1:   # every pixel: tensor-core path vs the CUDA-core path (IEEE fp32)
+            ref_full = run_ours(case, "simt", dtype=torch.float32, channels_last=True)
+            for name in ("y", "gx", "goffset", "gmask", "gw", "gb"):
+                gate(got[name], ref_full[name], 1e-3, "full-tensor " + name)
+
+
+def test_fused_adam_step_is_seen_by_the_next_forward():
+    """torch._fused_adam_ updates parameters without bumping Tensor._version: the packed weight image must not be
+    served from the cache in a differentiated forward (dcn_v2._PackedWeights)."""
+    import centerpoly_b200 as cp
+    torch.manual_seed(5)
+    m = cp.DCN(64, 64, (3, 3), 1, 1).cuda().to(memory_format=torch.channels_last)
+    torch.nn.init.normal_(m.conv_offset_mask.weight, std=0.05)
+    opt = torch.optim.Adam(m.parameters(), lr=0.05, fused=True)
+    x = torch.randn(2, 64, 16, 32, device="cuda").contiguous(memory_format=torch.channels_last)
+    y0 = m(x)
+    y0.square().mean().backward()
+    w_before = m.weight.detach().clone()
+    opt.step()
+    assert not torch.equal(w_before, m.weight.detach())
+    y1 = m(x)                                   # training-mode forward after the fused step
+    with torch.no_grad():
+        om = m.conv_offset_mask(x)
+        want = cp.dcn_v2_conv(x, om[:, :18], torch.sigmoid(om[:, 18:]), m.weight.detach().clone(), m.bias.detach().clone(), 1, 1, 1, 1)
+    gate(y1.detach().float().cpu().numpy(), want.float().cpu().numpy(), 1e-5, "forward after fused Adam")
+    assert not torch.allclose(y1.detach(), y0.detach())
+    # no-grad inference after an out-of-band update: the cache is dropped by hand
+    with torch.no_grad():
+        m.weight.data.mul_(2.0)                 # .data: no version bump
+        cp.invalidate_packed_weights(m)
+        y2 = m(x)
+        want2 = cp.dcn_v2_conv(x, om[:, :18], torch.sigmoid(om[:, 18:]), m.weight.detach().clone(), m.bias.detach().clone(), 1, 1, 1, 1)
+    gate(y2.float().cpu().numpy(), want2.float().cpu().numpy(), 1e-5, "forward after invalidate")
 
 
 def test_nchw_input_is_accepted():
