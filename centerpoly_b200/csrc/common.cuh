@@ -130,6 +130,10 @@ int dcn_wgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_
 bool dcn_tc_dgrad_eligible(const cpoly_dcn_bwd_args& a);
 size_t dcn_tc_dgrad_workspace(const cpoly_dcn_bwd_args& a);
 int dcn_dgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+bool dcn_col2im_eligible(const cpoly_dcn_bwd_args& a);
+size_t dcn_col2im_gcol_bytes(const cpoly_dcn_fwd_args& f);
+size_t dcn_col2im_workspace(const cpoly_dcn_bwd_args& a);
+int dcn_col2im_launch(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream);
 int idaup_upsample_backward_launch(const cpoly_upsample_bwd_args& a, cudaStream_t stream);
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K);

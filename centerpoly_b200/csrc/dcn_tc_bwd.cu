@@ -341,15 +341,16 @@ int dcn_wgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_
 //   gcol[px,(tap,c)] = sum_o gout[px,o] * W[o,c,tap]                       (tcgen05: M = 128 pixels, N = channel chunk, K = Cout)
 //   grad_mask[px,tap]      = sum_c gcol * v_c(p)                           v = bilinear sample (unmasked)
 //   grad_offset[px,2tap..] = m * sum_c gcol * dv_c/dp                      floor-based corner differences
-//   grad_input[corner,c]  += gcol * m * w_corner                           vector reductions (red.global.add.v4.f32)
+//   gcol is ALSO stored, one coalesced 16-byte store per lane, for the atomics-free col2im that follows
+//   (dcn_col2im.cu: grad_input[corner,c] += gcol * m * w_corner in gather form, bit-reproducible).
 //
 // Persistent warp-specialised CTA; a work item is (128-pixel tile, tap group) as in the forward kernel.
 //   warps 0-3  TMEM -> shared: the gcol tile of one block, converted to T, in the sampler's row layout
 //   warp  4    bulk-copies the block's pre-packed dgrad weights (K-major, rows = input channels) into a 2-stage ring
 //   warp  5    issues the MMAs (A = the item's gout tile, loaded once per item by the samplers)
 //   warps 6-21 gather the 4 corners of every (pixel, tap) exactly like the forward sampler, combine them with gcol,
-//              reduce the coordinate gradients over the 8 lanes of a pixel row (written once, no atomics) and scatter
-//              grad_input.
+//              reduce the coordinate gradients over the 8 lanes of a pixel row (written once, no atomics) and store
+//              their piece of the gcol row.
 namespace {
 
 constexpr int D_BUFS = 2;          // TMEM accumulators and shared gcol tiles
@@ -364,7 +365,7 @@ struct DgradParams {
   Geom g;
   const void* gout;        // dense NHWC (B,H,W,Cout), element type T
   const void* wpacked;     // dgrad weight image, see pack_dgrad_weights_kernel
-  float* gx;               // dense NHWC fp32 (B,H,W,Cin), pre-zeroed; or NULL
+  void* gcol;              // [B*H*W][9][Cin] element type T for dcn_col2im.cu; or NULL (grad_input not requested)
   cpoly_tensor4 goffset, gmask;   // fp32, any strides; ptr may be NULL
   int nchunk;              // channel chunks per tap
   int split, taps_per_item, num_items;
@@ -373,10 +374,6 @@ struct DgradParams {
   int w_stage_bytes;
 };
 
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
-}
-
 // Four channels of one (pixel, tap): v[q][e] corner values (invalid corners already zeroed), g[e] = gcol.
 struct TapCtx {
   float w[4];      // bilinear weights (unmasked)
@@ -384,7 +381,7 @@ struct TapCtx {
   uint32_t flags;  // bit q: corner q valid
 };
 __device__ __forceinline__ void quad_accumulate(const float (&v)[4][4], const float (&g)[4], const TapCtx& t, float& sm, float& sy,
-                                                float& sx, float (&out)[4][4]) {
+                                                float& sx) {
   const float hy = 1.0f - t.ly, hx = 1.0f - t.lx;
 #pragma unroll
   for (int e = 0; e < 4; ++e) {
@@ -394,9 +391,6 @@ __device__ __forceinline__ void quad_accumulate(const float (&v)[4][4], const fl
     sm = fmaf(g[e], val, sm);
     sy = fmaf(g[e], ty, sy);
     sx = fmaf(g[e], tx, sx);
-    const float gm = g[e] * t.m;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) out[q][e] = gm * t.w[q];
   }
 }
 
@@ -506,18 +500,17 @@ __global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
           const uint4 pm = lds16(pm_s + idx);
           const uint32_t flags = pm.w;
           if (flags & 15u) {
-            const uint4 po = lds16(poff_s + idx), pwv = lds16(pw_s + idx);
+            const uint4 pwv = lds16(pw_s + idx);
             const uint4 gq = lds16(gt + (uint32_t)r * ROW_BYTES + (uint32_t)((cg ^ (r & 7)) << 4));
             TapCtx t;
             t.w[0] = __uint_as_float(pwv.x); t.w[1] = __uint_as_float(pwv.y); t.w[2] = __uint_as_float(pwv.z); t.w[3] = __uint_as_float(pwv.w);
             t.m = __uint_as_float(pm.x); t.ly = __uint_as_float(pm.y); t.lx = __uint_as_float(pm.z); t.flags = flags;
-            const uint32_t offs[4] = {po.x, po.y, po.z, po.w};
             const uint32_t* cw[4] = {&c[pass][0].x, &c[pass][1].x, &c[pass][2].x, &c[pass][3].x};
             const uint32_t* gw = &gq.x;
             constexpr int kQuads = kVec / 4;   // 2 (bf16) or 1 (fp32)
 #pragma unroll
             for (int h = 0; h < kQuads; ++h) {
-              float v[4][4], g[4], out[4][4];
+              float v[4][4], g[4];
 #pragma unroll
               for (int qq = 0; qq < 4; ++qq) {
                 const bool ok = (flags >> qq) & 1u;
@@ -537,14 +530,12 @@ __global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
                 g[0] = __uint_as_float(gw[2 * h] << 16); g[1] = __uint_as_float(gw[2 * h] & 0xffff0000u);
                 g[2] = __uint_as_float(gw[2 * h + 1] << 16); g[3] = __uint_as_float(gw[2 * h + 1] & 0xffff0000u);
               }
-              quad_accumulate(v, g, t, sm[pass], sy[pass], sx[pass], out);
-              if (p.gx) {
-#pragma unroll
-                for (int qq = 0; qq < 4; ++qq)
-                  if ((flags >> qq) & 1u)
-                    red_add_v4(p.gx + (offs[qq] / (uint32_t)sizeof(T)) + (uint32_t)(cc * kChunk + cg * kVec + h * 4), out[qq][0],
-                               out[qq][1], out[qq][2], out[qq][3]);
-              }
+              quad_accumulate(v, g, t, sm[pass], sy[pass], sx[pass]);
+            }
+            if (p.gcol) {   // this lane's 16 bytes of the (pixel, tap) row of gcol, as the tensor cores produced it
+              const int yy = ty0 + (r >> 4), xx = tx0 + (r & (TILE_W - 1));
+              const size_t row = (size_t)((b * p.g.H + yy) * p.g.W + xx) * NUM_TAPS + (size_t)(tap0 + kl);
+              *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.gcol) + (row * p.g.Cin + (size_t)(cc * kChunk)) * sizeof(T) + (size_t)cg * 16) = gq;
             }
           }
           if (q + 1 < blocks_per_item) issue(q + 1, pass);
@@ -749,32 +740,39 @@ bool dcn_tc_dgrad_eligible(const cpoly_dcn_bwd_args& a) {
   f.weight_packed = nullptr;
   if (!dcn_tc_eligible(f)) return false;
   if (!dense_nhwc4(a.gout, a.f.Cout, a.f.H, a.f.W)) return false;
-  if (a.gx.ptr && (!dense_nhwc4(a.gx, a.f.Cin, a.f.H, a.f.W) || (reinterpret_cast<uintptr_t>(a.gx.ptr) & 15))) return false;
+  if (a.gx.ptr && !dcn_col2im_eligible(a)) return false;
   return plan_dgrad(a.f).ok;
 }
 
-size_t dcn_tc_dgrad_workspace(const cpoly_dcn_bwd_args& a) { return plan_dgrad(a.f).packed_bytes + 256; }
+static size_t dgrad_packed_aligned(const cpoly_dcn_fwd_args& f) { return (plan_dgrad(f).packed_bytes + 255) / 256 * 256; }
+
+// [dgrad weight image | gcol + boxes of the col2im (only when grad_input is requested)]
+size_t dcn_tc_dgrad_workspace(const cpoly_dcn_bwd_args& a) {
+  return dgrad_packed_aligned(a.f) + (a.gx.ptr ? dcn_col2im_workspace(a) : 0) + 256;
+}
 
 int dcn_dgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   const cpoly_dcn_fwd_args& f = a.f;
   const DgradPlan d = plan_dgrad(f);
   CPOLY_REQUIRE(d.ok, CPOLY_EUNSUPPORTED, "dgrad plan does not fit");
-  CPOLY_REQUIRE(workspace && workspace_bytes >= d.packed_bytes && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0, CPOLY_EWORKSPACE,
-                "dcn dgrad workspace too small or misaligned: need %zu bytes, have %zu", d.packed_bytes, workspace_bytes);
+  const size_t need = dcn_tc_dgrad_workspace(a) - 256;
+  CPOLY_REQUIRE(workspace && workspace_bytes >= need && (reinterpret_cast<uintptr_t>(workspace) & 255) == 0, CPOLY_EWORKSPACE,
+                "dcn dgrad workspace too small or misaligned: need %zu bytes, have %zu", need, workspace_bytes);
+  CPOLY_REQUIRE(!a.gx.ptr || dcn_col2im_eligible(a), CPOLY_EUNSUPPORTED, "grad_input layout not supported by the col2im");
+  uint8_t* c2i_ws = reinterpret_cast<uint8_t*>(workspace) + dgrad_packed_aligned(f);   // gcol first, boxes behind it
   const bool bf = f.dtype == CPOLY_BF16;
   const int64_t pieces = (int64_t)d.packed_bytes / 16;
   const unsigned pblocks = (unsigned)((pieces + 255) / 256);
   if (bf) pack_dgrad_weights_kernel<__nv_bfloat16><<<pblocks, 256, 0, stream>>>(f.weight, reinterpret_cast<uint4*>(workspace), f.Cin, f.Cout);
   else pack_dgrad_weights_kernel<float><<<pblocks, 256, 0, stream>>>(f.weight, reinterpret_cast<uint4*>(workspace), f.Cin, f.Cout);
   if (int rc = check_launch("pack_dgrad_weights_kernel")) return rc;
-  if (a.gx.ptr) CPOLY_CUDA_OK(cudaMemsetAsync(a.gx.ptr, 0, (size_t)f.B * f.H * f.W * f.Cin * sizeof(float), stream));
   DgradParams p;
   p.g.x = f.x.ptr; p.g.offset = f.offset; p.g.mask = f.mask; p.g.offset_bias = f.offset_bias; p.g.mask_bias = f.mask_bias;
   p.g.B = f.B; p.g.Cin = f.Cin; p.g.Cout = f.Cout; p.g.H = f.H; p.g.W = f.W;
   p.g.om_dtype = f.om_dtype; p.g.mask_is_logit = f.mask_is_logit;
   p.g.tiles_x = (f.W + TILE_W - 1) / TILE_W; p.g.tiles_y = (f.H + TILE_H - 1) / TILE_H;
   p.g.num_tiles = f.B * p.g.tiles_x * p.g.tiles_y;
-  p.gout = a.gout.ptr; p.wpacked = workspace; p.gx = reinterpret_cast<float*>(a.gx.ptr);
+  p.gout = a.gout.ptr; p.wpacked = workspace; p.gcol = a.gx.ptr ? c2i_ws : nullptr;
   p.goffset = a.goffset; p.gmask = a.gmask;
   p.nchunk = d.nchunk; p.split = d.split; p.taps_per_item = NUM_TAPS / d.split; p.num_items = p.g.num_tiles * d.split;
   p.k_atoms = d.k_atoms; p.a_bufs = d.a_bufs; p.w_stage_bytes = d.w_stage_bytes;
@@ -790,7 +788,10 @@ int dcn_dgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_
     CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_dgrad_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, d.smem_bytes));
     dcn_dgrad_tc_kernel<float><<<grid, NTHREADS, d.smem_bytes, stream>>>(p);
   }
-  return check_launch("dcn_dgrad_tc_kernel");
+  if (int rc = check_launch("dcn_dgrad_tc_kernel")) return rc;
+  // grad_input: gather-form col2im over the stored gcol (no atomics, every element written exactly once)
+  if (a.gx.ptr) return dcn_col2im_launch(a, c2i_ws, workspace_bytes - dgrad_packed_aligned(f), stream);
+  return CPOLY_OK;
 }
 
 }  // namespace cpoly
