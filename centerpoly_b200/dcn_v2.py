@@ -194,8 +194,7 @@ def _backward_impl(x, offset, mask, weight, gout, stride, padding, dilation, dg,
     dev = _lib.require_cuda(x, offset, mask, weight, gout)
     L = _lib.lib()
     w32 = _as_f32_contig(weight)
-    if gout.dtype != x.dtype:
-        gout = gout.to(x.dtype)
+    gout = _grad_like(gout, x)
     with torch.cuda.device(dev):
         gx = torch.empty_like(x, dtype=torch.float32) if needs[0] else None
         goff = torch.empty_like(offset, dtype=torch.float32) if needs[1] else None
@@ -213,6 +212,17 @@ def _backward_impl(x, offset, mask, weight, gout, stride, padding, dilation, dg,
         b.workspace, b.workspace_bytes = ws.data_ptr(), ws.numel()
         _lib.check(L.cpoly_dcn_backward(byref(b), _lib.stream_ptr(dev)), "cpoly_dcn_backward")
     return gx, goff, gmask, gw, gb
+
+
+def _grad_like(gout, x):
+    """grad_output in x's dtype and memory format: the tensor-core backward reads dense NHWC rows, and autograd hands
+    over whatever layout the consumer produced (a caller's ``y.backward(g)`` with an NCHW ``g`` would otherwise drop
+    the whole backward to the generic CUDA-core kernels)."""
+    if gout.dtype != x.dtype:
+        gout = gout.to(x.dtype)
+    if x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last) and not gout.is_contiguous(memory_format=torch.channels_last):
+        gout = gout.contiguous(memory_format=torch.channels_last)
+    return gout
 
 
 def _cast(g, like):
@@ -268,7 +278,7 @@ class _DCNFused(Function):
         dev = x.device
         L = _lib.lib()
         w32 = _as_f32_contig(weight)
-        gout = grad_output if grad_output.dtype == x.dtype else grad_output.to(x.dtype)
+        gout = _grad_like(grad_output, x)
         with torch.cuda.device(dev):
             gx = torch.empty_like(x, dtype=torch.float32) if needs[0] else None
             gw = torch.empty(weight.shape, dtype=torch.float32, device=dev) if needs[2] else None

@@ -90,15 +90,26 @@ class PolydetEngine:
             return torch.autocast("cuda", dtype=torch.bfloat16)
         return contextlib.nullcontext()
 
+    def _heads(self, x):
+        """The network part of a frame: head maps {hm (logits), poly, pseudo_depth, reg}."""
+        if self.optimize and not self._stem_direct:
+            # fp32 frame -> persistent network input in the model dtype: one conversion kernel
+            self._xin[:, :3].copy_(x)
+            x = self._xin
+        # (with our stem kernel the fp32 channels_last frame is read directly and rounded to bf16 on load)
+        return self.net(x)[-1]
+
+    def heads_eager(self, slot_idx=0):
+        """Head maps of the frame resident in a slot, computed eagerly on the engine stream (tests: the G3 gate)."""
+        with torch.cuda.stream(self.stream), torch.no_grad(), self._autocast():
+            out = {k: v.clone() for k, v in self._heads(self.slots[slot_idx]["x"]).items()}
+        self.stream.synchronize()
+        return out
+
     def _step(self, x):
         """One frame: network -> sigmoid -> decode (the body of PolydetDetector.process)."""
         with torch.no_grad(), self._autocast():
-            if self.optimize and not self._stem_direct:
-                # fp32 frame -> persistent network input in the model dtype: one conversion kernel
-                self._xin[:, :3].copy_(x)
-                x = self._xin
-            # (with our stem kernel the fp32 channels_last frame is read directly and rounded to bf16 on load)
-            out = self.net(x)[-1]
+            out = self._heads(x)
             if self.optimize:   # the sigmoid of detectors/polydet.py:28 is fused into the decode kernel
                 return cdecode.polydet_decode_from_logits(out["hm"], out["poly"], out["pseudo_depth"], reg=out.get("reg"),
                                                           K=self.K, rep=self.rep, post_affine=self.post_affine)

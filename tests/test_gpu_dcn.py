@@ -36,7 +36,7 @@ def run_ours(case, path, dtype=torch.float32, channels_last=False, stride=1, pad
         y = cp.dcn_v2_conv(x, off, msk, w, b, stride, pad, dil, dg)
         out = {"y": y.detach().float().cpu().numpy()}
         if backward:
-            y.backward(_cuda(case["gout"], dtype))
+            y.backward(_cuda(case["gout"], dtype, channels_last))
             for name, leaf in (("gx", x), ("goffset", off), ("gmask", msk), ("gw", w), ("gb", b)):
                 out[name] = leaf.grad.detach().float().cpu().numpy()
         torch.cuda.synchronize()

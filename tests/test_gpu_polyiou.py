@@ -110,9 +110,9 @@ def test_bf16_head_and_module_mirror():
     Opt.poly_loss = "l1+iou"
     both = cp.PolyLoss(Opt())(out, torch.as_tensor(mask).cuda(), ind, torch.as_tensor(tgt).cuda())
     assert float(both) > float(loss)
-    Opt.poly_order = True
-    with pytest.raises(NotImplementedError):
-        cp.PolyLoss(Opt())
+    Opt.poly_order = True          # the order arm (losses.py:891-906): forward then returns (loss, loss_order)
+    both2, order = cp.PolyLoss(Opt())(out, torch.as_tensor(mask).cuda(), ind, torch.as_tensor(tgt).cuda())
+    assert float(order) >= 0.0 and torch.isfinite(both2)
 
 
 def test_cpu_tensor_raises():
