@@ -11,8 +11,10 @@
 // by destination pixel with a deterministic counting sort, and each destination pixel is then summed by ONE thread
 // group in a fixed order and written exactly once.  No floating-point atomic, no pre-zeroing, same bits every run.
 //
-//   dcn_bbox_kernel     per source tile: the bounding box of the corner positions of every (tap, 32-pixel row pair)
-//                       ("unit", 36 per tile) and of the whole tile, as int16 x 4 (8 bytes).  Reads only the offsets.
+//   dcn_bbox_kernel     per source tile: one 16-byte record (y0, x0, ly, lx, m) per (pixel, tap) pair, laid out
+//                       [tile][tap][pixel] so that a warp of the col2im reads 32 pairs with one coalesced 512-byte load,
+//                       plus the bounding box of the corner positions of every (tap, 32-pixel row pair) ("unit", 36 per
+//                       tile) and of the whole tile, as int16 x 4 (8 bytes).
 //   dcn_col2im_kernel   per destination tile D:
 //     1. candidate source tiles = tiles of the image whose box meets D; candidate units likewise (ordered block
 //        compactions): with ordinary offsets that is D's own 36 units plus the rim of its neighbours, with far
@@ -46,6 +48,7 @@ struct Col2imParams {
   Geom g;
   const void* gcol;          // [B*H*W][9][Cin] element type T, rows of dead (pixel, tap) pairs are never read
   float* gx;                 // dense NHWC fp32 (B,H,W,Cin)
+  const uint4* pair;         // [num_tiles][9][128] (y0 | x0 << 16, ly, lx, m); dead pair: ly < 0
   const BBox* unit_box;      // [num_tiles][36]
   const BBox* tile_box;      // [num_tiles]
 };
@@ -82,7 +85,8 @@ __device__ __forceinline__ float pair_mask(const Geom& g, int b, int y, int x, i
 }
 
 // ---------------------------------------------------------------------------------------------- boxes
-__global__ void __launch_bounds__(TILE_PX) dcn_bbox_kernel(const Geom g, BBox* __restrict__ unit_box, BBox* __restrict__ tile_box) {
+__global__ void __launch_bounds__(TILE_PX) dcn_bbox_kernel(const Geom g, uint4* __restrict__ pair, BBox* __restrict__ unit_box,
+                                                           BBox* __restrict__ tile_box) {
   __shared__ int tb[4];
   const int tile = blockIdx.x, r = threadIdx.x, warp = r >> 5, lane = r & 31;
   int b, ty0, tx0;
@@ -94,10 +98,14 @@ __global__ void __launch_bounds__(TILE_PX) dcn_bbox_kernel(const Geom g, BBox* _
   for (int k = 0; k < NUM_TAPS; ++k) {
     const PairPos t = pair_pos(g, b, y, x, k);
     int ymin = 32767, ymax = -32768, xmin = 32767, xmax = -32768;
+    uint4 rec = make_uint4(0u, __float_as_uint(-1.f), 0u, 0u);
     if (t.alive) {   // alive => at least one corner row and one corner column inside the image
       ymin = max(t.y0, 0); ymax = min(t.y0 + 1, g.H - 1);
       xmin = max(t.x0, 0); xmax = min(t.x0 + 1, g.W - 1);
+      rec = make_uint4(((uint32_t)t.y0 & 0xffffu) | ((uint32_t)t.x0 << 16), __float_as_uint(t.ly), __float_as_uint(t.lx),
+                       __float_as_uint(pair_mask(g, b, y, x, k)));
     }
+    pair[((size_t)tile * NUM_TAPS + k) * TILE_PX + r] = rec;
 #pragma unroll
     for (int s = 16; s >= 1; s >>= 1) {
       ymin = min(ymin, __shfl_xor_sync(0xffffffffu, ymin, s)); ymax = max(ymax, __shfl_xor_sync(0xffffffffu, ymax, s));
@@ -164,6 +172,7 @@ __global__ void __launch_bounds__(C2I_THREADS, 2) dcn_col2im_kernel(const Col2im
   const int tpi = g.tiles_x * g.tiles_y;
   const BBox* tboxes = p.tile_box + (size_t)b * tpi;
   const BBox* uboxes = p.unit_box + (size_t)b * tpi * UNITS_PER_TILE;
+  const uint4* pairs = p.pair + (size_t)b * tpi * NUM_TAPS * TILE_PX;
   const uint32_t lt_mask = (1u << lane) - 1u;
 
   for (int i = tid; i < C2I_WARPS * TILE_PX; i += C2I_THREADS) (&cnt[0][0])[i] = 0u;
@@ -191,21 +200,34 @@ __global__ void __launch_bounds__(C2I_THREADS, 2) dcn_col2im_kernel(const Col2im
           nunits += block_compact(hit, code, units + nunits, wsum);
         }
         // ---- every warp walks its share of the units; lane = source pixel
+        // (the record of the warp's NEXT unit is requested before the current one is walked: one L2 latency per unit
+        //  would otherwise be exposed, there is nothing else for the warp to do)
+        auto fetch = [&](int ui, uint32_t& code, uint4& rec) {
+          code = units[ui];
+          const int st = (int)(code >> 6), k = (int)((code & 63u) >> 2), chunk = (int)(code & 3u);
+          rec = __ldg(pairs + ((size_t)st * NUM_TAPS + k) * TILE_PX + chunk * 32 + lane);
+        };
+        uint32_t code_n = 0;
+        uint4 rec_n = make_uint4(0u, 0u, 0u, 0u);
+        if (warp < nunits) fetch(warp, code_n, rec_n);
         for (int ui = warp; ui < nunits; ui += C2I_WARPS) {
-          const uint32_t code = units[ui];
+          const uint32_t code = code_n;
+          const uint4 rec = rec_n;
+          if (ui + C2I_WARPS < nunits) fetch(ui + C2I_WARPS, code_n, rec_n);
           const int st = (int)(code >> 6), k = (int)((code & 63u) >> 2), chunk = (int)(code & 3u);
           const int sty = st / g.tiles_x;
           const int r = chunk * 32 + lane;
           const int y = sty * TILE_H + (r >> 4), x = (st - sty * g.tiles_x) * TILE_W + (r & (TILE_W - 1));
-          const PairPos t = pair_pos(g, b, y, x, k);
-          const float m = (pass > 0 && t.alive) ? pair_mask(g, b, y, x, k) : 0.f;
-          const uint32_t src = (uint32_t)(((b * g.H + y) * g.W + x) * NUM_TAPS + k);
+          const float ly = __uint_as_float(rec.y), lx = __uint_as_float(rec.z), m = __uint_as_float(rec.w);
+          const bool alive = ly >= 0.f;
+          const int y0 = (int)(short)(rec.x & 0xffffu), x0 = (int)(short)(rec.x >> 16);
+          const uint32_t src = (uint32_t)((b * g.H + y) * g.W + x) * NUM_TAPS + (uint32_t)k;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const int cy = t.y0 + (j >> 1), cx = t.x0 + (j & 1);
-            const float wy = (j >> 1) ? t.ly : 1.0f - t.ly, wx = (j & 1) ? t.lx : 1.0f - t.lx;
+            const int cy = y0 + (j >> 1), cx = x0 + (j & 1);
+            const float wy = (j >> 1) ? ly : 1.0f - ly, wx = (j & 1) ? lx : 1.0f - lx;
             const float w = wy * wx;
-            const bool ok = t.alive && w != 0.f && cy >= ty0 && cy < ty0 + TILE_H && cx >= tx0 && cx < tx0 + TILE_W && cy < g.H && cx < g.W;
+            const bool ok = alive && w != 0.f && cy >= ty0 && cy < ty0 + TILE_H && cx >= tx0 && cx < tx0 + TILE_W && cy < g.H && cx < g.W;
             const uint32_t active = __ballot_sync(0xffffffffu, ok);
             if (active == 0u) continue;
             if (ok) {
@@ -365,11 +387,13 @@ size_t dcn_col2im_gcol_bytes(const cpoly_dcn_fwd_args& f) {
   return ((size_t)f.B * f.H * f.W * NUM_TAPS * f.Cin * (f.dtype == CPOLY_BF16 ? 2 : 4) + 255) / 256 * 256;
 }
 
+static size_t pair_bytes(const cpoly_dcn_fwd_args& f) { return (size_t)tiles_of(f) * NUM_TAPS * TILE_PX * sizeof(uint4); }
+
 size_t dcn_col2im_workspace(const cpoly_dcn_bwd_args& a) {
-  return dcn_col2im_gcol_bytes(a.f) + (size_t)tiles_of(a.f) * (UNITS_PER_TILE + 1) * sizeof(BBox) + 256;
+  return dcn_col2im_gcol_bytes(a.f) + pair_bytes(a.f) + (size_t)tiles_of(a.f) * (UNITS_PER_TILE + 1) * sizeof(BBox) + 256;
 }
 
-// gcol lives at the START of `workspace` (dcn_col2im_gcol_bytes), the boxes behind it.
+// gcol lives at the START of `workspace` (dcn_col2im_gcol_bytes), the pair records and the boxes behind it.
 int dcn_col2im_launch(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
   const cpoly_dcn_fwd_args& f = a.f;
   CPOLY_REQUIRE(workspace && workspace_bytes >= dcn_col2im_workspace(a) - 256 && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0,
@@ -383,11 +407,13 @@ int dcn_col2im_launch(const cpoly_dcn_bwd_args& a, void* workspace, size_t works
   if (p.g.num_tiles == 0) return CPOLY_OK;
   uint8_t* ws = reinterpret_cast<uint8_t*>(workspace);
   p.gcol = ws;
-  BBox* ub = reinterpret_cast<BBox*>(ws + dcn_col2im_gcol_bytes(f));
+  uint4* pr = reinterpret_cast<uint4*>(ws + dcn_col2im_gcol_bytes(f));
+  p.pair = pr;
+  BBox* ub = reinterpret_cast<BBox*>(ws + dcn_col2im_gcol_bytes(f) + pair_bytes(f));
   BBox* tb = ub + (size_t)p.g.num_tiles * UNITS_PER_TILE;
   p.unit_box = ub; p.tile_box = tb;
   p.gx = reinterpret_cast<float*>(a.gx.ptr);
-  dcn_bbox_kernel<<<p.g.num_tiles, TILE_PX, 0, stream>>>(p.g, ub, tb);
+  dcn_bbox_kernel<<<p.g.num_tiles, TILE_PX, 0, stream>>>(p.g, pr, ub, tb);
   if (int rc = check_launch("dcn_bbox_kernel")) return rc;
   constexpr int dyn = CAP * (int)sizeof(uint2);
   if (f.dtype == CPOLY_BF16) {

@@ -118,7 +118,7 @@ __global__ void __maxnreg__(80) dcn_wgrad_tc_kernel(const WgradParams p) {
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
         if (y < p.g.H && x < p.g.W)
           v = ldg16(gb + ((size_t)((b * p.g.H + y) * p.g.W + x) * row_pieces + j) * 16);
-        sts16(abuf + (uint32_t)(j >> 3) * ATOM_BYTES + (uint32_t)r * ROW_BYTES + (uint32_t)(((j & 7) ^ (r & 7)) << 4), v);
+        sts16(abuf + (uint32_t)(j >> 3) * ATOM_BYTES + (uint32_t)r * ROW_BYTES + (mn_major_piece<kTF32>(j & 7, r) << 4), v);
       }
       fence_proxy_async_smem();
       __syncwarp();
@@ -146,7 +146,7 @@ __global__ void __maxnreg__(80) dcn_wgrad_tc_kernel(const WgradParams p) {
 #pragma unroll
         for (int pass = 0; pass < PASSES; ++pass) {
           const int r = pass * ROWS_PER_PASS + row_in_pass;
-          sts16(bst + r * ROW_BYTES + ((cg ^ (r & 7)) << 4), Blend<T>::run(c[pass], pw[pass]));
+          sts16(bst + r * ROW_BYTES + (mn_major_piece<kTF32>(cg, r) << 4), Blend<T>::run(c[pass], pw[pass]));
           if (blk + 1 < blk1) issue(blk + 1, pass);
         }
         fence_proxy_async_smem();
@@ -172,8 +172,11 @@ __global__ void __maxnreg__(80) dcn_wgrad_tc_kernel(const WgradParams p) {
           if (elect_one()) {
             for (int mhalf = 0; mhalf < p.mh; ++mhalf) {
               const uint32_t d_tmem = tmem_base + (uint32_t)(((blk - blk0) * p.mh + mhalf) * kChunk);
-              const uint64_t adesc0 = umma_desc_sw128(abuf + (uint32_t)(mhalf * atoms_per_half) * ATOM_BYTES, ATOM_BYTES, 1024);
-              const uint64_t bdesc0 = umma_desc_sw128(bst, ATOM_BYTES, 1024);
+              // MN-major operands: 16-bit elements use SWIZZLE_128B (8-row atoms); 32-bit elements (tf32) need
+              // SWIZZLE_128B_BASE32B (4-row atoms, 512 B apart) - see umma_desc_sw128
+              constexpr uint32_t kSbo = kTF32 ? 512u : 1024u, kLayout = kTF32 ? 1u : 2u;
+              const uint64_t adesc0 = umma_desc_sw128(abuf + (uint32_t)(mhalf * atoms_per_half) * ATOM_BYTES, ATOM_BYTES, kSbo, kLayout);
+              const uint64_t bdesc0 = umma_desc_sw128(bst, ATOM_BYTES, kSbo, kLayout);
 #pragma unroll
               for (int kk = 0; kk < TILE_PX / kInstrK; ++kk) {   // the start address advances by whole 128-byte rows
                 const uint64_t step = (uint64_t)((kk * kInstrK * ROW_BYTES) >> 4);

@@ -84,14 +84,23 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 //   K-major operand  (rows = M/N index, 128 B of K per row): SBO = 1024 B between 8-row groups, LBO unused.
 //   MN-major operand (rows = K index, 128 B of M/N per row): LBO = bytes between 64-element (bf16) /
 //   32-element (tf32) blocks along M/N, SBO = 1024 B between 8-row K groups.
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes = 16, uint32_t sbo_bytes = 1024) {
+//   `layout_type`: 2 = SWIZZLE_128B (16-byte pieces XOR-ed with row & 7), 1 = SWIZZLE_128B_BASE32B (32-byte pieces
+//   XOR-ed with row & 3, swizzle atom = 4 rows): the layout the tensor core requires for MN-major operands of 32-bit
+//   elements (kind::tf32) - with type 2 such an MMA silently accumulates nothing.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes = 16, uint32_t sbo_bytes = 1024,
+                                                    uint32_t layout_type = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3ffffu) >> 4);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32;
   d |= (uint64_t)1 << 46;  // descriptor version
-  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  d |= (uint64_t)layout_type << 61;
   return d;
+}
+// Position of 16-byte piece j of row r inside a 128-byte row of an MN-major operand tile.
+template <bool kTF32>
+__device__ __forceinline__ uint32_t mn_major_piece(int j, int r) {
+  return kTF32 ? (uint32_t)((((j >> 1) ^ (r & 3)) << 1) | (j & 1)) : (uint32_t)(j ^ (r & 7));
 }
 
 // Instruction descriptor for kind::f16 (bf16 x bf16 -> f32) or kind::tf32 (tf32 x tf32 -> f32).

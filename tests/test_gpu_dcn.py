@@ -149,6 +149,19 @@ def test_full_size_vs_torchvision_golden(path):
     rounding = torch.bfloat16 if str(g["rounding"]) == "bfloat16" else torch.float32
     case = make_dcn_case(int(g["seed"]), B, Cin, Cout, H, W, dtype=rounding)
     flat = torch.from_numpy(g["positions"])
+    # A sample coordinate that fp32 arithmetic rounds onto an integer (y - 1 + i + dy == 266.0f exactly, 265.99999976 in
+    # float64) sits on a kink of the piecewise-bilinear function: the kernels (fp32 positions, like upstream) and the
+    # float64 stand-in then take the derivative from different sides.  Those grad_offset entries (about one in 10^6)
+    # are exempt; everything else is gated.
+    off_s = _take(case["offset"], flat).double()
+    yy, xx = ((flat % (H * W)) // W).double(), (flat % W).double()
+    kink = torch.zeros_like(off_s, dtype=torch.bool)
+    for k in range(9):
+        py, px = yy - 1 + k // 3 + off_s[:, 2 * k], xx - 1 + k % 3 + off_s[:, 2 * k + 1]
+        near = ((py - py.round()).abs() < 1e-4) | ((px - px.round()).abs() < 1e-4)
+        kink[:, 2 * k] = near
+        kink[:, 2 * k + 1] = near
+    kink = kink.numpy()
     modes = [torch.float32] if rounding == torch.float32 else [torch.bfloat16, torch.float32]
     ref_full = None
     for dtype in modes:
@@ -157,6 +170,8 @@ def test_full_size_vs_torchvision_golden(path):
         for name in ("y", "gx", "goffset", "gmask"):
             want = g[name].astype(np.float64)
             have = _take(torch.from_numpy(got[name]), flat).numpy().astype(np.float64)
+            if name == "goffset":
+                have = np.where(kink, want, have)
             err_max = np.abs(have - want).max() / float(g[name + "_max"])
             err_l2 = np.linalg.norm(have - want) / np.linalg.norm(want)
             assert err_max <= tol and err_l2 <= tol, f"{name} [{dtype}]: max-rel {err_max:.3e}, l2-rel {err_l2:.3e} > {tol}"
