@@ -25,6 +25,7 @@ EXPORTED_SYMBOLS = (
     "cpoly_dcn_backward_workspace_bytes", "cpoly_dcn_backward", "cpoly_decode_workspace_bytes", "cpoly_decode",
     "cpoly_rasterise_workspace_bytes", "cpoly_rasterise", "cpoly_poly_iou_forward", "cpoly_poly_iou_backward",
     "cpoly_stem_pack_weights", "cpoly_stem_conv7x7_forward", "cpoly_maxpool2x2_nhwc_forward",
+    "cpoly_offset_conv_packed_bytes", "cpoly_offset_conv_pack_weights", "cpoly_offset_conv_forward",
 )
 
 
@@ -83,6 +84,11 @@ class MaxPoolArgs(Structure):
     _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "dtype", "reserved0")] + [("x", c_void_p), ("y", c_void_p)]
 
 
+class OffsetConvArgs(Structure):
+    _fields_ = [(n, c_int32) for n in ("B", "Cin", "H", "W", "om_dtype", "reserved0")] + [
+        ("x", c_void_p), ("weight_packed", c_void_p), ("bias", c_void_p), ("om", c_void_p)]
+
+
 class UpsampleBwdArgs(Structure):
     _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "f", "dtype")] + [
         ("x", Tensor4), ("gy", Tensor4), ("weight", c_void_p), ("gx", Tensor4), ("gweight", c_void_p)]
@@ -90,7 +96,7 @@ class UpsampleBwdArgs(Structure):
 
 _lib = None
 # kernels launched by the shims since import (our kernels only; bench.py reports it as gpu_launches)
-LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "upsample_bwd": 0, "decode": 0, "rasterise": 0, "poly_iou": 0, "stem": 0, "maxpool": 0}
+LAUNCHES = {"dcn_forward": 0, "dcn_backward": 0, "pack_weights": 0, "upsample": 0, "upsample_bwd": 0, "decode": 0, "rasterise": 0, "poly_iou": 0, "stem": 0, "maxpool": 0, "offset_conv": 0}
 
 
 def lib():
@@ -141,7 +147,13 @@ def lib():
         L.cpoly_maxpool2x2_nhwc_forward.argtypes = [POINTER(MaxPoolArgs), c_void_p]
         L.cpoly_idaup_upsample_backward.restype = c_int32
         L.cpoly_idaup_upsample_backward.argtypes = [POINTER(UpsampleBwdArgs), c_void_p]
-        if L.cpoly_abi_version() != 7:
+        L.cpoly_offset_conv_packed_bytes.restype = c_size_t
+        L.cpoly_offset_conv_packed_bytes.argtypes = [c_int32]
+        L.cpoly_offset_conv_pack_weights.restype = c_int32
+        L.cpoly_offset_conv_pack_weights.argtypes = [c_void_p, c_void_p, c_int32, c_int32, c_void_p]
+        L.cpoly_offset_conv_forward.restype = c_int32
+        L.cpoly_offset_conv_forward.argtypes = [POINTER(OffsetConvArgs), c_void_p]
+        if L.cpoly_abi_version() != 8:
             raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
         _lib = L
     return _lib

@@ -249,4 +249,25 @@ int cpoly_idaup_upsample_backward(const cpoly_upsample_bwd_args* a, cpoly_stream
   return idaup_upsample_backward_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+size_t cpoly_offset_conv_packed_bytes(int32_t Cin) { return Cin > 0 ? offset_conv_packed_bytes(Cin) : 0; }
+
+int cpoly_offset_conv_pack_weights(const float* weight, void* packed, int32_t Cin, int32_t n_out, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(weight && packed, CPOLY_EINVAL, "NULL pointer");
+  CPOLY_REQUIRE(offset_conv_packed_bytes(Cin) > 0 && n_out >= 1 && n_out <= 32, CPOLY_EUNSUPPORTED,
+                "offset conv: Cin (%d) must be a multiple of 64 and n_out (%d) <= 32", Cin, n_out);
+  return offset_conv_pack_launch(weight, packed, Cin, n_out, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int cpoly_offset_conv_forward(const cpoly_offset_conv_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->H > 0 && a->W > 0 && offset_conv_packed_bytes(a->Cin) > 0, CPOLY_EUNSUPPORTED, "offset conv: bad dims / Cin %% 64 != 0");
+  CPOLY_REQUIRE(a->om_dtype == CPOLY_F32 || a->om_dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported om dtype %d", a->om_dtype);
+  CPOLY_REQUIRE(a->x && a->weight_packed && a->bias && a->om, CPOLY_EINVAL, "NULL pointer");
+  CPOLY_REQUIRE(((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(a->om) | reinterpret_cast<uintptr_t>(a->weight_packed)) & 15) == 0,
+                CPOLY_EINVAL, "x / om / weight_packed must be 16-byte aligned");
+  CPOLY_REQUIRE((int64_t)a->B * a->H * a->W < (1LL << 31), CPOLY_EINVAL, "too many pixels");
+  if (a->B == 0) return CPOLY_OK;
+  return offset_conv_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

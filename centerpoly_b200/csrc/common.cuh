@@ -145,4 +145,7 @@ int poly_iou_backward_launch(const cpoly_poly_iou_args& a, cudaStream_t stream);
 int stem_pack_weights_launch(const void* w, int w_dtype, void* out, cudaStream_t stream);
 int stem_conv_launch(const cpoly_stem_args& a, cudaStream_t stream);
 int maxpool2x2_launch(const cpoly_maxpool_args& a, cudaStream_t stream);
+size_t offset_conv_packed_bytes(int Cin);
+int offset_conv_pack_launch(const float* weight, void* packed, int Cin, int n_out, cudaStream_t stream);
+int offset_conv_launch(const cpoly_offset_conv_args& a, cudaStream_t stream);
 }  // namespace cpoly

@@ -156,8 +156,9 @@ template <typename T>
 __global__ void __launch_bounds__(C2I_THREADS, 2) dcn_col2im_kernel(const Col2imParams p) {
   constexpr int kVec = 16 / (int)sizeof(T);          // channels per 16-byte piece: 8 bf16 / 4 fp32
   constexpr int kChunk = ROW_BYTES / (int)sizeof(T); // channels per 128-byte chunk
-  __shared__ uint32_t cnt[C2I_WARPS][TILE_PX];       // pass 1: corners per (warp, destination pixel)
-  __shared__ uint32_t run[C2I_WARPS][TILE_PX];       // pass 2: next sorted slot of (warp, destination pixel)
+  constexpr int NSEG = C2I_WARPS * 4;                // (warp, corner) segments inside a destination pixel's slot range
+  // pass 0: corners per (warp, corner index, destination pixel); then, in place, the next sorted slot of that triple
+  __shared__ uint32_t slot[C2I_WARPS][4][TILE_PX];
   __shared__ uint32_t start[TILE_PX + 1];
   __shared__ uint32_t cand[C2I_THREADS];
   __shared__ uint32_t units[UNIT_CAP];
@@ -174,13 +175,18 @@ __global__ void __launch_bounds__(C2I_THREADS, 2) dcn_col2im_kernel(const Col2im
   const BBox* uboxes = p.unit_box + (size_t)b * tpi * UNITS_PER_TILE;
   const uint4* pairs = p.pair + (size_t)b * tpi * NUM_TAPS * TILE_PX;
   const uint32_t lt_mask = (1u << lane) - 1u;
-
-  for (int i = tid; i < C2I_WARPS * TILE_PX; i += C2I_THREADS) (&cnt[0][0])[i] = 0u;
-  __syncthreads();
+  const int hmax = min(TILE_H, g.H - ty0), wmax = min(TILE_W, g.W - tx0);    // the part of D inside the image
+  const uint32_t img_row0 = (uint32_t)(b * g.H) * (uint32_t)g.W;
 
   uint32_t total = 0, win_lo = 0;
-  // pass 0 counts; pass 1, 2, ... place the sorted slots [win_lo, win_lo + CAP) and accumulate them
+  // pass 0 counts; pass 1 places the sorted slots [0, CAP) and accumulates them.  A destination tile with more than CAP
+  // corners repeats (count, place window w, accumulate) for w = 1, 2, ...: rare (offset fields collapsing onto a spot).
   for (int pass = 0;; ++pass) {
+    const bool counting = (pass & 1) == 0;   // even passes count, odd passes place one window and accumulate it
+    if (counting) {
+      for (int i = tid; i < NSEG * TILE_PX; i += C2I_THREADS) (&slot[0][0][0])[i] = 0u;
+      __syncthreads();
+    }
     for (int tbase = 0; tbase < tpi; tbase += C2I_THREADS) {
       const int tc_ = tbase + tid;
       const int ncand = block_compact(tc_ < tpi && box_meets(tboxes[tc_ < tpi ? tc_ : 0], ty0, tx0), (uint32_t)tc_, cand, wsum);
@@ -195,7 +201,8 @@ __global__ void __launch_bounds__(C2I_THREADS, 2) dcn_col2im_kernel(const Col2im
           if (i < nu) {
             const uint32_t t = cand[cb + i / UNITS_PER_TILE], kc = (uint32_t)(i % UNITS_PER_TILE);
             hit = box_meets(uboxes[(size_t)t * UNITS_PER_TILE + kc], ty0, tx0);
-            code = (t << 6) | kc;
+            const uint32_t sty = t / (uint32_t)g.tiles_x, stx = t - sty * (uint32_t)g.tiles_x;   // one division per unit, here
+            code = (sty << 20) | (stx << 6) | kc;      // 12 + 14 + 6 bits (H, W <= 32767)
           }
           nunits += block_compact(hit, code, units + nunits, wsum);
         }
@@ -204,8 +211,8 @@ __global__ void __launch_bounds__(C2I_THREADS, 2) dcn_col2im_kernel(const Col2im
         //  would otherwise be exposed, there is nothing else for the warp to do)
         auto fetch = [&](int ui, uint32_t& code, uint4& rec) {
           code = units[ui];
-          const int st = (int)(code >> 6), k = (int)((code & 63u) >> 2), chunk = (int)(code & 3u);
-          rec = __ldg(pairs + ((size_t)st * NUM_TAPS + k) * TILE_PX + chunk * 32 + lane);
+          const uint32_t st = (code >> 20) * (uint32_t)g.tiles_x + ((code >> 6) & 0x3fffu);
+          rec = __ldg(pairs + ((size_t)st * NUM_TAPS + ((code & 63u) >> 2)) * TILE_PX + (code & 3u) * 32 + lane);
         };
         uint32_t code_n = 0;
         uint4 rec_n = make_uint4(0u, 0u, 0u, 0u);
@@ -214,48 +221,53 @@ __global__ void __launch_bounds__(C2I_THREADS, 2) dcn_col2im_kernel(const Col2im
           const uint32_t code = code_n;
           const uint4 rec = rec_n;
           if (ui + C2I_WARPS < nunits) fetch(ui + C2I_WARPS, code_n, rec_n);
-          const int st = (int)(code >> 6), k = (int)((code & 63u) >> 2), chunk = (int)(code & 3u);
-          const int sty = st / g.tiles_x;
-          const int r = chunk * 32 + lane;
-          const int y = sty * TILE_H + (r >> 4), x = (st - sty * g.tiles_x) * TILE_W + (r & (TILE_W - 1));
-          const float ly = __uint_as_float(rec.y), lx = __uint_as_float(rec.z), m = __uint_as_float(rec.w);
-          const bool alive = ly >= 0.f;
-          const int y0 = (int)(short)(rec.x & 0xffffu), x0 = (int)(short)(rec.x >> 16);
-          const uint32_t src = (uint32_t)((b * g.H + y) * g.W + x) * NUM_TAPS + (uint32_t)k;
+          const float ly = __uint_as_float(rec.y), lx = __uint_as_float(rec.z);
+          // top-left corner relative to D; the four corners are (ry, rx) + {0,1}^2
+          const int ry = (int)(short)(rec.x & 0xffffu) - ty0, rx = (int)(short)(rec.x >> 16) - tx0;
+          const bool near = ly >= 0.f && ry >= -1 && ry < hmax && rx >= -1 && rx < wmax;   // alive and some corner may be in D
+          const uint32_t act = __ballot_sync(0xffffffffu, near);
+          if (act == 0u) continue;
+          // lanes with the same top-left corner share all four destinations: ONE match per unit
+          uint32_t same = 0u;
+          if (near) same = __match_any_sync(act, (ry + 1) * 32 + (rx + 1));
+          const float m = __uint_as_float(rec.w);
+          const uint32_t k = (code & 63u) >> 2, r = (code & 3u) * 32 + (uint32_t)lane;
+          const uint32_t sy = (code >> 20) * TILE_H + (r >> 4), sx = ((code >> 6) & 0x3fffu) * TILE_W + (r & (TILE_W - 1));
+          const uint32_t src = (img_row0 + sy * (uint32_t)g.W + sx) * NUM_TAPS + k;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const int cy = y0 + (j >> 1), cx = x0 + (j & 1);
-            const float wy = (j >> 1) ? ly : 1.0f - ly, wx = (j & 1) ? lx : 1.0f - lx;
-            const float w = wy * wx;
-            const bool ok = alive && w != 0.f && cy >= ty0 && cy < ty0 + TILE_H && cx >= tx0 && cx < tx0 + TILE_W && cy < g.H && cx < g.W;
-            const uint32_t active = __ballot_sync(0xffffffffu, ok);
-            if (active == 0u) continue;
+            const int cy = ry + (j >> 1), cx = rx + (j & 1);
+            const float w = ((j >> 1) ? ly : 1.0f - ly) * ((j & 1) ? lx : 1.0f - lx);
+            const bool ok = near && (unsigned)cy < (unsigned)hmax && (unsigned)cx < (unsigned)wmax && w != 0.f;
+            const uint32_t okb = __ballot_sync(0xffffffffu, ok);
+            if (okb == 0u) continue;
             if (ok) {
-              const int q = (cy - ty0) * TILE_W + (cx - tx0);
-              const uint32_t same = __match_any_sync(active, q);
-              const uint32_t rank = (uint32_t)__popc(same & lt_mask);
-              if (pass == 0) {
-                if (rank == 0) cnt[warp][q] += (uint32_t)__popc(same);
+              // same destination pixel <=> same top-left corner (for a fixed corner index j)
+              const uint32_t grp = same & okb;
+              const uint32_t rank = (uint32_t)__popc(grp & lt_mask);
+              uint32_t* sl = &slot[warp][j][cy * TILE_W + cx];
+              if (counting) {
+                if (rank == 0) *sl += (uint32_t)__popc(grp);
               } else {
-                const uint32_t pos = run[warp][q] + rank;
+                const uint32_t pos = *sl + rank;
                 if (pos >= win_lo && pos < win_lo + CAP) contrib[pos - win_lo] = make_uint2(src, __float_as_uint(m * w));
-                __syncwarp(same);
-                if (rank == 0) run[warp][q] += (uint32_t)__popc(same);
+                __syncwarp(grp);
+                if (rank == 0) *sl += (uint32_t)__popc(grp);
               }
             }
-            __syncwarp();
           }
+          __syncwarp();   // the slot cursors written by this unit's group leaders are read by the warp's next unit
         }
         __syncthreads();   // units[] / cand[] are rewritten by the next batch
       }
     }
     __syncthreads();
-    if (pass == 0) {
-      // ---- slot ranges: start[q] = corners landing on pixels < q; warps in index order inside a pixel's range
+    if (counting) {
+      // ---- slot ranges: start[q] = corners landing on pixels < q; inside a pixel's range (warp, corner index) order
       if (tid < TILE_PX) {
         uint32_t s = 0;
 #pragma unroll
-        for (int w = 0; w < C2I_WARPS; ++w) s += cnt[w][tid];
+        for (int w = 0; w < NSEG; ++w) s += (&slot[0][0][0])[w * TILE_PX + tid];
         start[tid + 1] = s;
       }
       __syncthreads();
@@ -276,6 +288,18 @@ __global__ void __launch_bounds__(C2I_THREADS, 2) dcn_col2im_kernel(const Col2im
       }
       __syncthreads();
       total = start[TILE_PX];
+      // counts -> first slot of every (warp, corner, pixel) segment, in place
+      if (tid < TILE_PX) {
+        uint32_t s = start[tid];
+#pragma unroll
+        for (int w = 0; w < NSEG; ++w) {
+          uint32_t* c = &(&slot[0][0][0])[w * TILE_PX + tid];
+          const uint32_t n = *c;
+          *c = s;
+          s += n;
+        }
+      }
+      __syncthreads();
     } else {
       // ---- accumulate the resident window: 8 lanes per destination pixel, 16 bytes of a gcol row per lane
       const int grp = tid >> 3, l8 = tid & 7;
@@ -350,13 +374,6 @@ __global__ void __launch_bounds__(C2I_THREADS, 2) dcn_col2im_kernel(const Col2im
       }
       win_lo += CAP;
       if (win_lo >= total) break;
-    }
-    // ---- (re)arm the running slot cursors for the next placement pass
-    __syncthreads();
-    if (tid < TILE_PX) {
-      uint32_t s = start[tid];
-#pragma unroll
-      for (int w = 0; w < C2I_WARPS; ++w) { run[w][tid] = s; s += cnt[w][tid]; }
     }
     __syncthreads();
   }

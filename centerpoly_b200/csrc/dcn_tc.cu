@@ -71,6 +71,7 @@ struct TcParams {
   int nchunk;      // channel chunks per tap
   int stages, b_stage_bytes, stage_bytes;
   int acc_cols, tmem_cols;
+  int om_esize;    // element size of the fused 32-channel offset/mask tensor (kOmFast kernels)
 };
 
 // ---- blend of the four corner vectors (16 B each) into one 16-B piece of the A row ----------------
@@ -134,7 +135,12 @@ __device__ __forceinline__ void item_coords(const TcParams& p, int item, int& b,
 }
 
 // ---------------------------------------------------------------------------------------- kernel
-template <typename T>
+// kOmFast: offsets and mask logits are channels 0..17 / 18..26 of ONE dense 32-channel NHWC tensor (what
+// cpoly_offset_conv_forward and the padded cuDNN producer write).  The item's 128 x 32 values are then fetched with
+// coalesced 16-byte loads one item ahead (8 registers), transposed through shared memory (odd word pitch: conflict-free)
+// and the parameters computed from there - instead of three strided 2/4-byte loads per (pixel, tap), which cost ~180 of
+// the ~1500 LSU wavefronts of every (tile, tap) step (ncu, profiles/r01m_dcn_fwd_tc_64x64_raw.txt).
+template <typename T, bool kOmFast>
 __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   constexpr bool kTF32 = sizeof(T) == 4;
   extern __shared__ uint8_t smem_raw[];
@@ -184,25 +190,85 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
     const int row_in_pass = st >> 3, cg = st & 7;
     const int n_param = p.taps_per_item * TILE_PX;
     float raw_dy[MAX_ITEMS], raw_dx[MAX_ITEMS], raw_m[MAX_ITEMS];
+    uint4 omv[2];   // kOmFast: this thread's 16-byte pieces of the NEXT item's offset/mask tile
     // raw offsets / mask of one item -> registers (issued one item ahead so the latency hides behind sampling)
     auto fetch_raw = [&](int item) {
       int b, ty0, tx0, tap0;
       item_coords(p, item, b, ty0, tx0, tap0);
+      if constexpr (kOmFast) {
+        const int ppp = p.om_esize * 2;                  // 16-byte pieces per pixel: 32 channels * esize / 16
+        const uint8_t* base = reinterpret_cast<const uint8_t*>(p.offset.ptr);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int idx = st + i * NS;
+          const int r = idx / ppp, j = idx - r * ppp;
+          const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
+          omv[i] = make_uint4(0u, 0u, 0u, 0u);
+          if (r < TILE_PX && y < p.H && x < p.W)
+            omv[i] = ldg16(base + ((size_t)((b * p.H + y) * p.W + x) * 32) * p.om_esize + j * 16);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < MAX_ITEMS; ++i) {
+          const int e = st + i * NS;
+          const int k = tap0 + (e >> 7), r = e & (TILE_PX - 1);
+          const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
+          raw_dy[i] = raw_dx[i] = raw_m[i] = 0.f;
+          if (e < n_param && y < p.H && x < p.W) {
+            const int64_t opix = (int64_t)b * p.offset.sb + (int64_t)y * p.offset.sh + (int64_t)x * p.offset.sw;
+            raw_dy[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k) * p.offset.sc, p.om_dtype);
+            raw_dx[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k + 1) * p.offset.sc, p.om_dtype);
+            raw_m[i] = ld_dyn(p.mask.ptr, (int64_t)b * p.mask.sb + (int64_t)k * p.mask.sc + (int64_t)y * p.mask.sh + (int64_t)x * p.mask.sw, p.om_dtype);
+            if (p.offset_bias) { raw_dy[i] += __ldg(p.offset_bias + 2 * k); raw_dx[i] += __ldg(p.offset_bias + 2 * k + 1); }
+            if (p.mask_bias) raw_m[i] += __ldg(p.mask_bias + k);
+          }
+        }
+      }
+    };
+    // kOmFast: registers -> shared tile [pixel][32 channels] with an odd word pitch (33 words fp32 / 17 words bf16), then
+    // every thread picks the (dy, dx, mask) of its own (pixel, tap) entries.  The tile aliases the weight-parameter
+    // array, which is dead between the first barrier of an item and the parameter stores.
+    auto stage_raw = [&](int tap0) {
+      const int ppp = p.om_esize * 2;
+      const uint32_t pitch = p.om_esize == 4 ? 132u : 68u;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int idx = st + i * NS;
+        const int r = idx / ppp, j = idx - r * ppp;
+        if (r < TILE_PX) {
+          const uint32_t a = pw_s + (uint32_t)r * pitch + (uint32_t)j * 16u;
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(omv[i].x) : "memory");
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(a + 4u), "r"(omv[i].y) : "memory");
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(a + 8u), "r"(omv[i].z) : "memory");
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(a + 12u), "r"(omv[i].w) : "memory");
+        }
+      }
+      named_bar_sync(1, NS);
 #pragma unroll
       for (int i = 0; i < MAX_ITEMS; ++i) {
         const int e = st + i * NS;
-        const int k = tap0 + (e >> 7), r = e & (TILE_PX - 1);
-        const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
         raw_dy[i] = raw_dx[i] = raw_m[i] = 0.f;
-        if (e < n_param && y < p.H && x < p.W) {
-          const int64_t opix = (int64_t)b * p.offset.sb + (int64_t)y * p.offset.sh + (int64_t)x * p.offset.sw;
-          raw_dy[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k) * p.offset.sc, p.om_dtype);
-          raw_dx[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k + 1) * p.offset.sc, p.om_dtype);
-          raw_m[i] = ld_dyn(p.mask.ptr, (int64_t)b * p.mask.sb + (int64_t)k * p.mask.sc + (int64_t)y * p.mask.sh + (int64_t)x * p.mask.sw, p.om_dtype);
+        if (e < n_param) {
+          const int k = tap0 + (e >> 7), r = e & (TILE_PX - 1);
+          const uint32_t a = pw_s + (uint32_t)r * pitch;
+          uint32_t u0, u1;
+          if (p.om_esize == 4) {
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u0) : "r"(a + (uint32_t)(8 * k)));
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u1) : "r"(a + (uint32_t)(8 * k + 4)));
+            raw_dy[i] = __uint_as_float(u0); raw_dx[i] = __uint_as_float(u1);
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u0) : "r"(a + (uint32_t)(72 + 4 * k)));
+            raw_m[i] = __uint_as_float(u0);
+          } else {
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u0) : "r"(a + (uint32_t)(4 * k)));          // (dy, dx) bf16 pair
+            raw_dy[i] = __uint_as_float(u0 << 16); raw_dx[i] = __uint_as_float(u0 & 0xffff0000u);
+            asm volatile("ld.shared.u16 %0, [%1];" : "=r"(u1) : "r"(a + (uint32_t)(36 + 2 * k)));
+            raw_m[i] = __uint_as_float(u1 << 16);
+          }
           if (p.offset_bias) { raw_dy[i] += __ldg(p.offset_bias + 2 * k); raw_dx[i] += __ldg(p.offset_bias + 2 * k + 1); }
           if (p.mask_bias) raw_m[i] += __ldg(p.mask_bias + k);
         }
       }
+      named_bar_sync(1, NS);   // the tile is dead: its bytes become weight parameters again
     };
     RingCursor rc;
     if ((int)blockIdx.x < p.num_items) fetch_raw(blockIdx.x);
@@ -211,6 +277,7 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       item_coords(p, item, b, ty0, tx0, tap0);
       const int img_base = b * p.H * p.W * p.Cin;   // element offset; bytes < 2^32 (checked on the host)
       named_bar_sync(1, NS);  // everyone finished reading the previous item's params
+      if constexpr (kOmFast) stage_raw(tap0);
 #pragma unroll
       for (int i = 0; i < MAX_ITEMS; ++i) {
         const int e = st + i * NS;
@@ -557,13 +624,25 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   CPOLY_CUDA_OK(cudaGetDevice(&dev));
   CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const int grid = p.num_items < sms ? p.num_items : sms;
+  // offsets + mask as ONE dense 32-channel NHWC tensor (channels 0..17 / 18..26)?  -> coalesced staging
+  const int oes = a.om_dtype == CPOLY_BF16 ? 2 : 4;
+  p.om_esize = oes;
+  const cpoly_tensor4 &o = a.offset, &m = a.mask;
+  bool om_fast = o.sc == 1 && o.sw == 32 && o.sh == (int64_t)a.W * 32 && o.sb == (int64_t)a.H * a.W * 32 && m.sc == 1 && m.sw == 32 &&
+                 m.sh == o.sh && m.sb == o.sb && reinterpret_cast<const uint8_t*>(m.ptr) == reinterpret_cast<const uint8_t*>(o.ptr) + 18 * oes &&
+                 (reinterpret_cast<uintptr_t>(o.ptr) & 15) == 0 && (int64_t)a.B * a.H * a.W < (1LL << 26);
+  if (const char* e = getenv("CPOLY_TC_OM")) om_fast = om_fast && atoi(e) != 0;   // profiling knob: CPOLY_TC_OM=0 keeps the strided loads
+#define CPOLY_LAUNCH_FWD(TT, FAST)                                                                                            \
+  do {                                                                                                                        \
+    CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_fwd_tc_kernel<TT, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes)); \
+    dcn_fwd_tc_kernel<TT, FAST><<<grid, NTHREADS, smem_bytes, stream>>>(p);                                                   \
+  } while (0)
   if (a.dtype == CPOLY_BF16) {
-    CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_fwd_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    dcn_fwd_tc_kernel<__nv_bfloat16><<<grid, NTHREADS, smem_bytes, stream>>>(p);
+    if (om_fast) CPOLY_LAUNCH_FWD(__nv_bfloat16, true); else CPOLY_LAUNCH_FWD(__nv_bfloat16, false);
   } else {
-    CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_fwd_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    dcn_fwd_tc_kernel<float><<<grid, NTHREADS, smem_bytes, stream>>>(p);
+    if (om_fast) CPOLY_LAUNCH_FWD(float, true); else CPOLY_LAUNCH_FWD(float, false);
   }
+#undef CPOLY_LAUNCH_FWD
   if (int rc = check_launch("dcn_fwd_tc_kernel")) return rc;
   if (p.split > 1) return dcn_tc_launch_combine(p.partial, a.y.ptr, a.dtype, a.out_scale, a.bias, npix, a.Cout, p.split, a.relu, stream);
   return CPOLY_OK;

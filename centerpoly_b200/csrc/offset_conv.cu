@@ -1,0 +1,204 @@
+// The offset / mask producer of the DCN module: `conv_offset_mask`, a regular 3x3 / stride 1 / pad 1
+// convolution Cin -> 27 whose output is chunked into 18 offsets and 9 mask logits by upstream DCNv2's `DCN.forward`
+// (module constructed at src/lib/models/networks/pose_dla_dcn.py:354 and resnet_dcn.py:221-223; the extension is the
+// missing submodule src/lib/models/networks/DCNv2).  The reference runs it as cuDNN; here it is one implicit-GEMM kernel:
+//
+//   om[px, n] = bias[n] + sum_{tap, c} x[px + tap, c] * W[n, c, tap]        n < 32 (27 real channels + zero padding)
+//
+// NHWC bf16 activations, fp32 accumulation, fp32 (or bf16) NHWC output with the bias already added - the DCN kernels
+// then read exact fp32 offsets instead of bf16-rounded ones (an offset of 5.3 px rounded to bf16 moves the sampling
+// point by up to 0.02 px).  The GEMM is M = pixels, N = 32, K = 9 * Cin: N is far too narrow for tcgen05 to matter
+// (a 128 x 32 UMMA tile keeps the tensor pipe < 2 % busy either way) and the op is bound by reading x once and writing
+// 128 B per pixel, so it uses warp-level mma.sync (HMMA) fed by ldmatrix from a shared-memory window:
+//
+//   CTA = 8 warps = one 8 x 16 pixel tile per work item; warp w owns tile row w (16 pixels = one m16 block) x 32 outputs.
+//   Per (tile, 64-channel chunk): the 10 x 18 pixel halo window (23 KB, out-of-image pixels zero-filled by cp.async)
+//   and the chunk's 9 x 32 x 64 weights (36 KB, pre-swizzled image) are staged with 16-byte cp.async, double-buffered
+//   against the MMAs of the previous stage; 16-byte pieces are XOR-swizzled by (row & 7) so every ldmatrix phase is
+//   conflict-free.  A tap is just a shifted row address into the window: x is read from HBM/L2 exactly once per tile.
+#include "common.cuh"
+
+namespace cpoly {
+namespace {
+
+constexpr int OC_THREADS = 256;
+constexpr int OC_TH = 8, OC_TW = 16;                   // pixel tile
+constexpr int OC_WH = OC_TH + 2, OC_WW = OC_TW + 2;    // halo window
+constexpr int OC_N = 32;                               // padded output channels
+constexpr int OC_KC = 64;                              // input channels per stage (128 bytes of bf16)
+constexpr int OC_WIN_BYTES = OC_WH * OC_WW * 128;      // 23040
+constexpr int OC_WGT_BYTES = 9 * OC_N * 128;           // 36864
+
+struct OffsetConvParams {
+  const __nv_bfloat16* x;        // dense NHWC (B,H,W,Cin)
+  const uint4* wpacked;          // [Cin/64][9][32][8] 16-byte pieces, piece index XOR (n & 7)
+  const float* bias;             // [32] (padded with zeros)
+  void* om;                      // dense NHWC (B,H,W,32), fp32 or bf16
+  int B, Cin, H, W, nchunk, out_bf16;
+  int tiles_x, tiles_y, num_tiles, wgt_stages;
+};
+
+__device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(OC_THREADS) offset_conv3x3_kernel(const OffsetConvParams p) {
+  extern __shared__ __align__(128) uint8_t oc_smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  uint8_t* win_s[2] = {oc_smem, oc_smem + OC_WIN_BYTES};
+  uint8_t* wgt_s[2] = {oc_smem + 2 * OC_WIN_BYTES, oc_smem + 2 * OC_WIN_BYTES + (p.wgt_stages == 2 ? OC_WGT_BYTES : 0)};
+  const int tiles_per_img = p.tiles_x * p.tiles_y;
+  const int my_tiles = ((int)blockIdx.x < p.num_tiles) ? (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const int n_items = my_tiles * p.nchunk;
+  const size_t pixb = (size_t)p.Cin * sizeof(__nv_bfloat16);
+
+  // stage `it` = (tile, chunk): window + (when the weights are not resident) the chunk's weights
+  auto issue = [&](int it) {
+    const int tile = (int)blockIdx.x + (it / p.nchunk) * (int)gridDim.x, cc = it % p.nchunk;
+    const int b = tile / tiles_per_img, trem = tile - b * tiles_per_img;
+    const int ty0 = (trem / p.tiles_x) * OC_TH, tx0 = (trem % p.tiles_x) * OC_TW;
+    const uint32_t wbase = s_u32(win_s[it & 1]);
+    for (int i = tid; i < OC_WH * OC_WW * 8; i += OC_THREADS) {
+      const int pidx = i >> 3, j = i & 7;
+      const int y = ty0 - 1 + pidx / OC_WW, x = tx0 - 1 + pidx % OC_WW;
+      const bool in = (unsigned)y < (unsigned)p.H && (unsigned)x < (unsigned)p.W;
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(p.x) + ((size_t)(b * p.H + (in ? y : 0)) * p.W + (in ? x : 0)) * pixb + (size_t)cc * 128 + j * 16;
+      cp_async16(wbase + pidx * 128 + ((j ^ (pidx & 7)) << 4), src, in ? 16 : 0);     // src-size 0: zero fill (the conv's padding)
+    }
+    if (p.wgt_stages == 2 || it == 0) {
+      const uint32_t gbase = s_u32(wgt_s[p.wgt_stages == 2 ? (it & 1) : 0]);
+      const uint4* src = p.wpacked + (size_t)cc * (OC_WGT_BYTES / 16);
+      for (int i = tid; i < OC_WGT_BYTES / 16; i += OC_THREADS) cp_async16(gbase + i * 16, src + i, 16);
+    }
+    cp_async_commit();
+  };
+
+  if (n_items > 0) issue(0);
+  float acc[4][4];
+  // ldmatrix lane roles (constant): A x4 = (rows 0-7, k 0-7) (rows 8-15, k 0-7) (rows 0-7, k 8-15) (rows 8-15, k 8-15)
+  const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_kh = lane >> 4;
+  // B x4 = (n 0-7, k 0-7) (n 0-7, k 8-15) (n 8-15, k 0-7) (n 8-15, k 8-15) of a 16-output pair
+  const int b_n = (lane & 7) + (lane >> 4) * 8, b_kh = (lane >> 3) & 1;
+  for (int it = 0; it < n_items; ++it) {
+    if (it + 1 < n_items) { issue(it + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    __syncthreads();
+    const int tile = (int)blockIdx.x + (it / p.nchunk) * (int)gridDim.x, cc = it % p.nchunk;
+    if (cc == 0) {
+#pragma unroll
+      for (int t = 0; t < 4; ++t) acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
+    }
+    const uint32_t wbase = s_u32(win_s[it & 1]);
+    const uint32_t gbase = s_u32(wgt_s[p.wgt_stages == 2 ? (it & 1) : 0]);
+#pragma unroll 1
+    for (int tap = 0; tap < 9; ++tap) {
+      const int ti = tap / 3, tj = tap - 3 * ti;
+      const int pidx = (warp + ti) * OC_WW + tj + a_row;          // window pixel this lane addresses for the A rows
+      const uint32_t a_addr = wbase + pidx * 128;
+      const uint32_t b_addr = gbase + tap * (OC_N * 128) + b_n * 128;
+#pragma unroll
+      for (int ks = 0; ks < OC_KC / 16; ++ks) {
+        uint32_t a[4], b0[4], b1[4];
+        ldmatrix_x4(a_addr + ((((ks << 1) | a_kh) ^ (pidx & 7)) << 4), a[0], a[1], a[2], a[3]);
+        ldmatrix_x4(b_addr + ((((ks << 1) | b_kh) ^ (b_n & 7)) << 4), b0[0], b0[1], b0[2], b0[3]);
+        ldmatrix_x4(b_addr + 16 * 128 + ((((ks << 1) | b_kh) ^ (b_n & 7)) << 4), b1[0], b1[1], b1[2], b1[3]);
+        mma_bf16_16816(acc[0], a, b0[0], b0[1]);
+        mma_bf16_16816(acc[1], a, b0[2], b0[3]);
+        mma_bf16_16816(acc[2], a, b1[0], b1[1]);
+        mma_bf16_16816(acc[3], a, b1[2], b1[3]);
+      }
+    }
+    if (cc == p.nchunk - 1) {
+      // C fragment: c0,c1 -> row lane/4, columns 2*(lane%4), +1 of each 8-wide output block; c2,c3 -> row lane/4 + 8
+      const int b = tile / tiles_per_img, trem = tile - b * tiles_per_img;
+      const int y = (trem / p.tiles_x) * OC_TH + warp, tx0 = (trem % p.tiles_x) * OC_TW;
+      if (y < p.H) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int x = tx0 + (lane >> 2) + half * 8;
+          if (x >= p.W) continue;
+          const size_t pix = (size_t)(b * p.H + y) * p.W + x;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const int n = t * 8 + (lane & 3) * 2;
+            const float v0 = acc[t][half * 2] + __ldg(p.bias + n), v1 = acc[t][half * 2 + 1] + __ldg(p.bias + n + 1);
+            if (p.out_bf16) {
+              const __nv_bfloat162 pk = __floats2bfloat162_rn(v0, v1);
+              *reinterpret_cast<__nv_bfloat162*>(reinterpret_cast<__nv_bfloat16*>(p.om) + pix * OC_N + n) = pk;
+            } else {
+              *reinterpret_cast<float2*>(reinterpret_cast<float*>(p.om) + pix * OC_N + n) = make_float2(v0, v1);
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();   // the buffers of this stage are refilled by the next issue()
+  }
+}
+
+// conv_offset_mask.weight (n_out <= 32, Cin, 3, 3), any float dtype as fp32 -> [Cin/64][9][32][8 pieces] bf16, piece j of
+// row n stored at j ^ (n & 7); rows >= n_out are zero.
+__global__ void offset_conv_pack_kernel(const float* __restrict__ w, uint4* __restrict__ out, int Cin, int n_out) {
+  const int total = (Cin / OC_KC) * 9 * OC_N * 8;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int j = i & 7;
+    int t = i >> 3;
+    const int n = t % OC_N; t /= OC_N;
+    const int tap = t % 9;
+    const int cc = t / 9;
+    uint32_t words[4] = {0u, 0u, 0u, 0u};
+    if (n < n_out) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int c = cc * OC_KC + j * 8 + 2 * e;
+        const __nv_bfloat162 pk = __floats2bfloat162_rn(w[((size_t)n * Cin + c) * 9 + tap], w[((size_t)n * Cin + c + 1) * 9 + tap]);
+        words[e] = *reinterpret_cast<const uint32_t*>(&pk);
+      }
+    }
+    out[((size_t)(cc * 9 + tap) * OC_N + n) * 8 + (j ^ (n & 7))] = make_uint4(words[0], words[1], words[2], words[3]);
+  }
+}
+
+}  // namespace
+
+size_t offset_conv_packed_bytes(int Cin) { return (Cin % OC_KC == 0) ? (size_t)(Cin / OC_KC) * OC_WGT_BYTES : 0; }
+
+int offset_conv_pack_launch(const float* weight, void* packed, int Cin, int n_out, cudaStream_t stream) {
+  const int total = (Cin / OC_KC) * 9 * OC_N * 8;
+  offset_conv_pack_kernel<<<(total + 255) / 256, 256, 0, stream>>>(weight, reinterpret_cast<uint4*>(packed), Cin, n_out);
+  return check_launch("offset_conv_pack_kernel");
+}
+
+int offset_conv_launch(const cpoly_offset_conv_args& a, cudaStream_t stream) {
+  OffsetConvParams p;
+  p.x = reinterpret_cast<const __nv_bfloat16*>(a.x);
+  p.wpacked = reinterpret_cast<const uint4*>(a.weight_packed);
+  p.bias = a.bias;
+  p.om = a.om;
+  p.B = a.B; p.Cin = a.Cin; p.H = a.H; p.W = a.W; p.nchunk = a.Cin / OC_KC; p.out_bf16 = a.om_dtype == CPOLY_BF16;
+  p.tiles_x = (a.W + OC_TW - 1) / OC_TW; p.tiles_y = (a.H + OC_TH - 1) / OC_TH;
+  p.num_tiles = a.B * p.tiles_x * p.tiles_y;
+  if (p.num_tiles == 0) return CPOLY_OK;
+  p.wgt_stages = p.nchunk == 1 ? 1 : 2;          // one chunk: the weights stay resident for the whole kernel
+  const int smem = 2 * OC_WIN_BYTES + p.wgt_stages * OC_WGT_BYTES;
+  int dev = 0, sms = 0;
+  CPOLY_CUDA_OK(cudaGetDevice(&dev));
+  CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  CPOLY_CUDA_OK(cudaFuncSetAttribute(offset_conv3x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const int per_sm = p.wgt_stages == 1 ? 2 : 1;
+  const int grid = p.num_tiles < sms * per_sm ? p.num_tiles : sms * per_sm;
+  offset_conv3x3_kernel<<<grid, OC_THREADS, smem, stream>>>(p);
+  return check_launch("offset_conv3x3_kernel");
+}
+
+}  // namespace cpoly

@@ -23,9 +23,16 @@ from torch.nn.modules.utils import _pair
 
 from . import _lib
 
-__all__ = ["DCN", "DCNv2", "dcn_v2_conv", "_DCNv2", "set_dcn_path", "invalidate_packed_weights"]
+__all__ = ["DCN", "DCNv2", "dcn_v2_conv", "_DCNv2", "set_dcn_path", "set_offset_conv", "invalidate_packed_weights"]
 
 _FORCED_PATH = _lib.PATH_AUTO
+_USE_OWN_OFFSET_CONV = True     # tests / profiling: False routes the fused inference path back to F.conv2d (cuDNN)
+
+
+def set_offset_conv(own: bool) -> None:
+    global _USE_OWN_OFFSET_CONV
+    _USE_OWN_OFFSET_CONV = bool(own)
+
 
 
 def set_dcn_path(path: str) -> None:
@@ -345,6 +352,48 @@ class DCN(DCNv2):
             self.conv_offset_mask.weight.zero_()
             self.conv_offset_mask.bias.zero_()
 
+    def _offset_conv_image(self):
+        """(packed bf16 weight image of conv_offset_mask for cpoly_offset_conv_forward, fp32 bias padded to 32) or
+        None when the shape has no fast path: a derived cache, never in state_dict."""
+        w, b = self.conv_offset_mask.weight, self.conv_offset_mask.bias
+        L = _lib.lib()
+        nbytes = L.cpoly_offset_conv_packed_bytes(self.in_channels)
+        if (nbytes == 0 or w.shape[0] > 32 or tuple(w.shape[2:]) != (3, 3) or self.stride != (1, 1) or self.padding != (1, 1) or
+                self.dilation != (1, 1)):
+            return None
+        tag = (w._version, w.data_ptr(), w.dtype, w.device, b._version, b.data_ptr())
+        hit = getattr(self, "_oc_cache", None)
+        if hit is None or hit[0] != tag:
+            w32 = w.detach().float().contiguous()
+            packed = torch.empty(nbytes, dtype=torch.uint8, device=w.device)
+            _lib.check(L.cpoly_offset_conv_pack_weights(w32.data_ptr(), packed.data_ptr(), self.in_channels, w.shape[0],
+                                                        _lib.stream_ptr(w.device)), "cpoly_offset_conv_pack_weights")
+            bias = torch.zeros(32, dtype=torch.float32, device=w.device)
+            bias[:w.shape[0]] = b.detach().float()
+            hit = (tag, packed, bias)
+            self._oc_cache = hit
+        return hit[1], hit[2]
+
+    def offset_conv(self, input):
+        """``conv_offset_mask(input)`` on our kernel (csrc/offset_conv.cu): (B,32,H,W) fp32 channels_last, channels
+        27..31 zero, bias included; None when the input does not qualify (then the caller uses the nn.Conv2d)."""
+        if not (input.is_cuda and input.dtype == torch.bfloat16 and input.dim() == 4):
+            return None
+        img = self._offset_conv_image()
+        if img is None:
+            return None
+        if not input.is_contiguous(memory_format=torch.channels_last):
+            input = input.contiguous(memory_format=torch.channels_last)
+        B, C, H, W = input.shape
+        with torch.cuda.device(input.device):
+            om = torch.empty((B, 32, H, W), dtype=torch.float32, device=input.device, memory_format=torch.channels_last)
+            a = _lib.OffsetConvArgs()
+            a.B, a.Cin, a.H, a.W, a.om_dtype = B, C, H, W, _lib.F32
+            a.x, a.weight_packed, a.bias, a.om = input.data_ptr(), img[0].data_ptr(), img[1].data_ptr(), om.data_ptr()
+            _lib.check(_lib.lib().cpoly_offset_conv_forward(byref(a), _lib.stream_ptr(input.device)), "cpoly_offset_conv_forward")
+            _lib.LAUNCHES["offset_conv"] += 1
+        return om
+
     def _padded_offset_conv(self):
         """(weight padded to a multiple of 8 output channels, fp32 bias): derived cache, never in state_dict."""
         w, b = self.conv_offset_mask.weight, self.conv_offset_mask.bias
@@ -369,13 +418,24 @@ class DCN(DCNv2):
             if torch.is_grad_enabled() and (input.requires_grad or self.weight.requires_grad):
                 raise RuntimeError("the fused DeformConv epilogue is inference-only; rebuild the model for training")
             scale, shift, relu = fused
-            w_om, b_om = self._padded_offset_conv()
-            om = torch.nn.functional.conv2d(input, w_om, None, self.stride, self.padding)
             n_off = self.deformable_groups * 2 * self.kernel_size[0] * self.kernel_size[1]
             n_all = n_off // 2 * 3
+            om = self.offset_conv(input) if _USE_OWN_OFFSET_CONV else None
+            if om is not None:      # our kernel: fp32 offsets / mask logits, bias already added
+                y, _ = _forward_impl(input, om[:, :n_off], om[:, n_off:n_all], self.weight, shift, self.stride, self.padding,
+                                     self.dilation, self.deformable_groups, True, out_scale=scale, relu=relu)
+                return y
+            w_om, b_om = self._padded_offset_conv()
+            om = torch.nn.functional.conv2d(input, w_om, None, self.stride, self.padding)
             y, _ = _forward_impl(input, om[:, :n_off], om[:, n_off:n_all], self.weight, shift, self.stride, self.padding,
                                  self.dilation, self.deformable_groups, True, out_scale=scale, relu=relu, om_bias=b_om)
             return y
+        if not torch.is_grad_enabled() and _USE_OWN_OFFSET_CONV and not torch.is_autocast_enabled():
+            om = self.offset_conv(input)       # inference through the plain module: same kernel as the fused path
+            if om is not None:
+                y, _ = _forward_impl(input, om[:, :18], om[:, 18:27], self.weight, self.bias, self.stride, self.padding,
+                                     self.dilation, self.deformable_groups, True)
+                return y
         om = self.conv_offset_mask(input)
         return _DCNFused.apply(input, om, self.weight, self.bias, self.stride, self.padding, self.dilation,
                                self.deformable_groups)

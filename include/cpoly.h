@@ -14,6 +14,8 @@
  *                           src/lib/trains/base_trainer.py:97-98 `loss.backward()`).
  *   cpoly_dcn_pack_weights  (new) derived tap-major / MMA-swizzled weight cache; the stored parameter stays
  *                           (Cout,Cin,kh,kw) so checkpoints (src/lib/models/model.py:31-130) are unaffected.
+ *   cpoly_offset_conv_forward <- `conv_offset_mask(input)` inside upstream DCNv2's `DCN.forward` (the module built at
+ *                           src/lib/models/networks/pose_dla_dcn.py:354); cuDNN in the reference.
  *   cpoly_idaup_upsample_forward <- the depthwise `nn.ConvTranspose2d` `up_i` of IDAUp
  *                           (src/lib/models/networks/pose_dla_dcn.py:372-375,385) fused with the skip add of :387.
  *   cpoly_decode         <- `polydet_decode(heat, polys, depth, reg, cat_spec_poly, K, rep)`  [+ optionally the
@@ -53,7 +55,7 @@
 extern "C" {
 #endif
 
-#define CPOLY_ABI_VERSION 7
+#define CPOLY_ABI_VERSION 8
 
 /* element types */
 #define CPOLY_F32 0
@@ -307,6 +309,27 @@ typedef struct {
 } cpoly_maxpool_args;
 
 int cpoly_maxpool2x2_nhwc_forward(const cpoly_maxpool_args* args, cpoly_stream_t stream);
+
+/* ---- the DCN module's offset / mask producer (ABI v8) ------------------------------------------------------------
+ * `conv_offset_mask` of upstream DCNv2's `DCN` (a regular 3x3, stride 1, pad 1 Conv2d(Cin, 27) constructed with the
+ * module at src/lib/models/networks/pose_dla_dcn.py:354 / resnet_dcn.py:221-223; `DCN.forward` chunks its output into
+ * 18 offsets + 9 mask logits).  om = conv3x3(x, W) + bias, 32 output channels (27 + 5 zero), NHWC, fp32 or bf16 - the
+ * layout cpoly_dcn_forward reads with offset = om[:, :18], mask = om[:, 18:27] (mask_is_logit = 1).
+ * x: dense channels_last bf16 (B,Cin,H,W), Cin a multiple of 64. */
+typedef struct {
+  int32_t B, Cin, H, W;
+  int32_t om_dtype;          /* CPOLY_F32 or CPOLY_BF16 */
+  int32_t reserved0;
+  const void* x;             /* bf16, dense NHWC, 16-byte aligned */
+  const void* weight_packed; /* cpoly_offset_conv_pack_weights image */
+  const float* bias;         /* 32 floats (27 + zeros) */
+  void* om;                  /* dense NHWC (B,H,W,32), 16-byte aligned */
+} cpoly_offset_conv_args;
+
+size_t cpoly_offset_conv_packed_bytes(int32_t Cin);   /* 0 when the shape has no fast path */
+/* weight: fp32 contiguous (n_out <= 32, Cin, 3, 3) */
+int cpoly_offset_conv_pack_weights(const float* weight, void* packed, int32_t Cin, int32_t n_out, cpoly_stream_t stream);
+int cpoly_offset_conv_forward(const cpoly_offset_conv_args* args, cpoly_stream_t stream);
 
 #ifdef __cplusplus
 }

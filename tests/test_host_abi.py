@@ -18,7 +18,7 @@ def test_library_exports_every_declared_symbol():
     L = ctypes.CDLL(_lib.LIB_PATH)
     for sym in declared:
         assert hasattr(L, sym), sym
-    assert _lib.lib().cpoly_abi_version() == 7
+    assert _lib.lib().cpoly_abi_version() == 8
 
 
 def test_struct_layouts_match_header(tmp_path):
@@ -28,7 +28,8 @@ def test_struct_layouts_match_header(tmp_path):
     names = {"cpoly_tensor4": _lib.Tensor4, "cpoly_dcn_fwd_args": _lib.DcnFwdArgs, "cpoly_dcn_bwd_args": _lib.DcnBwdArgs,
              "cpoly_upsample_args": _lib.UpsampleArgs, "cpoly_decode_args": _lib.DecodeArgs,
              "cpoly_raster_args": _lib.RasterArgs, "cpoly_poly_iou_args": _lib.PolyIouArgs, "cpoly_stem_args": _lib.StemArgs,
-             "cpoly_maxpool_args": _lib.MaxPoolArgs, "cpoly_upsample_bwd_args": _lib.UpsampleBwdArgs}
+             "cpoly_maxpool_args": _lib.MaxPoolArgs, "cpoly_upsample_bwd_args": _lib.UpsampleBwdArgs,
+             "cpoly_offset_conv_args": _lib.OffsetConvArgs}
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include "cpoly.h"\nint main(void){' +
                    "".join(f'printf("{n} %zu\\n", sizeof({n}));' for n in names) + "return 0;}\n")
@@ -48,6 +49,7 @@ def test_size_queries_need_no_gpu():
     assert L.cpoly_dcn_packed_weight_bytes(48, 64, 3, 3, _lib.BF16) == 0      # Cin not a multiple of 64
     assert L.cpoly_dcn_packed_weight_bytes(64, 64, 5, 5, _lib.BF16) == 0
     assert L.cpoly_decode_workspace_bytes(1, 8, 256, 512, 100) >= 256
+    assert L.cpoly_offset_conv_packed_bytes(128) == 2 * 9 * 32 * 64 * 2 and L.cpoly_offset_conv_packed_bytes(48) == 0
 
 
 def test_module_api_and_state_dict():
