@@ -1,0 +1,114 @@
+"""GPU, 2 ranks, NCCL: data-parallel correctness on the REAL network (last row) - DLA-34 + 16 DCN layers
+through the tensor-core backward.  After one backward, the bucket-averaged gradients of every rank equal the
+single-process gradients of the concatenated batch (BatchNorm in eval mode so that the statistics do not depend on the
+batch split; the loss is a mean over equal shards, so mean-of-means == mean).  Also: replicas that start from different
+weights are repaired by the broadcast, and the all-reduces are enqueued BEFORE the backward has finished (overlap).
+
+Reference semantics: nn.DataParallel reduce-adds replica gradients onto GPU 0 and averages the loss
+(src/lib/models/data_parallel.py:119-128, src/lib/trains/base_trainer.py:95).  Skipped unless >= 2 GPUs are visible."""
+import os
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+HEADS = {"hm": 8, "poly": 64, "pseudo_depth": 1, "reg": 2}
+H, W, PER_RANK = 128, 256, 2
+
+
+def _build(seed):
+    from centerpoly_b200.harness.dla34 import PolydetDLA34, calibrate_random_init
+    torch.manual_seed(seed)
+    net = PolydetDLA34(HEADS).cuda().to(memory_format=torch.channels_last)
+    calibrate_random_init(net, 64, 128)
+    return net.eval()          # BN running statistics: independent of how the batch is split
+
+
+def _loss(net, batch, dtype):
+    from centerpoly_b200.harness.train import polydet_l1_loss
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=dtype == "bf16"):
+        out = net(batch["input"])[-1]
+    return polydet_l1_loss(out, batch)
+
+
+def _batch(lo, hi):
+    from centerpoly_b200.harness.train import synthetic_batch
+    full = synthetic_batch(2 * PER_RANK, H, W, n_obj=5, device="cuda", seed=9)
+    b = {k: v[lo:hi].contiguous() for k, v in full.items()}
+    b["input"] = b["input"].contiguous(memory_format=torch.channels_last)
+    return b
+
+
+def _worker(rank, world, port, dtype, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    from centerpoly_b200.harness.train import BucketedAllReduce, broadcast_module_state
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    net = _build(317 + rank)                       # rank-dependent init on purpose
+    assert broadcast_module_state(net) > 0          # ... repaired here
+    red = BucketedAllReduce(list(net.parameters()), bucket_bytes=8 << 20)
+    assert len(red.buckets) >= 2
+    batch = _batch(rank * PER_RANK, (rank + 1) * PER_RANK)
+    done = torch.cuda.Event(enable_timing=True)
+    loss = _loss(net, batch, dtype)
+    loss.backward()
+    done.record()
+    red.finish()
+    torch.cuda.synchronize()
+    # overlap: the first bucket's all-reduce was enqueued before the backward's last kernel finished
+    first_launch = red.last_launch_events[0][1]
+    early = first_launch.elapsed_time(done)         # > 0: launch happened before `done`
+    grads = {n: p.grad.detach().float().cpu().numpy() for n, p in net.named_parameters() if p.grad is not None}
+    q.put((rank, float(loss), early, len(red.buckets), grads))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("dtype", ["fp32", "bf16"])
+def test_two_rank_gradients_equal_full_batch_gradients(dtype):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import numpy as np
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, dtype, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = {}
+    for _ in range(2):
+        r = q.get(timeout=600)
+        got[r[0]] = r[1:]
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    # single process, concatenated batch, rank 0's weights
+    torch.cuda.set_device(0)
+    net = _build(317)
+    loss = _loss(net, _batch(0, 2 * PER_RANK), dtype)
+    loss.backward()
+    want = {n: p.grad.detach().float().cpu().numpy() for n, p in net.named_parameters() if p.grad is not None}
+    g0, g1 = got[0][3], got[1][3]
+    assert set(g0) == set(want) == set(g1)
+    # the all-reduce leaves identical bits on both ranks
+    assert all(np.array_equal(g0[n], g1[n]) for n in want)
+    # per-rank losses average to the full-batch loss; the heat-map focal term is normalised per shard by its own number
+    # of positives (equal here: 5 objects per image), so mean-of-means == mean
+    tol = 1e-2 if dtype == "bf16" else 1e-3
+    assert abs(0.5 * (got[0][0] + got[1][0]) - float(loss)) <= tol * abs(float(loss))
+    bad = []
+    for n in want:
+        scale = max(np.abs(want[n]).max(), 1e-12)
+        err = np.abs(g0[n] - want[n]).max() / scale
+        if err > (5e-2 if dtype == "bf16" else 5e-3):
+            bad.append((n, float(err)))
+    assert not bad, bad[:8]
+    print(f"\n2-rank DP [{dtype}]: {len(want)} gradient tensors match the full-batch gradients; first all-reduce enqueued "
+          f"{got[0][1]:.2f} ms before the backward finished on rank 0, {got[1][1]:.2f} ms on rank 1 ({got[0][2]} buckets)")
+    assert got[0][1] > 0 and got[1][1] > 0
