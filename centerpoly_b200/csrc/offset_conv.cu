@@ -16,7 +16,10 @@
 //   and the chunk's 9 x 32 x 64 weights (36 KB, pre-swizzled image) are staged with 16-byte cp.async, double-buffered
 //   against the MMAs of the previous stage; 16-byte pieces are XOR-swizzled by (row & 7) so every ldmatrix phase is
 //   conflict-free.  A tap is just a shifted row address into the window: x is read from HBM/L2 exactly once per tile.
-#include "common.cuh"
+#include <stdlib.h>
+#include <string.h>
+
+#include "tc_common.cuh"
 
 namespace cpoly {
 namespace {
@@ -146,6 +149,117 @@ __global__ void __launch_bounds__(OC_THREADS) offset_conv3x3_kernel(const Offset
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// tcgen05 version (default).  mma.sync tops out near 180 TFLOP/s on this part (the kernel above: 27 us for the
+// 64-channel 256x512 layer, 338 us per frame against cuDNN's ~190), so the GEMM moves to the 5th-generation tensor
+// cores: per (tile, 64-channel chunk) 9 taps x 4 tcgen05.mma (M = 128 pixels, N = 32, K = 16) accumulate in 32 TMEM
+// columns.  The A operand of a tap must be a K-major SWIZZLE_128B tile whose 8-row groups are 1024 B apart, which a
+// halo window with an 18-pixel pitch cannot offer; so the window is staged THREE times, shifted by -1 / 0 / +1 pixel
+// (10 rows x 16 pixels x 128 B each, cp.async with zero fill = the convolution's padding): tap (i, j) is then the
+// contiguous 16 KB starting at row i of window j - a plain descriptor, 1024-byte aligned.  One stage (3 windows +
+// the chunk's weights, 96 KB) per CTA, two CTAs per SM overlap each other's load and MMA phases.
+constexpr int OT_THREADS = 128;
+constexpr int OT_WIN1 = OC_WH * OC_TW * 128;           // one shifted window: 10 x 16 pixels x 128 B = 20480
+constexpr int OT_WIN_BYTES = 3 * OT_WIN1;              // 61440
+constexpr int OT_SMEM = OT_WIN_BYTES + OC_WGT_BYTES + 1024;   // + alignment slack
+
+__global__ void __launch_bounds__(OT_THREADS) offset_conv3x3_tc_kernel(const OffsetConvParams p) {
+  using namespace tc;
+  extern __shared__ uint8_t ot_smem_raw[];
+  __shared__ __align__(8) uint64_t bar_storage;
+  __shared__ uint32_t tmem_ptr_s;
+  uint8_t* smem = ot_smem_raw + ((1024u - (smem_u32(ot_smem_raw) & 1023u)) & 1023u);
+  const uint32_t win0 = smem_u32(smem), wgt0 = win0 + OT_WIN_BYTES;
+  const uint32_t bar = smem_u32(&bar_storage);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tiles_per_img = p.tiles_x * p.tiles_y;
+  const int my_tiles = ((int)blockIdx.x < p.num_tiles) ? (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const int n_items = my_tiles * p.nchunk;
+  const size_t pixb = (size_t)p.Cin * sizeof(__nv_bfloat16);
+
+  if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_ptr_s), 32u);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = tmem_ptr_s;
+  const uint32_t idesc = umma_idesc(false, 128, OC_N);
+  uint32_t phase = 0;
+
+  for (int it = 0; it < n_items; ++it) {
+    const int tile = (int)blockIdx.x + (it / p.nchunk) * (int)gridDim.x, cc = it % p.nchunk;
+    const int b = tile / tiles_per_img, trem = tile - b * tiles_per_img;
+    const int ty0 = (trem / p.tiles_x) * OC_TH, tx0 = (trem % p.tiles_x) * OC_TW;
+    // ---- stage: three shifted windows (+ the chunk's weights unless they are resident)
+    for (int i = tid; i < 3 * OC_WH * OC_TW * 8; i += OT_THREADS) {
+      const int j = i & 7, row = (i >> 3) % (OC_WH * OC_TW), sh = (i >> 3) / (OC_WH * OC_TW);
+      const int y = ty0 - 1 + (row >> 4), x = tx0 - 1 + sh + (row & 15);
+      const bool in = (unsigned)y < (unsigned)p.H && (unsigned)x < (unsigned)p.W;
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(p.x) + ((size_t)(b * p.H + (in ? y : 0)) * p.W + (in ? x : 0)) * pixb + (size_t)cc * 128 + j * 16;
+      cp_async16(win0 + sh * OT_WIN1 + row * 128 + ((j ^ (row & 7)) << 4), src, in ? 16 : 0);
+    }
+    if (p.nchunk > 1 || it == 0) {
+      const uint4* src = p.wpacked + (size_t)cc * (OC_WGT_BYTES / 16);
+      for (int i = tid; i < OC_WGT_BYTES / 16; i += OT_THREADS) cp_async16(wgt0 + i * 16, src + i, 16);
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
+    fence_proxy_async_smem();     // generic-proxy (cp.async) writes -> visible to the tensor core
+    __syncthreads();
+    // ---- 9 taps x 4 K-steps
+    if (warp == 0) {
+      tc_fence_after();
+      if (elect_one()) {
+#pragma unroll 1
+        for (int tap = 0; tap < 9; ++tap) {
+          const int ti = tap / 3, tj = tap - 3 * ti;
+          const uint64_t adesc = umma_desc_sw128(win0 + tj * OT_WIN1 + ti * (OC_TW * 128));
+          const uint64_t bdesc = umma_desc_sw128(wgt0 + tap * (OC_N * 128));
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            umma<false>(tmem_acc, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (cc | tap | kk) != 0 ? 1u : 0u);
+        }
+        umma_commit(bar);
+      }
+      __syncwarp();
+    }
+    mbar_wait(bar, phase, 20);    // the MMAs have read the stage (and, after the last chunk, the accumulator is complete)
+    phase ^= 1u;
+    if (cc == p.nchunk - 1) {
+      tc_fence_after();
+      const int r = warp * 32 + lane;                          // TMEM lane = M row = pixel (r / 16, r % 16) of the tile
+      const int y = ty0 + (r >> 4), x = tx0 + (r & 15);
+      const uint32_t t_row = tmem_acc + ((uint32_t)(warp * 32) << 16);
+      uint32_t v0[16], v1[16];
+      tmem_ld16(t_row, v0);
+      tmem_ld16(t_row + 16u, v1);
+      tmem_ld_wait();
+      if (y < p.H && x < p.W) {
+        const size_t pix = (size_t)(b * p.H + y) * p.W + x;
+        float o[32];
+#pragma unroll
+        for (int n = 0; n < 16; ++n) { o[n] = __uint_as_float(v0[n]) + __ldg(p.bias + n); o[16 + n] = __uint_as_float(v1[n]) + __ldg(p.bias + 16 + n); }
+        if (p.out_bf16) {
+          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.om) + pix * OC_N);
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            dst[q] = make_uint4(pack_bf16x2(o[8 * q], o[8 * q + 1]), pack_bf16x2(o[8 * q + 2], o[8 * q + 3]), pack_bf16x2(o[8 * q + 4], o[8 * q + 5]),
+                                pack_bf16x2(o[8 * q + 6], o[8 * q + 7]));
+        } else {
+          float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.om) + pix * OC_N);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) dst[q] = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+        }
+      }
+      tc_fence_before();
+    }
+    __syncthreads();   // every warp has read the accumulator / the stage may be refilled
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem_acc, 32u); }
+}
+
 // conv_offset_mask.weight (n_out <= 32, Cin, 3, 3), any float dtype as fp32 -> [Cin/64][9][32][8 pieces] bf16, piece j of
 // row n stored at j ^ (n & 7); rows >= n_out are zero.
 __global__ void offset_conv_pack_kernel(const float* __restrict__ w, uint4* __restrict__ out, int Cin, int n_out) {
@@ -189,11 +303,19 @@ int offset_conv_launch(const cpoly_offset_conv_args& a, cudaStream_t stream) {
   p.tiles_x = (a.W + OC_TW - 1) / OC_TW; p.tiles_y = (a.H + OC_TH - 1) / OC_TH;
   p.num_tiles = a.B * p.tiles_x * p.tiles_y;
   if (p.num_tiles == 0) return CPOLY_OK;
-  p.wgt_stages = p.nchunk == 1 ? 1 : 2;          // one chunk: the weights stay resident for the whole kernel
-  const int smem = 2 * OC_WIN_BYTES + p.wgt_stages * OC_WGT_BYTES;
   int dev = 0, sms = 0;
   CPOLY_CUDA_OK(cudaGetDevice(&dev));
   CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const char* e = getenv("CPOLY_OFFSET_CONV");
+  if (!(e && strcmp(e, "mma") == 0)) {            // default: tcgen05; CPOLY_OFFSET_CONV=mma keeps the warp-level kernel
+    p.wgt_stages = 1;
+    CPOLY_CUDA_OK(cudaFuncSetAttribute(offset_conv3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OT_SMEM));
+    const int grid = p.num_tiles < 2 * sms ? p.num_tiles : 2 * sms;
+    offset_conv3x3_tc_kernel<<<grid, OT_THREADS, OT_SMEM, stream>>>(p);
+    return check_launch("offset_conv3x3_tc_kernel");
+  }
+  p.wgt_stages = p.nchunk == 1 ? 1 : 2;          // one chunk: the weights stay resident for the whole kernel
+  const int smem = 2 * OC_WIN_BYTES + p.wgt_stages * OC_WGT_BYTES;
   CPOLY_CUDA_OK(cudaFuncSetAttribute(offset_conv3x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int per_sm = p.wgt_stages == 1 ? 2 : 1;
   const int grid = p.num_tiles < sms * per_sm ? p.num_tiles : sms * per_sm;

@@ -153,7 +153,7 @@ class BucketedAllReduce:
         for p in plist:
             views.append((p, flat[off:off + p.numel()].view_as(p)))
             off += p.numel()
-        self.buckets.append(dict(flat=flat, views=views, pending=len(plist), work=None, n=len(plist), launched=False))
+        self.buckets.append(dict(flat=flat, views=views, pending=len(plist), work=None, n=len(plist), launched=False, idx=len(self.buckets)))
 
     def _on_grad(self, p):
         b = self.buckets[self._where[p]]
@@ -184,7 +184,7 @@ class BucketedAllReduce:
             if self.stream is not None:
                 ev = torch.cuda.Event(enable_timing=True)
                 ev.record(self.stream)
-                self.launch_events.append((self.buckets.index(b), ev))
+                self.launch_events.append((b["idx"], ev))
         b["launched"] = True
 
     def finish(self):

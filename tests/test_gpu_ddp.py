@@ -81,10 +81,19 @@ def test_two_rank_gradients_equal_full_batch_gradients(dtype):
     procs = [ctx.Process(target=_worker, args=(r, 2, port, dtype, q)) for r in range(2)]
     for p in procs:
         p.start()
-    got = {}
-    for _ in range(2):
-        r = q.get(timeout=600)
-        got[r[0]] = r[1:]
+    import queue as _queue
+    import time
+    got, t0 = {}, time.time()
+    while len(got) < 2:                      # a crashed worker must fail the test at once, not after a long timeout
+        try:
+            r = q.get(timeout=2)
+            got[r[0]] = r[1:]
+        except _queue.Empty:
+            dead = [p.exitcode for p in procs if p.exitcode not in (None, 0)]
+            if dead or time.time() - t0 > 240:
+                for p in procs:
+                    p.kill()
+                pytest.fail(f"data-parallel worker failed (exit codes {dead}) or timed out")
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
