@@ -7,15 +7,16 @@
 //
 // NHWC bf16 activations, fp32 accumulation, fp32 (or bf16) NHWC output with the bias already added - the DCN kernels
 // then read exact fp32 offsets instead of bf16-rounded ones (an offset of 5.3 px rounded to bf16 moves the sampling
-// point by up to 0.02 px).  The GEMM is M = pixels, N = 32, K = 9 * Cin: N is far too narrow for tcgen05 to matter
-// (a 128 x 32 UMMA tile keeps the tensor pipe < 2 % busy either way) and the op is bound by reading x once and writing
-// 128 B per pixel, so it uses warp-level mma.sync (HMMA) fed by ldmatrix from a shared-memory window:
+// point by up to 0.02 px).  The GEMM is M = pixels, N = 32, K = 9 * Cin.  Two kernels:
 //
-//   CTA = 8 warps = one 8 x 16 pixel tile per work item; warp w owns tile row w (16 pixels = one m16 block) x 32 outputs.
-//   Per (tile, 64-channel chunk): the 10 x 18 pixel halo window (23 KB, out-of-image pixels zero-filled by cp.async)
-//   and the chunk's 9 x 32 x 64 weights (36 KB, pre-swizzled image) are staged with 16-byte cp.async, double-buffered
-//   against the MMAs of the previous stage; 16-byte pieces are XOR-swizzled by (row & 7) so every ldmatrix phase is
-//   conflict-free.  A tap is just a shifted row address into the window: x is read from HBM/L2 exactly once per tile.
+//   offset_conv3x3_tc_kernel (default)  tcgen05 / TMEM, further down in this file.
+//   offset_conv3x3_kernel (CPOLY_OFFSET_CONV=mma)  the first version: warp-level mma.sync (HMMA) fed by ldmatrix from a
+//   shared-memory halo window.  CTA = 8 warps = one 8 x 16 pixel tile per work item; warp w owns tile row w (16 pixels =
+//   one m16 block) x 32 outputs.  Per (tile, 64-channel chunk): the 10 x 18 pixel halo window (23 KB, out-of-image
+//   pixels zero-filled by cp.async) and the chunk's 9 x 32 x 64 weights (36 KB, pre-swizzled image) are staged with
+//   16-byte cp.async, double-buffered against the MMAs of the previous stage; 16-byte pieces are XOR-swizzled by
+//   (row & 7) so every ldmatrix phase is conflict-free.  Measured: HMMA-bound at ~180 TFLOP/s (27 us for the 64-channel
+//   256x512 layer, 338 us per frame) - kept for comparison.
 #include <stdlib.h>
 #include <string.h>
 
@@ -166,18 +167,19 @@ constexpr int OT_SMEM = OT_WIN_BYTES + OC_WGT_BYTES + 1024;   // + alignment sla
 __global__ void __launch_bounds__(OT_THREADS) offset_conv3x3_tc_kernel(const OffsetConvParams p) {
   using namespace tc;
   extern __shared__ uint8_t ot_smem_raw[];
-  __shared__ __align__(8) uint64_t bar_storage;
+  __shared__ __align__(8) uint64_t bar_storage, wbar_storage;
   __shared__ uint32_t tmem_ptr_s;
   uint8_t* smem = ot_smem_raw + ((1024u - (smem_u32(ot_smem_raw) & 1023u)) & 1023u);
   const uint32_t win0 = smem_u32(smem), wgt0 = win0 + OT_WIN_BYTES;
-  const uint32_t bar = smem_u32(&bar_storage);
+  const uint32_t bar = smem_u32(&bar_storage), wbar = smem_u32(&wbar_storage);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int tiles_per_img = p.tiles_x * p.tiles_y;
   const int my_tiles = ((int)blockIdx.x < p.num_tiles) ? (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
   const int n_items = my_tiles * p.nchunk;
   const size_t pixb = (size_t)p.Cin * sizeof(__nv_bfloat16);
+  uint32_t wphase = 0;
 
-  if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+  if (tid == 0) { mbar_init(bar, 1); mbar_init(wbar, 1); fence_mbar_init(); }
   if (warp == 0) tmem_alloc(smem_u32(&tmem_ptr_s), 32u);
   tc_fence_before();
   __syncthreads();
@@ -190,21 +192,34 @@ __global__ void __launch_bounds__(OT_THREADS) offset_conv3x3_tc_kernel(const Off
     const int tile = (int)blockIdx.x + (it / p.nchunk) * (int)gridDim.x, cc = it % p.nchunk;
     const int b = tile / tiles_per_img, trem = tile - b * tiles_per_img;
     const int ty0 = (trem / p.tiles_x) * OC_TH, tx0 = (trem % p.tiles_x) * OC_TW;
-    // ---- stage: three shifted windows (+ the chunk's weights unless they are resident)
-    for (int i = tid; i < 3 * OC_WH * OC_TW * 8; i += OT_THREADS) {
-      const int j = i & 7, row = (i >> 3) % (OC_WH * OC_TW), sh = (i >> 3) / (OC_WH * OC_TW);
-      const int y = ty0 - 1 + (row >> 4), x = tx0 - 1 + sh + (row & 15);
-      const bool in = (unsigned)y < (unsigned)p.H && (unsigned)x < (unsigned)p.W;
-      const uint8_t* src = reinterpret_cast<const uint8_t*>(p.x) + ((size_t)(b * p.H + (in ? y : 0)) * p.W + (in ? x : 0)) * pixb + (size_t)cc * 128 + j * 16;
-      cp_async16(win0 + sh * OT_WIN1 + row * 128 + ((j ^ (row & 7)) << 4), src, in ? 16 : 0);
+    // ---- stage: three shifted windows (+ the chunk's weights unless they are resident).  The 128 threads cover exactly
+    // one window row (16 pixels x 8 pieces) per step, so the address of a step is the previous one plus a row pitch: no
+    // per-piece index arithmetic (the first version spent ~3000 cycles per stage on it).  The weights are ONE bulk copy.
+    if (tid == 0 && (p.nchunk > 1 || it == 0)) {
+      mbar_arrive_expect_tx(wbar, (uint32_t)OC_WGT_BYTES);
+      bulk_copy_g2s(wgt0, p.wpacked + (size_t)cc * (OC_WGT_BYTES / 16), (uint32_t)OC_WGT_BYTES, wbar);
     }
-    if (p.nchunk > 1 || it == 0) {
-      const uint4* src = p.wpacked + (size_t)cc * (OC_WGT_BYTES / 16);
-      for (int i = tid; i < OC_WGT_BYTES / 16; i += OT_THREADS) cp_async16(wgt0 + i * 16, src + i, 16);
+    {
+      const int px = tid >> 3, j = tid & 7;
+      const uint32_t dst0 = win0 + (uint32_t)px * 128u + (uint32_t)((j ^ (px & 7)) << 4);
+      const uint8_t* img = reinterpret_cast<const uint8_t*>(p.x) + (size_t)b * p.H * p.W * pixb + (size_t)cc * 128 + j * 16;
+#pragma unroll
+      for (int sh = 0; sh < 3; ++sh) {
+        const int x = tx0 - 1 + sh + px;
+        const bool xin = (unsigned)x < (unsigned)p.W;
+        const uint8_t* col = img + (size_t)(xin ? x : 0) * pixb;
+#pragma unroll
+        for (int wy = 0; wy < OC_WH; ++wy) {
+          const int y = ty0 - 1 + wy;
+          const bool in = xin && (unsigned)y < (unsigned)p.H;
+          cp_async16(dst0 + (uint32_t)(sh * OT_WIN1 + wy * (OC_TW * 128)), col + (size_t)(in ? y : 0) * p.W * pixb, in ? 16 : 0);
+        }
+      }
     }
     cp_async_commit();
     cp_async_wait<0>();
     fence_proxy_async_smem();     // generic-proxy (cp.async) writes -> visible to the tensor core
+    if (p.nchunk > 1 || it == 0) { mbar_wait(wbar, wphase, 20); wphase ^= 1u; }
     __syncthreads();
     // ---- 9 taps x 4 K-steps
     if (warp == 0) {

@@ -60,12 +60,59 @@ def fuse_deform_convs(model: nn.Module) -> int:
     return n
 
 
+CONCURRENT_PROJ = True      # run the mutually independent proj_i DCNs of one IDAUp call on side streams (see below)
+_SIDE_STREAMS = {}
+
+
+def _side_streams(device, n):
+    pool = _SIDE_STREAMS.setdefault(device, [])
+    while len(pool) < n:
+        pool.append(torch.cuda.Stream(device))
+    return pool[:n]
+
+
 def _idaup_forward_fused(self, layers, startp, endp):
-    """IDAUp.forward (pose_dla_dcn.py:381-387) with up + skip-add as one kernel."""
-    for i in range(startp + 1, endp):
+    """IDAUp.forward (pose_dla_dcn.py:381-387) with up + skip-add as one kernel.
+
+    Inside one call every ``proj_i`` reads only its own ``layers[i]`` (the ``node_i`` form the serial chain through
+    ``layers[i-1]``), so the proj DCNs - and their offset/mask producers - are forked onto side streams and joined
+    before their ``up_i``.  At batch 1 a proj layer is 64..256 pixel tiles on 148 SMs: a persistent kernel's last wave
+    leaves up to 100 SMs idle, which the next proj's CTAs now fill.  The fork/join is plain events, so it is captured
+    into the engine's CUDA graph as parallel branches."""
+    idx = list(range(startp + 1, endp))
+    x0 = layers[idx[0]] if idx else None
+    if not (CONCURRENT_PROJ and len(idx) >= 2 and x0.is_cuda and not torch.is_grad_enabled()):
+        for i in idx:
+            j = str(i - startp)
+            up, proj, node = getattr(self, "up_" + j), getattr(self, "proj_" + j), getattr(self, "node_" + j)
+            layers[i] = node(up(proj(layers[i]), layers[i - 1]))
+        return
+    cur = torch.cuda.current_stream(x0.device)
+    side = _side_streams(x0.device, len(idx) - 1)
+    fork = torch.cuda.Event()
+    fork.record(cur)
+    projected = {}
+    for n, i in enumerate(idx):
+        proj = getattr(self, "proj_" + str(i - startp))
+        if n == 0:
+            projected[i] = (proj(layers[i]), None)
+        else:
+            s = side[n - 1]
+            s.wait_event(fork)
+            with torch.cuda.stream(s):
+                t = proj(layers[i])
+            ev = torch.cuda.Event()
+            ev.record(s)
+            projected[i] = (t, ev)
+    capturing = torch.cuda.is_current_stream_capturing()
+    for i in idx:
         j = str(i - startp)
-        up, proj, node = getattr(self, "up_" + j), getattr(self, "proj_" + j), getattr(self, "node_" + j)
-        layers[i] = node(up(proj(layers[i]), layers[i - 1]))
+        t, ev = projected.pop(i)
+        if ev is not None:
+            cur.wait_event(ev)
+            if not capturing:
+                t.record_stream(cur)     # produced on a side stream, consumed (and later freed) under the main stream
+        layers[i] = getattr(self, "node_" + j)(getattr(self, "up_" + j)(t, layers[i - 1]))
 
 
 def fuse_idaup(model: nn.Module) -> int:
