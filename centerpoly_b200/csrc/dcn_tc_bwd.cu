@@ -357,12 +357,7 @@ int dcn_wgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_
 namespace {
 
 constexpr int D_BUFS = 2;          // TMEM accumulators and shared gcol tiles
-constexpr int W_STAGES = 2;
-constexpr int DG_PARAM_BYTES = NUM_TAPS * TILE_PX * 16;
-constexpr int DG_POFF_OFF = 1024;
-constexpr int DG_PW_OFF = DG_POFF_OFF + DG_PARAM_BYTES;
-constexpr int DG_PM_OFF = DG_PW_OFF + DG_PARAM_BYTES;
-constexpr int DG_BUF_OFF = ((DG_PM_OFF + DG_PARAM_BYTES + 1023) / 1024) * 1024;
+constexpr int DG_POFF_OFF = 1024;  // three parameter arrays of taps_per_item * 128 * 16 bytes follow (runtime size)
 
 struct DgradParams {
   Geom g;
@@ -375,6 +370,8 @@ struct DgradParams {
   int k_atoms;             // 128-byte atoms along K = Cout
   int a_bufs;
   int w_stage_bytes;
+  int w_stages;            // 2, or 1 when shared memory is short (fp32 with Cout = 256: the gout tile alone is 128 KB)
+  int param_bytes;         // bytes of ONE parameter array = taps_per_item * 128 * 16
 };
 
 // Four channels of one (pixel, tap): v[q][e] corner values (invalid corners already zeroed), g[e] = gcol.
@@ -408,11 +405,12 @@ __global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
   const uint32_t bar_fullG = smem_base, bar_emptyG = bar_fullG + 16, bar_Wfull = bar_emptyG + 16, bar_Wempty = bar_Wfull + 16;
   const uint32_t bar_Dfull = bar_Wempty + 16, bar_Dempty = bar_Dfull + 16, bar_gfull = bar_Dempty + 16, bar_gempty = bar_gfull + 16;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + 8 * 16);
-  const uint32_t poff_s = smem_base + DG_POFF_OFF, pw_s = smem_base + DG_PW_OFF, pm_s = smem_base + DG_PM_OFF;
+  const uint32_t poff_s = smem_base + DG_POFF_OFF, pw_s = poff_s + (uint32_t)p.param_bytes, pm_s = pw_s + (uint32_t)p.param_bytes;
   const uint32_t a_bytes = (uint32_t)p.k_atoms * ATOM_BYTES;
-  const uint32_t abuf0 = smem_base + DG_BUF_OFF;
+  const uint32_t abuf0 = smem_base + ((DG_POFF_OFF + 3u * (uint32_t)p.param_bytes + 1023u) & ~1023u);
   const uint32_t wst0 = abuf0 + (uint32_t)p.a_bufs * a_bytes;
-  const uint32_t gcol0 = wst0 + (uint32_t)W_STAGES * (uint32_t)p.w_stage_bytes;
+  const uint32_t gcol0 = wst0 + (uint32_t)p.w_stages * (uint32_t)p.w_stage_bytes;
+  const bool w2 = p.w_stages == 2;   // weight ring cursor of block n: stage n & 1 / phase (n >> 1) & 1, or stage 0 / phase n & 1
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int blocks_per_item = p.taps_per_item * p.nchunk;
 
@@ -584,7 +582,7 @@ __global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
       for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
         const int tap0 = (item % p.split) * p.taps_per_item;
         for (int q = 0; q < blocks_per_item; ++q, ++nblk) {
-          const uint32_t ws = nblk & 1u, wph = (nblk >> 1) & 1u;
+          const uint32_t ws = w2 ? (nblk & 1u) : 0u, wph = w2 ? ((nblk >> 1) & 1u) : (nblk & 1u);
           mbar_wait(bar_Wempty + 8 * ws, wph ^ 1u, 200);
           mbar_arrive_expect_tx(bar_Wfull + 8 * ws, (uint32_t)p.w_stage_bytes);
           bulk_copy_g2s(wst0 + ws * (uint32_t)p.w_stage_bytes, wsrc + (size_t)(tap0 * p.nchunk + q) * p.w_stage_bytes,
@@ -604,10 +602,11 @@ __global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
         const uint32_t abuf = abuf0 + ra.s * a_bytes;
         for (int q = 0; q < blocks_per_item; ++q, ++nblk) {
           const uint32_t d = nblk & 1u, dph = (nblk >> 1) & 1u;
-          mbar_wait(bar_Wfull + 8 * d, dph, 32);
+          const uint32_t ws = w2 ? d : 0u, wph = w2 ? dph : (nblk & 1u);
+          mbar_wait(bar_Wfull + 8 * ws, wph, 32);
           mbar_wait(bar_Dempty + 8 * d, dph ^ 1u, 32);
           tc_fence_after();
-          const uint32_t wst = wst0 + d * (uint32_t)p.w_stage_bytes;
+          const uint32_t wst = wst0 + ws * (uint32_t)p.w_stage_bytes;
           const uint32_t d_tmem = tmem_base + d * (uint32_t)kChunk;
           if (elect_one()) {
             for (int ka = 0; ka < p.k_atoms; ++ka) {
@@ -617,7 +616,7 @@ __global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
               for (int kk = 0; kk < 4; ++kk)
                 umma<kTF32>(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (ka | kk) != 0 ? 1u : 0u);
             }
-            umma_commit(bar_Wempty + 8 * d);
+            umma_commit(bar_Wempty + 8 * ws);
             umma_commit(bar_Dfull + 8 * d);
             if (q == blocks_per_item - 1) umma_commit(bar_emptyG + 8 * ra.s);
           }
@@ -712,7 +711,7 @@ __global__ void pack_dgrad_weights_kernel(const float* __restrict__ w, uint4* __
 }
 
 struct DgradPlan {
-  int nchunk, k_atoms, a_bufs, w_stage_bytes, split, smem_bytes;
+  int nchunk, k_atoms, a_bufs, w_stage_bytes, w_stages, split, param_bytes, smem_bytes;
   size_t packed_bytes;
   bool ok;
 };
@@ -724,14 +723,25 @@ DgradPlan plan_dgrad(const cpoly_dcn_fwd_args& a) {
   d.nchunk = a.Cin / kchunk;
   d.k_atoms = a.Cout / kchunk;
   d.w_stage_bytes = d.k_atoms * kchunk * ROW_BYTES;
-  const int a_bytes = d.k_atoms * ATOM_BYTES;
-  const int fixed = DG_BUF_OFF + W_STAGES * d.w_stage_bytes + D_BUFS * ATOM_BYTES;
-  d.a_bufs = (SMEM_LIMIT - fixed) / a_bytes >= 2 ? 2 : 1;
-  d.smem_bytes = fixed + d.a_bufs * a_bytes + 1024;
   d.packed_bytes = (size_t)NUM_TAPS * a.Cin * a.Cout * esize;
+  const int a_bytes = d.k_atoms * ATOM_BYTES;
   const int tiles = a.B * ((a.W + TILE_W - 1) / TILE_W) * ((a.H + TILE_H - 1) / TILE_H);
   d.split = tiles >= 148 ? 1 : (tiles * 3 >= 148 ? 3 : 9);
-  d.ok = a.Cout % kchunk == 0 && a.Cin % kchunk == 0 && fixed + a_bytes <= SMEM_LIMIT;
+  d.ok = false;
+  if (a.Cout % kchunk != 0 || a.Cin % kchunk != 0) return d;
+  // first choice: the natural tap split and a 2-stage weight ring; when that does not fit (fp32 with Cout = 256: the gout
+  // tile alone is 128 KB) stage at most 3 taps of parameters per item and keep ONE weight stage
+  for (int attempt = 0; attempt < 2 && !d.ok; ++attempt) {
+    if (attempt == 1) { d.split = d.split < 3 ? 3 : d.split; }
+    d.w_stages = attempt == 0 ? 2 : 1;
+    d.param_bytes = (NUM_TAPS / d.split) * TILE_PX * 16;
+    const int buf_off = (DG_POFF_OFF + 3 * d.param_bytes + 1023) / 1024 * 1024;
+    const int fixed = buf_off + d.w_stages * d.w_stage_bytes + D_BUFS * ATOM_BYTES;
+    if (fixed + a_bytes > SMEM_LIMIT) continue;
+    d.a_bufs = (SMEM_LIMIT - fixed) / a_bytes >= 2 ? 2 : 1;
+    d.smem_bytes = fixed + d.a_bufs * a_bytes + 1024;
+    d.ok = true;
+  }
   return d;
 }
 
@@ -778,7 +788,7 @@ int dcn_dgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_
   p.gout = a.gout.ptr; p.wpacked = workspace; p.gcol = a.gx.ptr ? c2i_ws : nullptr;
   p.goffset = a.goffset; p.gmask = a.gmask;
   p.nchunk = d.nchunk; p.split = d.split; p.taps_per_item = NUM_TAPS / d.split; p.num_items = p.g.num_tiles * d.split;
-  p.k_atoms = d.k_atoms; p.a_bufs = d.a_bufs; p.w_stage_bytes = d.w_stage_bytes;
+  p.k_atoms = d.k_atoms; p.a_bufs = d.a_bufs; p.w_stage_bytes = d.w_stage_bytes; p.w_stages = d.w_stages; p.param_bytes = d.param_bytes;
   if (p.num_items == 0) return CPOLY_OK;
   int dev = 0, sms = 0;
   CPOLY_CUDA_OK(cudaGetDevice(&dev));

@@ -325,6 +325,7 @@ int offset_conv_launch(const cpoly_offset_conv_args& a, cudaStream_t stream) {
   if (!(e && strcmp(e, "mma") == 0)) {            // default: tcgen05; CPOLY_OFFSET_CONV=mma keeps the warp-level kernel
     p.wgt_stages = 1;
     CPOLY_CUDA_OK(cudaFuncSetAttribute(offset_conv3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OT_SMEM));
+    CPOLY_CUDA_OK(cudaFuncSetAttribute(offset_conv3x3_tc_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));   // two CTAs per SM
     const int grid = p.num_tiles < 2 * sms ? p.num_tiles : 2 * sms;
     offset_conv3x3_tc_kernel<<<grid, OT_THREADS, OT_SMEM, stream>>>(p);
     return check_launch("offset_conv3x3_tc_kernel");
