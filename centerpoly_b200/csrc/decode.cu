@@ -7,21 +7,20 @@
 // 64-channel poly map (33.5 MB at 2048x1024) to fetch K x 64 values; here the heat map is read from HBM once
 // (a second time from L2) and only K x (2N+3) head values are gathered.
 //
-// Exact top-K by histogram threshold, three small launches per image group (groups are sized so that a group's
-// heat maps stay L2 resident between the first two):
-//   1 scan + histogram   every warp owns a 128-column band x RH rows of one (image, class) plane; rows roll
-//                        through registers (vertical 3-max), the horizontal 3-max uses warp shuffles; a pixel is
-//                        a peak iff it equals its 3x3 max (plateaus keep every member, like `hmax == heat`).
-//                        Peaks are counted in a shared-memory histogram over the top 13 bits of the score
-//                        (32 bins per octave), flushed to the image's global histogram once per CTA.
-//   2 threshold + collect each CTA finds the bin holding the K-th best peak of its image and re-scans its items
-//                        (now L2 hits), appending the peaks at or above that bin — about K + one bin's
-//                        population — to the image's candidate list as 64-bit keys (score << 32 | ~flat index).
-//   3 select + gather    one CTA per image: radix-select the top K candidates, bitonic-sort them (score desc,
-//                        flat index asc — the oracle's tie rule), gather reg / poly / depth at the K centres,
-//                        polar -> cartesian, centre add, bbox, write (K, 2N+7).
-// Degenerate maps whose boundary bin overflows the candidate list (e.g. a constant map) take a slow exact path in
-// launch 3 (the CTA re-scans the image itself).
+// Exact top-K in five small launches:
+//   1 bounds             the only pass over every pixel: per item (128 columns x 8 rows of one class plane) the largest
+//                        value, and whether it is certainly an NMS peak (>= the one-pixel ring around the item).
+//   2 T0                 per image: the K-th largest certified peak is a lower bound T0 of the K-th best peak score.
+//   3 collect            items whose maximum reaches T0's bin (a few percent) are re-scanned with the full NMS: 3x3
+//                        maximum by warp shuffles (horizontal) and rolling registers (vertical); a pixel is a peak iff it
+//                        equals its 3x3 max (plateaus keep every member, like `hmax == heat`); peaks at or above that bin
+//                        go to the image's candidate list as 64-bit keys (score << 32 | ~flat index).
+//   4 select             one CTA per image: radix-select the top K candidates, bitonic-sort them (score desc, flat index
+//                        asc - the oracle's tie rule).
+//   5 gather             one warp per detection: reg / poly / depth at the K centres, polar -> cartesian, centre add,
+//                        bbox, optional back-mapping, write (K, 2N+7).
+// Degenerate maps whose candidates overflow the list (e.g. a constant map) take a slow exact path in launch 4 (the CTA
+// re-scans the image itself).
 //
 // The two-stage top-K of the reference (per class, then over C*K) equals the global top-K over
 // (class, y, x) whenever scores are tie-free; heat must be non-negative (it is post-sigmoid).
@@ -49,11 +48,11 @@ struct DecodeParams {
   float* out;
   int64_t* out_inds;
   const double* post_affine;   // (B,6) inverse affine of polydet_post_process, or NULL
-  unsigned int* hist;          // [B][HBINS]
   unsigned long long* cand;    // [B][CAND_CAP]
   unsigned int* cand_count;    // [B]
-  int* tbin;                   // [B] histogram bin of the K-th best peak (decode_threshold_kernel)
+  int* tbin;                   // [B] score bin (bits [30:18]) of T0, the lower bound of the K-th best peak (decode_t0_kernel)
   unsigned int* item_max;      // [B][items_per_image] upper bound (float bits) of the peak scores of every scan item
+  unsigned int* item_cert;     // [B][items_per_image] that maximum when it is certainly an NMS peak, else 0 (float bits)
   int rh;                      // rows per warp work item
   int nbands, nrowchunks, items_per_image;
   int b0, nb;                  // image group handled by this launch (kernels 1 and 2)
@@ -213,37 +212,41 @@ __device__ __forceinline__ float head_value(const cpoly_tensor4& t, int b, int c
 // All RH + 2 rows (one halo row above and below) are LOADED FIRST - RH + 2 independent 16-byte loads per lane in
 // flight (5 KB per warp) - and only then shuffled / compared: with one row per loop iteration a warp paid one DRAM
 // latency per row, and a 64-image batch ran at 5 % of the HBM roof (tools/decode_bench.py).
-template <typename T, int RH, typename F>
-__device__ __forceinline__ void scan_item(const DecodeParams& p, int b, int item, int lane, F&& f) {
+// Loads of one item (a 128-column band x RH rows of one class plane, plus one halo row above / below and one halo column
+// left / right): v[i][j] = row r0 - 1 + i, columns xb .. xb + 3 of this lane; hv[i] = the halo column of that row (lane 0:
+// left, lane 31: right).  Raw values (logits stay logits); out-of-image -> -inf.  ALL RH + 2 rows are requested before
+// anything is consumed.
+template <typename T, int RH>
+__device__ __forceinline__ void load_item(const DecodeParams& p, int b, int item, int lane, float (&v)[RH + 2][4], float (&hv)[RH + 2],
+                                          int& c, int& r0, int& xb) {
   constexpr int NR = RH + 2;
   const float NEG = -CUDART_INF_F;
   int t = item;
   const int band = t % p.nbands; t /= p.nbands;
   const int rc = t % p.nrowchunks;
-  const int c = t / p.nrowchunks;
-  const int r0 = rc * RH, x0 = band * BAND;
-  const bool logit = p.heat_is_logit != 0;
+  c = t / p.nrowchunks;
+  r0 = rc * RH;
+  const int x0 = band * BAND;
   const int64_t sh = p.heat.sh, sw = p.heat.sw;
   const T* plane = reinterpret_cast<const T*>(p.heat.ptr) + (int64_t)b * p.heat.sb + (int64_t)c * p.heat.sc;
-  const int xb = x0 + lane * 4;
+  xb = x0 + lane * 4;
+  const int xbl = xb;
   // vector path: unit column stride, every row start aligned like the plane
   const bool aligned = sw == 1 && (sh % 4 == 0) && ((reinterpret_cast<uintptr_t>(plane + x0) % (4 * sizeof(T))) == 0);
   const bool full = aligned && x0 + BAND <= p.W;   // warp-uniform: the whole band is inside the row
   // lane 0 fetches the column left of the band, lane 31 the one right of it: one halo register per row
   const bool want_h = (lane == 0 && x0 > 0) || (lane == 31 && x0 + BAND < p.W);
   const int hx = lane == 0 ? x0 - 1 : x0 + BAND;
-  float v[NR][4], hv[NR];
   auto vec_load = [&](const T* row, float (&o)[4]) {
     if (sizeof(T) == 4) {
-      const float4 q = __ldg(reinterpret_cast<const float4*>(row + xb));
+      const float4 q = __ldg(reinterpret_cast<const float4*>(row + xbl));
       o[0] = q.x; o[1] = q.y; o[2] = q.z; o[3] = q.w;
     } else {
-      const uint2 q = __ldg(reinterpret_cast<const uint2*>(row + xb));
+      const uint2 q = __ldg(reinterpret_cast<const uint2*>(row + xbl));
       o[0] = __uint_as_float(q.x << 16); o[1] = __uint_as_float(q.x & 0xffff0000u);
       o[2] = __uint_as_float(q.y << 16); o[3] = __uint_as_float(q.y & 0xffff0000u);
     }
   };
-  // ---- phase 1: loads only
   if (full) {
 #pragma unroll
     for (int i = 0; i < NR; ++i) {
@@ -258,7 +261,7 @@ __device__ __forceinline__ void scan_item(const DecodeParams& p, int b, int item
       }
     }
   } else if (aligned && p.W % 4 == 0) {   // ragged band, but every lane's 4 columns are all inside or all outside the row
-    const bool in = xb < p.W;
+    const bool in = xbl < p.W;
 #pragma unroll
     for (int i = 0; i < NR; ++i) {
       const int y = r0 - 1 + i;
@@ -282,11 +285,21 @@ __device__ __forceinline__ void scan_item(const DecodeParams& p, int b, int item
       if (rv) {
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-          if (xb + j < p.W) v[i][j] = ld_as_float(row + (int64_t)(xb + j) * sw);
+          if (xbl + j < p.W) v[i][j] = ld_as_float(row + (int64_t)(xbl + j) * sw);
         if (want_h) hv[i] = ld_as_float(row + (int64_t)hx * sw);
       }
     }
   }
+}
+
+template <typename T, int RH, typename F>
+__device__ __forceinline__ void scan_item(const DecodeParams& p, int b, int item, int lane, F&& f) {
+  constexpr int NR = RH + 2;
+  const float NEG = -CUDART_INF_F;
+  const bool logit = p.heat_is_logit != 0;
+  float v[NR][4], hv[NR];
+  int c, r0, xb;
+  load_item<T, RH>(p, b, item, lane, v, hv, c, r0, xb);
   // ---- phase 2 (rolling, three rows of horizontal maxima live): logistic (fused hm.sigmoid_), horizontal
   // neighbours + 3-max of row i, then vertical 3-max + peak test of row i - 1
   const unsigned int flat0 = (unsigned int)(c * (p.H * p.W) + r0 * p.W + xb);
@@ -317,15 +330,7 @@ __device__ __forceinline__ void scan_item(const DecodeParams& p, int b, int item
   }
 }
 
-// hist[bin]++ when `on`: one predicated RED.shared, no branch around it
-__device__ __forceinline__ void red_shared_inc_if(bool on, uint32_t addr) {
-  asm volatile(
-      "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %0, 0;\n\t@q red.shared.add.u32 [%1], 1;\n\t}" ::"r"((uint32_t)on), "r"(addr)
-      : "memory");
-}
-
-// Work items of the image group [b0, b0+nb) are dealt to warps in CTA-contiguous blocks, so one CTA touches one
-// image (or two at a boundary) and flushes / thresholds once per image.
+// Work items of the image group [b0, b0+nb) are dealt to warps in CTA-contiguous blocks.
 __device__ __forceinline__ void cta_item_range(const DecodeParams& p, int64_t& beg, int64_t& end) {
   const int64_t total = (int64_t)p.nb * p.items_per_image;
   const int64_t per = (total + gridDim.x - 1) / gridDim.x;
@@ -333,97 +338,91 @@ __device__ __forceinline__ void cta_item_range(const DecodeParams& p, int64_t& b
   end = beg + per < total ? beg + per : total;
 }
 
-// ------------------------------------------------------------------ launch 1: NMS scan + score histogram
+// ------------------------------------------------------------------ launch 1: per-item bounds (the streaming pass)
+// The one pass that touches every pixel does only load + max (3 instructions per pixel; the histogram scan it replaces
+// needed 31 and was issue-bound at 39 % of the HBM roof).  Per item (128 columns x 8 rows of one class plane):
+//   item_max  = largest value inside the item        -> upper bound of its peak scores (the collection pass skips items
+//                                                       whose bound is below the image's threshold)
+//   item_cert = item_max if it is >= every value of the one-pixel ring around the item (and > 0), else 0.  A certified
+//               maximum IS an NMS peak (it equals its 3x3 maximum; plateaus keep every member, decode.py:13-19), so the
+//               K-th largest certificate of an image is a LOWER bound T0 of its K-th best peak score: every top-K
+//               detection has score >= T0, and for an untrained heat map only about K pixels in a million reach T0.
+// Logits: maxima are taken on the logits (the logistic function is monotone) and converted once per item.
 template <typename T>
-__global__ void __launch_bounds__(DNT, 3) decode_hist_kernel(DecodeParams p) {
-  __shared__ unsigned int hist[HBINS];
+__global__ void __launch_bounds__(DNT, 3) decode_bound_kernel(DecodeParams p) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int64_t beg, end;
   cta_item_range(p, beg, end);
-  if (beg >= end) return;
-  int cur_b = (int)(beg / p.items_per_image);
-  for (int i = tid; i < HBINS; i += DNT) hist[i] = 0u;
-  const uint32_t hist_addr = (uint32_t)__cvta_generic_to_shared(hist);
-  __syncthreads();
-  for (int64_t base = beg; base < end; base += DWARPS) {
-    // all warps of an iteration work on the same image: stop the batch at the image boundary
-    const int64_t img_end = (int64_t)(cur_b + 1) * p.items_per_image;
-    const int64_t lim = end < img_end ? end : img_end;
-    const int64_t it = base + warp;
-    if (it < lim) {
-      const int item = (int)(it - (int64_t)cur_b * p.items_per_image);
-      float mx = 0.f;   // upper bound of the item's peak scores: lets the collection pass skip items below the threshold bin
-      scan_item<T, SCAN_RH>(p, p.b0 + cur_b, item, lane, [&](bool pk, float s, float m3, unsigned int) {
-        red_shared_inc_if(pk, hist_addr + ((uint32_t)score_bin(s) << 2));
-        mx = fmaxf(mx, m3);   // >= every peak of the item (3x3 maxima incl. the halo): a conservative bound, one instruction
-      });
+  for (int64_t it = beg + warp; it < end; it += DWARPS) {
+    const int lb = (int)(it / p.items_per_image), item = (int)(it - (int64_t)lb * p.items_per_image);
+    constexpr int NR = SCAN_RH + 2;
+    float v[NR][4], hv[NR];
+    int c, r0, xb;
+    load_item<T, SCAN_RH>(p, p.b0 + lb, item, lane, v, hv, c, r0, xb);
+    float m_in = -CUDART_INF_F, m_ring = fmaxf(hv[0], hv[NR - 1]);
 #pragma unroll
-      for (int d = 16; d >= 1; d >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-      if (lane == 0) p.item_max[(int64_t)(p.b0 + cur_b) * p.items_per_image + item] = __float_as_uint(mx);
+    for (int j = 0; j < 4; ++j) m_ring = fmaxf(m_ring, fmaxf(v[0][j], v[NR - 1][j]));
+#pragma unroll
+    for (int i = 1; i < NR - 1; ++i) {
+      m_ring = fmaxf(m_ring, hv[i]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) m_in = fmaxf(m_in, v[i][j]);
     }
-    if (base + DWARPS >= lim) {   // uniform: image (or range) finished -> flush
-      __syncthreads();
-      unsigned int* gh = p.hist + (int64_t)(p.b0 + cur_b) * HBINS;
-      for (int i = tid; i < HBINS; i += DNT) {
-        const unsigned int n = hist[i];
-        if (n) { atomicAdd(gh + i, n); hist[i] = 0u; }
-      }
-      __syncthreads();
-      if (lim < end) {            // continue with the next image; re-align the batch start
-        cur_b += 1;
-        base = lim - DWARPS;      // loop increment brings it to `lim`
-      }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+      m_in = fmaxf(m_in, __shfl_xor_sync(0xffffffffu, m_in, d));
+      m_ring = fmaxf(m_ring, __shfl_xor_sync(0xffffffffu, m_ring, d));
+    }
+    if (lane == 0) {
+      const bool cert = m_in >= m_ring;
+      float mx = m_in;
+      if (p.heat_is_logit && mx != -CUDART_INF_F) mx = sigmoidf_accurate(mx);
+      mx = mx > 0.f ? mx : 0.f;
+      const int64_t slot = (int64_t)(p.b0 + lb) * p.items_per_image + item;
+      p.item_max[slot] = __float_as_uint(mx);
+      p.item_cert[slot] = __float_as_uint(cert ? mx : 0.f);
     }
   }
 }
 
-// Bin holding the K-th best peak of the image: smallest tb with count(bins >= tb) >= K (0 if there are fewer
-// than K peaks).  All DNT threads call it; `sh` is HBINS ints of shared scratch.
-__device__ int threshold_bin(const unsigned int* __restrict__ gh, int K, unsigned int* sh, int* s_result) {
-  const int tid = threadIdx.x;
-  constexpr int PER = HBINS / DNT;   // bins per thread, thread t owns the descending range starting at HBINS-1-t*PER
-  unsigned int mine = 0, cnt[PER];
-#pragma unroll
-  for (int q = 0; q < PER; ++q) cnt[q] = __ldcg(gh + (HBINS - 1 - tid * PER - q));   // all PER loads in flight
-#pragma unroll
-  for (int q = 0; q < PER; ++q) {
-    sh[HBINS - 1 - tid * PER - q] = cnt[q];
-    mine += cnt[q];
-  }
-  // inclusive scan of per-thread sums over the block (descending bin order)
-  __shared__ unsigned int warp_tot[DWARPS];
-  unsigned int incl = mine;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
-    if ((tid & 31) >= d) incl += t;
-  }
-  if ((tid & 31) == 31) warp_tot[tid >> 5] = incl;
-  if (tid == 0) *s_result = 0;
-  __syncthreads();
-  unsigned int before = 0;
-  for (int w = 0; w < (tid >> 5); ++w) before += warp_tot[w];
-  incl += before;
-  const unsigned int excl = incl - mine;
-  if (excl < (unsigned)K && incl >= (unsigned)K) {
-    unsigned int run = excl;
-    for (int q = 0; q < PER; ++q) {
-      run += sh[HBINS - 1 - tid * PER - q];
-      if (run >= (unsigned)K) { *s_result = HBINS - 1 - tid * PER - q; break; }
-    }
-  }
-  __syncthreads();
-  return *s_result;
-}
-
-// ------------------------------------------------------------------ launch 2: threshold bin of every image
+// ------------------------------------------------------------------ launch 2: T0 of every image (one CTA per image)
+// tbin[b] = histogram bin (score bits [30:18]) of the K-th largest certificate, 0 when the image has fewer than K.
 template <typename T>
-__global__ void __launch_bounds__(DNT) decode_threshold_kernel(DecodeParams p) {
-  __shared__ unsigned int sh[HBINS];
-  __shared__ int s_tb;
+__global__ void __launch_bounds__(DNT) decode_t0_kernel(DecodeParams p) {
+  __shared__ unsigned long long list[CAP];
+  __shared__ SelectScratch scratch;
+  __shared__ int s_pos;
+  const int tid = threadIdx.x;
   const int b = p.b0 + blockIdx.x;
-  const int tb = threshold_bin(p.hist + (int64_t)b * HBINS, p.K, sh, &s_tb);
-  if (threadIdx.x == 0) p.tbin[b] = tb;
+  const unsigned int* cert = p.item_cert + (int64_t)b * p.items_per_image;
+  const int K = p.K;
+  if (tid == 0) s_pos = 0;
+  __syncthreads();
+  int n = 0, mine = 0;
+  for (int off = 0; off < p.items_per_image;) {
+    if (n == CAP) {   // uniform: keep the K largest so far
+      block_select_topk(list, n, K, scratch);
+      n = K;
+    }
+    const int take = min(CAP - n, p.items_per_image - off);
+    for (int i = tid; i < take; i += DNT) {
+      const float c = __uint_as_float(__ldcg(cert + off + i));
+      list[n + i] = make_key(c, (unsigned int)(off + i));
+      mine += c > 0.f ? 1 : 0;
+    }
+    n += take;
+    off += take;
+    __syncthreads();
+  }
+  atomicAdd(&s_pos, mine);
+  __syncthreads();
+  int tb = 0;
+  if (s_pos >= K) {   // uniform; at least K certified peaks: the K-th largest of them bounds the K-th best peak from below
+    const unsigned long long lo = block_select_topk(list, n, K, scratch);
+    const float t0 = ordered_to_float((unsigned int)(lo >> 32));
+    tb = t0 > 0.f ? score_bin(t0) : 0;
+  }
+  if (tid == 0) p.tbin[b] = tb;
 }
 
 // ------------------------------------------------------------------ launch 3: candidate collection
@@ -674,13 +673,13 @@ size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 
 }  // namespace
 
-static size_t decode_zero_bytes(int B) { return (size_t)B * HBINS * sizeof(unsigned int) + 2 * (size_t)B * sizeof(unsigned int); }
+static size_t decode_zero_bytes(int B) { return 2 * (size_t)B * sizeof(unsigned int); }   // cand_count + tbin
 static size_t decode_items_per_image(int C, int H, int W) {
   return (size_t)C * ((H + SCAN_RH - 1) / SCAN_RH) * ((W + BAND - 1) / BAND);
 }
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K) {
   (void)K;
-  return align256(decode_zero_bytes(B)) + align256((size_t)B * decode_items_per_image(C, H, W) * sizeof(unsigned int)) +
+  return align256(decode_zero_bytes(B)) + 2 * align256((size_t)B * decode_items_per_image(C, H, W) * sizeof(unsigned int)) +
          align256((size_t)B * CAND_CAP * sizeof(unsigned long long)) + 256;
 }
 
@@ -697,14 +696,15 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
   CPOLY_REQUIRE((reinterpret_cast<uintptr_t>(a.workspace) & 255) == 0, CPOLY_EINVAL, "decode workspace must be 256-byte aligned");
   char* ws = reinterpret_cast<char*>(a.workspace);
   const size_t zero_bytes = decode_zero_bytes(a.B);
-  p.hist = reinterpret_cast<unsigned int*>(ws);
-  p.cand_count = p.hist + (size_t)a.B * HBINS;
+  p.cand_count = reinterpret_cast<unsigned int*>(ws);
   p.tbin = reinterpret_cast<int*>(p.cand_count + a.B);
   ws += align256(zero_bytes);
   p.item_max = reinterpret_cast<unsigned int*>(ws);
   ws += align256((size_t)a.B * decode_items_per_image(a.C, a.H, a.W) * sizeof(unsigned int));
+  p.item_cert = reinterpret_cast<unsigned int*>(ws);
+  ws += align256((size_t)a.B * decode_items_per_image(a.C, a.H, a.W) * sizeof(unsigned int));
   p.cand = reinterpret_cast<unsigned long long*>(ws);
-  CPOLY_CUDA_OK(cudaMemsetAsync(p.hist, 0, zero_bytes, stream));
+  CPOLY_CUDA_OK(cudaMemsetAsync(p.cand_count, 0, zero_bytes, stream));
   int dev = 0, sms = 0;
   CPOLY_CUDA_OK(cudaGetDevice(&dev));
   CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -717,12 +717,12 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
     const int64_t items = (int64_t)p.nb * p.items_per_image;
     int64_t ctas = (items + DWARPS - 1) / DWARPS;
     if (ctas > 3 * sms) ctas = 3 * sms;   // one resident wave: 24 warps per SM, each with (SCAN_RH + 2) x 512 B of loads in flight
-    if (bf) decode_hist_kernel<__nv_bfloat16><<<(unsigned)ctas, DNT, 0, stream>>>(p);
-    else decode_hist_kernel<float><<<(unsigned)ctas, DNT, 0, stream>>>(p);
-    if (int rc = check_launch("decode_hist_kernel")) return rc;
-    if (bf) decode_threshold_kernel<__nv_bfloat16><<<(unsigned)a.B, DNT, 0, stream>>>(p);
-    else decode_threshold_kernel<float><<<(unsigned)a.B, DNT, 0, stream>>>(p);
-    if (int rc = check_launch("decode_threshold_kernel")) return rc;
+    if (bf) decode_bound_kernel<__nv_bfloat16><<<(unsigned)ctas, DNT, 0, stream>>>(p);
+    else decode_bound_kernel<float><<<(unsigned)ctas, DNT, 0, stream>>>(p);
+    if (int rc = check_launch("decode_bound_kernel")) return rc;
+    if (bf) decode_t0_kernel<__nv_bfloat16><<<(unsigned)a.B, DNT, 0, stream>>>(p);
+    else decode_t0_kernel<float><<<(unsigned)a.B, DNT, 0, stream>>>(p);
+    if (int rc = check_launch("decode_t0_kernel")) return rc;
     const int64_t warps_wanted = (int64_t)3 * sms * DWARPS;
     int ipw = (int)((items + warps_wanted - 1) / warps_wanted);
     ipw = ipw < 1 ? 1 : (ipw > 32 ? 32 : ipw);

@@ -151,7 +151,11 @@ class BucketedAllReduce:
         flat = torch.zeros(n, dtype=torch.float32, device=plist[0].device)
         views, off = [], 0
         for p in plist:
-            views.append((p, flat[off:off + p.numel()].view_as(p)))
+            seg = flat[off:off + p.numel()]
+            # the slice takes the parameter's own (dense) layout - channels_last weights keep channels_last strides - so
+            # that p.grad can BE the slice (fused optimizers require params and grads of the same layout)
+            dense = p.is_contiguous() or (p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last))
+            views.append((p, seg.as_strided(p.shape, p.stride()) if dense else seg.view_as(p)))
             off += p.numel()
         self.buckets.append(dict(flat=flat, views=views, pending=len(plist), work=None, n=len(plist), launched=False, idx=len(self.buckets)))
 
