@@ -72,6 +72,7 @@ struct TcParams {
   int stages, b_stage_bytes, stage_bytes;
   int acc_cols, tmem_cols;
   int om_esize;    // element size of the fused 32-channel offset/mask tensor (kOmFast kernels)
+  int late_issue;  // sampler: corner loads of the next chunk issued after (1) or before (0) the proxy fence
 };
 
 // ---- blend of the four corner vectors (16 B each) into one 16-B piece of the A row ----------------
@@ -183,6 +184,11 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   const uint32_t tmem_base = *tmem_ptr_smem;
   const int chunks_per_item = p.taps_per_item * p.nchunk;
   const uint32_t nstages = (uint32_t)p.stages;
+  // A CTA walks a CONTIGUOUS range of items: consecutive tiles of a tile row share 43 % of their bilinear footprint
+  // (and the tap groups of one tile all of it), so the halo of the next item is already in this SM's L1 - with the
+  // round-robin deal of round 1 every item started cold (L1 sector hit rate 83 %, long-scoreboard stalls dominant).
+  const int item_beg = (int)(((long long)p.num_items * blockIdx.x) / gridDim.x);
+  const int item_end = (int)(((long long)p.num_items * (blockIdx.x + 1)) / gridDim.x);
 
   if (warp >= SAMPLER_WARP0) {
     // =========================================================================== samplers
@@ -271,8 +277,8 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       named_bar_sync(1, NS);   // the tile is dead: its bytes become weight parameters again
     };
     RingCursor rc;
-    if ((int)blockIdx.x < p.num_items) fetch_raw(blockIdx.x);
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+    if (item_beg < item_end) fetch_raw(item_beg);
+    for (int item = item_beg; item < item_end; ++item) {
       int b, ty0, tx0, tap0;
       item_coords(p, item, b, ty0, tx0, tap0);
       const int img_base = b * p.H * p.W * p.Cin;   // element offset; bytes < 2^32 (checked on the host)
@@ -307,7 +313,7 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
         sts16(pw_s + (uint32_t)(kl * TILE_PX + r) * 16u, pw);
       }
       named_bar_sync(1, NS);
-      if (item + (int)gridDim.x < p.num_items) fetch_raw(item + gridDim.x);
+      if (item + 1 < item_end) fetch_raw(item + 1);
       // Rolling software pipeline over the item's chunks: the corner loads of chunk q+1 are issued while chunk q
       // is blended, so every sampler warp keeps one pass (4 x 16 B per thread) in flight at all times instead of
       // alternating between a load phase and a blend phase.
@@ -337,16 +343,24 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
         mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u);
         const uint32_t a_base = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
         const bool more = q + 1 < chunks_per_item;
+        const bool late = p.late_issue != 0;
 #pragma unroll
         for (int pass = 0; pass < PASSES; ++pass) {
           const int r = pass * ROWS_PER_PASS + row_in_pass;
           sts16(a_base + r * ROW_BYTES + ((cg ^ (r & 7)) << 4), Blend<T>::run(c[pass], pw[pass]));
-          if (more) issue(n_pidx, n_cbyte, pass);
+          if (more && !late) issue(n_pidx, n_cbyte, pass);
         }
-        next_chunk();
         fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_fullA + 8 * rc.s);
+        // (fence.proxy.async is MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC in SASS: it waits for every load this thread has in
+        //  flight, so loads issued before it are drained at every step; issuing them after it keeps them in flight
+        //  across the wait for the next free stage)
+        if (more && late) {
+#pragma unroll
+          for (int pass = 0; pass < PASSES; ++pass) issue(n_pidx, n_cbyte, pass);
+        }
+        next_chunk();
         rc.advance(nstages);
       }
     }
@@ -355,7 +369,7 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
     // (whole warp walks the ring, one elected lane issues: see elect_one() in tc_common.cuh)
     RingCursor rc;
     const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(p.wpacked);
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+    for (int item = item_beg; item < item_end; ++item) {
       const int q0 = (item % p.split) * chunks_per_item;
       for (int q = 0; q < chunks_per_item; ++q) {
         mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u, 100);
@@ -373,7 +387,7 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
     const uint32_t idesc = umma_idesc(kTF32, TILE_PX, p.Cout);
     RingCursor rc;
     uint32_t tcount = 0;
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++tcount) {
+    for (int item = item_beg; item < item_end; ++item, ++tcount) {
       const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
       mbar_wait(bar_tempty + 8 * acc, accph ^ 1u, 50);  // epilogue drained this accumulator
       tc_fence_after();
@@ -401,7 +415,7 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
     T* yg = reinterpret_cast<T*>(p.y);
     const int64_t npix = (int64_t)p.B * p.H * p.W;
     uint32_t tcount = 0;
-    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++tcount) {
+    for (int item = item_beg; item < item_end; ++item, ++tcount) {
       const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
       int b, ty0, tx0, tap0;
       item_coords(p, item, b, ty0, tx0, tap0);
@@ -610,10 +624,11 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   p.stage_bytes = A_STAGE_BYTES + p.b_stage_bytes;
   int stages = (SMEM_LIMIT - SMEM_STAGE_OFF) / p.stage_bytes;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
-  if (const char* e = getenv("CPOLY_TC_STAGES")) {  // profiling knob: fewer stages leave more of the 256 KB to L1
-    const int v = atoi(e);
-    if (v >= 2 && v < stages) stages = v;
-  }
+  // 4 stages are as fast as 6 (r02 sweep: 2 / 3 / 4 / 6 stages = 79.8 / 77.9 / 78.0 / 79.9 us on 64->64 @256x512) and
+  // leave 48 KB more of the SM's 256 KB to L1, which is what the corner gathers live on
+  int want = 4;
+  if (const char* e = getenv("CPOLY_TC_STAGES")) want = atoi(e);  // profiling knob
+  if (want >= 2 && want < stages) stages = want;
   CPOLY_REQUIRE(stages >= 2, CPOLY_EUNSUPPORTED, "not enough shared memory for a 2-stage pipeline");
   p.stages = stages;
   p.acc_cols = a.Cout;
@@ -627,6 +642,8 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   // offsets + mask as ONE dense 32-channel NHWC tensor (channels 0..17 / 18..26)?  -> coalesced staging
   const int oes = a.om_dtype == CPOLY_BF16 ? 2 : 4;
   p.om_esize = oes;
+  p.late_issue = 1;
+  if (const char* e = getenv("CPOLY_TC_LATE")) p.late_issue = atoi(e) != 0;
   const cpoly_tensor4 &o = a.offset, &m = a.mask;
   bool om_fast = o.sc == 1 && o.sw == 32 && o.sh == (int64_t)a.W * 32 && o.sb == (int64_t)a.H * a.W * 32 && m.sc == 1 && m.sw == 32 &&
                  m.sh == o.sh && m.sb == o.sb && reinterpret_cast<const uint8_t*>(m.ptr) == reinterpret_cast<const uint8_t*>(o.ptr) + 18 * oes &&
