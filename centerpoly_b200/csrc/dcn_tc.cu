@@ -50,6 +50,7 @@ template <int kTH> struct TileCfg {
   static constexpr int SAMPLER_WARPS = kTH == 8 ? 16 : 24;
   static constexpr int NS = SAMPLER_WARPS * 32;                       // sampler threads
   static constexpr int NTHREADS = (SAMPLER_WARP0 + SAMPLER_WARPS) * 32;
+  static constexpr int MAXREG = kTH == 8 ? 80 : 64;                   // 704 x 80 / 960 x 64 registers (warp allocations are multiples of 512: 88 does not fit)
   static constexpr int ROWS_PER_PASS = NS / 8;                        // 8 lanes x 16 B cover one 128-byte row
   static constexpr int PASSES = TILE_PX / ROWS_PER_PASS;
   static constexpr int MAX_ITEMS = (NUM_TAPS * TILE_PX + NS - 1) / NS;  // (pixel, tap) parameter items per sampler thread
@@ -85,6 +86,7 @@ struct TcParams {
   int acc_cols, tmem_cols;
   int om_esize;    // element size of the fused 32-channel offset/mask tensor (kOmFast kernels)
   int tile_h;      // 8 or 6 (TileCfg)
+  uint32_t poll_ns; // back-off of the waiting roles between mbarrier polls (MMA issuer; x8 weight loader, x16 epilogue)
   int late_issue;  // sampler: corner loads of the next chunk issued after (1) or before (0) the proxy fence
 };
 
@@ -155,7 +157,7 @@ __device__ __forceinline__ void item_coords(const TcParams& p, int item, int& b,
 // and the parameters computed from there - instead of three strided 2/4-byte loads per (pixel, tap), which cost ~180 of
 // the ~1500 LSU wavefronts of every (tile, tap) step (ncu, profiles/r01m_dcn_fwd_tc_64x64_raw.txt).
 template <typename T, bool kOmFast, int kTH>
-__global__ void __launch_bounds__(TileCfg<kTH>::NTHREADS) dcn_fwd_tc_kernel(const TcParams p) {
+__global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcParams p) {
   constexpr bool kTF32 = sizeof(T) == 4;
   using Cfg = TileCfg<kTH>;
   constexpr int TILE_PX = Cfg::TILE_PX, SAMPLER_WARPS = Cfg::SAMPLER_WARPS, NS = Cfg::NS, NTHREADS = Cfg::NTHREADS;
@@ -420,7 +422,7 @@ __global__ void __launch_bounds__(TileCfg<kTH>::NTHREADS) dcn_fwd_tc_kernel(cons
     for (int item = item_beg; item < item_end; ++item) {
       const int q0 = (item % p.split) * chunks_per_item;
       for (int q = 0; q < chunks_per_item; ++q) {
-        mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u, 100);
+        mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u, p.poll_ns * 8);
         if (elect_one()) {
           mbar_arrive_expect_tx(bar_fullB + 8 * rc.s, (uint32_t)p.b_stage_bytes);
           bulk_copy_g2s(smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes + A_STAGE_BYTES,
@@ -441,8 +443,8 @@ __global__ void __launch_bounds__(TileCfg<kTH>::NTHREADS) dcn_fwd_tc_kernel(cons
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.acc_cols;
       for (int q = 0; q < chunks_per_item; ++q) {
-        mbar_wait(bar_fullB + 8 * rc.s, rc.ph, 32);
-        mbar_wait(bar_fullA + 8 * rc.s, rc.ph, 32);
+        mbar_wait(bar_fullB + 8 * rc.s, rc.ph, p.poll_ns);
+        mbar_wait(bar_fullA + 8 * rc.s, rc.ph, p.poll_ns);
         tc_fence_after();
         const uint32_t a_addr = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
         const uint64_t adesc = umma_desc_sw128(a_addr);
@@ -471,7 +473,7 @@ __global__ void __launch_bounds__(TileCfg<kTH>::NTHREADS) dcn_fwd_tc_kernel(cons
       const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
       const bool valid = (r < TILE_PX) && (y < p.H) && (x < p.W);
       const int64_t pix = ((int64_t)b * p.H + y) * p.W + x;
-      mbar_wait(bar_tfull + 8 * acc, accph, 1000);
+      mbar_wait(bar_tfull + 8 * acc, accph, p.poll_ns * 16);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + acc * (uint32_t)p.acc_cols;
       if (p.split == 1) {
@@ -702,6 +704,8 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   const int oes = a.om_dtype == CPOLY_BF16 ? 2 : 4;
   p.om_esize = oes;
   p.late_issue = 1;
+  p.poll_ns = 32;    // 16.5 % of the issued instructions are polls of the waiting roles (ncu r02p), but 256 / 1000 ns are slower: 84.0 / 90.2 vs 83.8 us
+  if (const char* e = getenv("CPOLY_TC_POLL")) p.poll_ns = (uint32_t)atoi(e);
   if (const char* e = getenv("CPOLY_TC_LATE")) p.late_issue = atoi(e) != 0;
   const cpoly_tensor4 &o = a.offset, &m = a.mask;
   bool om_fast = o.sc == 1 && o.sw == 32 && o.sh == (int64_t)a.W * 32 && o.sb == (int64_t)a.H * a.W * 32 && m.sc == 1 && m.sw == 32 &&
