@@ -33,39 +33,26 @@ namespace {
 
 using namespace tc;
 
-constexpr int TILE_W = 16;
-constexpr int MMA_M = 128;                         // UMMA M: rows of the A stage (a tile uses the first TILE_PX of them)
+constexpr int TILE_H = 8, TILE_W = 16, TILE_PX = TILE_H * TILE_W;  // 128 = UMMA M
 constexpr int NUM_TAPS = 9;
-constexpr int A_STAGE_BYTES = MMA_M * ROW_BYTES;   // 16 KB
+constexpr int A_STAGE_BYTES = TILE_PX * ROW_BYTES;  // 16 KB
 constexpr int MAX_STAGES = 6;
 constexpr int EPI_WARPS = 4;
 constexpr int SAMPLER_WARP0 = 6;
-// Two tile / sampler geometries (template parameter kTH of the kernel):
-//   kTH = 8: 8 x 16 = 128-pixel tiles, 16 sampler warps, two 64-row passes per thread and step, 704 threads, 80 registers
-//   kTH = 6: 6 x 16 =  96-pixel tiles, 24 sampler warps, ONE pass per thread and step, 960 threads, 64 registers:
-//            36 % more warps per SM for the latency-bound corner gathers; the MMA still has M = 128 (rows 96..127 of the
-//            A stage are never written and their accumulator rows never read)
-template <int kTH> struct TileCfg {
-  static constexpr int TILE_H = kTH, TILE_PX = kTH * TILE_W;
-  static constexpr int SAMPLER_WARPS = kTH == 8 ? 16 : 24;
-  static constexpr int NS = SAMPLER_WARPS * 32;                       // sampler threads
-  static constexpr int NTHREADS = (SAMPLER_WARP0 + SAMPLER_WARPS) * 32;
-  static constexpr int MAXREG = kTH == 8 ? 80 : 64;                   // 704 x 80 / 960 x 64 registers (warp allocations are multiples of 512: 88 does not fit)
-  static constexpr int ROWS_PER_PASS = NS / 8;                        // 8 lanes x 16 B cover one 128-byte row
-  static constexpr int PASSES = TILE_PX / ROWS_PER_PASS;
-  static constexpr int MAX_ITEMS = (NUM_TAPS * TILE_PX + NS - 1) / NS;  // (pixel, tap) parameter items per sampler thread
-  static constexpr int SMEM_PW_OFF = 3072 + NUM_TAPS * TILE_PX * 16;
-  static constexpr int SMEM_STAGE_OFF = ((SMEM_PW_OFF + NUM_TAPS * TILE_PX * 16 + 1023) / 1024) * 1024;
-};
+constexpr int SAMPLER_WARPS = 16;
+constexpr int NS = SAMPLER_WARPS * 32;         // sampler threads
+constexpr int NTHREADS = (SAMPLER_WARP0 + SAMPLER_WARPS) * 32;
+constexpr int ROWS_PER_PASS = NS / 8;          // 8 lanes x 16 B cover one 128-byte row
+constexpr int PASSES = TILE_PX / ROWS_PER_PASS;
+constexpr int MAX_ITEMS = (NUM_TAPS * TILE_PX + NS - 1) / NS;  // (pixel, tap) parameter items per sampler thread
 
 // shared-memory map (dynamic, 1024-byte aligned)
 constexpr int SMEM_BAR_OFF = 0;        // mbarriers + tmem pointer
 constexpr int SMEM_VEC_OFF = 1024;     // scale[256] + bias[256] floats
-constexpr int SMEM_POFF_OFF = 3072;    // corner offsets: NUM_TAPS * TILE_PX * 16 B, then the corner weights (same size): TileCfg
+constexpr int SMEM_POFF_OFF = 3072;    // corner offsets: NUM_TAPS * TILE_PX * 16 B
+constexpr int SMEM_PW_OFF = SMEM_POFF_OFF + NUM_TAPS * TILE_PX * 16;  // corner weights: same size
+constexpr int SMEM_STAGE_OFF = ((SMEM_PW_OFF + NUM_TAPS * TILE_PX * 16 + 1023) / 1024) * 1024;
 constexpr int SMEM_LIMIT = 226 * 1024;  // 227 KB per CTA minus the alignment slack
-#ifndef CPOLY_TC_DEFAULT_TILEH
-#define CPOLY_TC_DEFAULT_TILEH 8
-#endif
 
 struct TcParams {
   const void* x;
@@ -85,8 +72,6 @@ struct TcParams {
   int stages, b_stage_bytes, stage_bytes;
   int acc_cols, tmem_cols;
   int om_esize;    // element size of the fused 32-channel offset/mask tensor (kOmFast kernels)
-  int tile_h;      // 8 or 6 (TileCfg)
-  uint32_t poll_ns; // back-off of the waiting roles between mbarrier polls (MMA issuer; x8 weight loader, x16 epilogue)
   int late_issue;  // sampler: corner loads of the next chunk issued after (1) or before (0) the proxy fence
 };
 
@@ -146,7 +131,7 @@ __device__ __forceinline__ void item_coords(const TcParams& p, int item, int& b,
   b = tile / tiles_per_img;
   const int trem = tile - b * tiles_per_img;
   const int tyi = trem / p.tiles_x;
-  ty0 = tyi * p.tile_h;
+  ty0 = tyi * TILE_H;
   tx0 = (trem - tyi * p.tiles_x) * TILE_W;
 }
 
@@ -156,13 +141,9 @@ __device__ __forceinline__ void item_coords(const TcParams& p, int item, int& b,
 // coalesced 16-byte loads one item ahead (8 registers), transposed through shared memory (odd word pitch: conflict-free)
 // and the parameters computed from there - instead of three strided 2/4-byte loads per (pixel, tap), which cost ~180 of
 // the ~1500 LSU wavefronts of every (tile, tap) step (ncu, profiles/r01m_dcn_fwd_tc_64x64_raw.txt).
-template <typename T, bool kOmFast, int kTH>
-__global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcParams p) {
+template <typename T, bool kOmFast>
+__global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   constexpr bool kTF32 = sizeof(T) == 4;
-  using Cfg = TileCfg<kTH>;
-  constexpr int TILE_PX = Cfg::TILE_PX, SAMPLER_WARPS = Cfg::SAMPLER_WARPS, NS = Cfg::NS, NTHREADS = Cfg::NTHREADS;
-  constexpr int ROWS_PER_PASS = Cfg::ROWS_PER_PASS, PASSES = Cfg::PASSES, MAX_ITEMS = Cfg::MAX_ITEMS;
-  constexpr int SMEM_PW_OFF = Cfg::SMEM_PW_OFF, SMEM_STAGE_OFF = Cfg::SMEM_STAGE_OFF;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operand tiles need 1024-byte alignment: align the window ourselves (+1 KB is requested)
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -236,7 +217,7 @@ __global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcPara
 #pragma unroll
         for (int i = 0; i < MAX_ITEMS; ++i) {
           const int e = st + i * NS;
-          const int k = tap0 + e / TILE_PX, r = e % TILE_PX;
+          const int k = tap0 + (e >> 7), r = e & (TILE_PX - 1);
           const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
           raw_dy[i] = raw_dx[i] = raw_m[i] = 0.f;
           if (e < n_param && y < p.H && x < p.W) {
@@ -274,7 +255,7 @@ __global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcPara
         const int e = st + i * NS;
         raw_dy[i] = raw_dx[i] = raw_m[i] = 0.f;
         if (e < n_param) {
-          const int k = tap0 + e / TILE_PX, r = e % TILE_PX;
+          const int k = tap0 + (e >> 7), r = e & (TILE_PX - 1);
           const uint32_t a = pw_s + (uint32_t)r * pitch;
           uint32_t u0, u1;
           if (p.om_esize == 4) {
@@ -307,12 +288,9 @@ __global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcPara
       for (int i = 0; i < MAX_ITEMS; ++i) {
         const int e = st + i * NS;
         if (e >= n_param) continue;
-        const int kl = e / TILE_PX, k = tap0 + kl, r = e % TILE_PX;
+        const int kl = e >> 7, k = tap0 + kl, r = e & (TILE_PX - 1);
         const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
         uint4 po = make_uint4(0u, 0u, 0u, 0u), pw = make_uint4(0u, 0u, 0u, 0u);  // dead corner: offset 0, weight 0
-        bool pk_alive = false;
-        int pk_y0c = 0, pk_x0c = 0;
-        uint32_t pk_flags = 0u;
         if (y < p.H && x < p.W) {
           const float m = p.mask_is_logit ? sigmoidf_accurate(raw_m[i]) : raw_m[i];
           const int ki = k / 3;
@@ -329,25 +307,10 @@ __global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcPara
             if (vy0 && vx1) { po.y = o00 + pixb;        pw.y = Blend<T>::weight(hy * lx * m); }
             if (vy1 && vx0) { po.z = o00 + rowb;        pw.z = Blend<T>::weight(ly * hx * m); }
             if (vy1 && vx1) { po.w = o00 + rowb + pixb; pw.w = Blend<T>::weight(ly * lx * m); }
-            pk_alive = true;
-            pk_y0c = vy0 ? y0 : 0; pk_x0c = vx0 ? x0 : 0;                       // y0, x0 >= -1 here
-            pk_flags = ((vx0 && vx1) ? 1u : 0u) | ((vy0 && vy1) ? 2u : 0u);       // clamped x1 != x0 / y1 != y0
           }
         }
-        if constexpr (kTF32) {
-          sts16(poff_s + (uint32_t)(kl * TILE_PX + r) * 16u, po);
-          sts16(pw_s + (uint32_t)(kl * TILE_PX + r) * 16u, pw);
-        } else {
-          // bf16: ONE 16-byte entry per (pixel, tap) - every sampler thread reads it once per chunk, and a 128-bit shared
-          // load costs a wavefront per quarter warp however few distinct addresses it has (256 -> 128 wavefronts per step).
-          // {byte offset of the corner at (clamp y0, clamp x0) | dx flag | dy flag << 1, (w0, w1), (w2, w3) as bf16 pairs}:
-          // the other corners are +pixel / +row when the clamped coordinates differ; a corner outside the image has weight
-          // 0 and reads an in-image neighbour instead.
-          uint32_t rec = (uint32_t)img_base * (uint32_t)sizeof(T);
-          if (pk_alive) rec = (rec + (uint32_t)(pk_y0c * p.W + pk_x0c) * ((uint32_t)p.Cin * (uint32_t)sizeof(T))) | pk_flags;
-          sts16(poff_s + (uint32_t)(kl * TILE_PX + r) * 16u,
-                make_uint4(rec, (pw.x & 0xffffu) | (pw.y << 16), (pw.z & 0xffffu) | (pw.w << 16), 0u));
-        }
+        sts16(poff_s + (uint32_t)(kl * TILE_PX + r) * 16u, po);
+        sts16(pw_s + (uint32_t)(kl * TILE_PX + r) * 16u, pw);
       }
       named_bar_sync(1, NS);
       if (item + 1 < item_end) fetch_raw(item + 1);
@@ -356,27 +319,14 @@ __global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcPara
       // alternating between a load phase and a blend phase.
       uint4 c[PASSES][4], pw[PASSES];
       const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x);
-      const uint32_t s_pixb = (uint32_t)p.Cin * (uint32_t)sizeof(T), s_rowb = (uint32_t)p.W * s_pixb;
       auto issue = [&](uint32_t pidx, uint32_t cbyte, int pass) {   // params + corner loads of one (chunk, pass)
         const uint32_t idx = pidx + (uint32_t)(pass * ROWS_PER_PASS) * 16u;
-        if constexpr (kTF32) {
-          const uint4 po = lds16(poff_s + idx);   // BYTE offsets of the four corner vectors
-          pw[pass] = lds16(pw_s + idx);
-          c[pass][0] = ldg16(xb + (po.x + cbyte));
-          c[pass][1] = ldg16(xb + (po.y + cbyte));
-          c[pass][2] = ldg16(xb + (po.z + cbyte));
-          c[pass][3] = ldg16(xb + (po.w + cbyte));
-        } else {
-          const uint4 pr = lds16(poff_s + idx);   // packed entry, see the parameter stores above
-          const uint32_t b0 = (pr.x & ~15u) + cbyte;
-          const uint32_t dxo = (pr.x & 1u) ? s_pixb : 0u, dyo = (pr.x & 2u) ? s_rowb : 0u;
-          c[pass][0] = ldg16(xb + b0);
-          c[pass][1] = ldg16(xb + (b0 + dxo));
-          c[pass][2] = ldg16(xb + (b0 + dyo));
-          c[pass][3] = ldg16(xb + (b0 + dyo + dxo));
-          pw[pass] = make_uint4(__byte_perm(pr.y, 0u, 0x1010), __byte_perm(pr.y, 0u, 0x3232), __byte_perm(pr.z, 0u, 0x1010),
-                                __byte_perm(pr.z, 0u, 0x3232));   // (w, w) bf16 pairs for the packed FMAs
-        }
+        const uint4 po = lds16(poff_s + idx);   // BYTE offsets of the four corner vectors
+        pw[pass] = lds16(pw_s + idx);
+        c[pass][0] = ldg16(xb + (po.x + cbyte));
+        c[pass][1] = ldg16(xb + (po.y + cbyte));
+        c[pass][2] = ldg16(xb + (po.z + cbyte));
+        c[pass][3] = ldg16(xb + (po.w + cbyte));
       };
       // (tap, channel chunk) cursor of the NEXT chunk to issue: parameter row index and channel byte offset
       const uint32_t cbyte0 = (uint32_t)(cg * 16);
@@ -422,7 +372,7 @@ __global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcPara
     for (int item = item_beg; item < item_end; ++item) {
       const int q0 = (item % p.split) * chunks_per_item;
       for (int q = 0; q < chunks_per_item; ++q) {
-        mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u, p.poll_ns * 8);
+        mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u, 100);
         if (elect_one()) {
           mbar_arrive_expect_tx(bar_fullB + 8 * rc.s, (uint32_t)p.b_stage_bytes);
           bulk_copy_g2s(smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes + A_STAGE_BYTES,
@@ -434,7 +384,7 @@ __global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcPara
     }
   } else if (warp == 5) {
     // =========================================================================== MMA issuer
-    const uint32_t idesc = umma_idesc(kTF32, MMA_M, p.Cout);
+    const uint32_t idesc = umma_idesc(kTF32, TILE_PX, p.Cout);
     RingCursor rc;
     uint32_t tcount = 0;
     for (int item = item_beg; item < item_end; ++item, ++tcount) {
@@ -443,8 +393,8 @@ __global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcPara
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.acc_cols;
       for (int q = 0; q < chunks_per_item; ++q) {
-        mbar_wait(bar_fullB + 8 * rc.s, rc.ph, p.poll_ns);
-        mbar_wait(bar_fullA + 8 * rc.s, rc.ph, p.poll_ns);
+        mbar_wait(bar_fullB + 8 * rc.s, rc.ph, 32);
+        mbar_wait(bar_fullA + 8 * rc.s, rc.ph, 32);
         tc_fence_after();
         const uint32_t a_addr = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
         const uint64_t adesc = umma_desc_sw128(a_addr);
@@ -471,9 +421,9 @@ __global__ void __maxnreg__(TileCfg<kTH>::MAXREG) dcn_fwd_tc_kernel(const TcPara
       item_coords(p, item, b, ty0, tx0, tap0);
       const int r = warp * 32 + lane;
       const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
-      const bool valid = (r < TILE_PX) && (y < p.H) && (x < p.W);
+      const bool valid = (y < p.H) && (x < p.W);
       const int64_t pix = ((int64_t)b * p.H + y) * p.W + x;
-      mbar_wait(bar_tfull + 8 * acc, accph, p.poll_ns * 16);
+      mbar_wait(bar_tfull + 8 * acc, accph, 1000);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + acc * (uint32_t)p.acc_cols;
       if (p.split == 1) {
@@ -618,15 +568,8 @@ bool dcn_tc_eligible(const cpoly_dcn_fwd_args& a) {
   return true;
 }
 
-// Tile geometry of the forward kernel (TileCfg): CPOLY_TC_TILEH=6 selects the 96-pixel / 24-sampler-warp variant.
-static int tile_h_choice() {
-  if (const char* e = getenv("CPOLY_TC_TILEH")) return atoi(e) == 6 ? 6 : 8;
-  return CPOLY_TC_DEFAULT_TILEH;
-}
-
 size_t dcn_tc_forward_workspace(const cpoly_dcn_fwd_args& a) {
-  const int th = tile_h_choice();
-  const int tiles = a.B * ((a.W + TILE_W - 1) / TILE_W) * ((a.H + th - 1) / th);
+  const int tiles = a.B * ((a.W + TILE_W - 1) / TILE_W) * ((a.H + TILE_H - 1) / TILE_H);
   return split_workspace(choose_split(tiles), (int64_t)a.B * a.H * a.W, a.Cout) + 256;
 }
 
@@ -664,12 +607,8 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   p.y = a.y.ptr;
   p.B = a.B; p.Cin = a.Cin; p.Cout = a.Cout; p.H = a.H; p.W = a.W;
   p.om_dtype = a.om_dtype; p.mask_is_logit = a.mask_is_logit; p.relu = a.relu;
-  const int th = tile_h_choice();
-  p.tile_h = th;
-  const int stage_off = th == 8 ? TileCfg<8>::SMEM_STAGE_OFF : TileCfg<6>::SMEM_STAGE_OFF;
-  const int nthreads = th == 8 ? TileCfg<8>::NTHREADS : TileCfg<6>::NTHREADS;
   p.tiles_x = (a.W + TILE_W - 1) / TILE_W;
-  p.tiles_y = (a.H + th - 1) / th;
+  p.tiles_y = (a.H + TILE_H - 1) / TILE_H;
   p.num_tiles = a.B * p.tiles_x * p.tiles_y;
   if (p.num_tiles == 0) return CPOLY_OK;
   const int64_t npix = (int64_t)a.B * a.H * a.W;
@@ -683,7 +622,7 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   p.nchunk = a.Cin / (ROW_BYTES / esize);
   p.b_stage_bytes = a.Cout * ROW_BYTES;
   p.stage_bytes = A_STAGE_BYTES + p.b_stage_bytes;
-  int stages = (SMEM_LIMIT - stage_off) / p.stage_bytes;
+  int stages = (SMEM_LIMIT - SMEM_STAGE_OFF) / p.stage_bytes;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   // 4 stages are as fast as 6 (r02 sweep: 2 / 3 / 4 / 6 stages = 79.8 / 77.9 / 78.0 / 79.9 us on 64->64 @256x512) and
   // leave 48 KB more of the SM's 256 KB to L1, which is what the corner gathers live on
@@ -694,7 +633,7 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   p.stages = stages;
   p.acc_cols = a.Cout;
   p.tmem_cols = pow2_at_least(2 * a.Cout);
-  const int smem_bytes = stage_off + stages * p.stage_bytes + 1024;  // +1 KB alignment slack
+  const int smem_bytes = SMEM_STAGE_OFF + stages * p.stage_bytes + 1024;  // +1 KB alignment slack
 
   int dev = 0, sms = 0;
   CPOLY_CUDA_OK(cudaGetDevice(&dev));
@@ -704,29 +643,22 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   const int oes = a.om_dtype == CPOLY_BF16 ? 2 : 4;
   p.om_esize = oes;
   p.late_issue = 1;
-  p.poll_ns = 32;    // 16.5 % of the issued instructions are polls of the waiting roles (ncu r02p), but 256 / 1000 ns are slower: 84.0 / 90.2 vs 83.8 us
-  if (const char* e = getenv("CPOLY_TC_POLL")) p.poll_ns = (uint32_t)atoi(e);
   if (const char* e = getenv("CPOLY_TC_LATE")) p.late_issue = atoi(e) != 0;
   const cpoly_tensor4 &o = a.offset, &m = a.mask;
   bool om_fast = o.sc == 1 && o.sw == 32 && o.sh == (int64_t)a.W * 32 && o.sb == (int64_t)a.H * a.W * 32 && m.sc == 1 && m.sw == 32 &&
                  m.sh == o.sh && m.sb == o.sb && reinterpret_cast<const uint8_t*>(m.ptr) == reinterpret_cast<const uint8_t*>(o.ptr) + 18 * oes &&
                  (reinterpret_cast<uintptr_t>(o.ptr) & 15) == 0 && (int64_t)a.B * a.H * a.W < (1LL << 26);
   if (const char* e = getenv("CPOLY_TC_OM")) om_fast = om_fast && atoi(e) != 0;   // profiling knob: CPOLY_TC_OM=0 keeps the strided loads
-#define CPOLY_LAUNCH_FWD(TT, FAST, TH)                                                                                            \
-  do {                                                                                                                            \
-    CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_fwd_tc_kernel<TT, FAST, TH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes)); \
-    dcn_fwd_tc_kernel<TT, FAST, TH><<<grid, nthreads, smem_bytes, stream>>>(p);                                                   \
-  } while (0)
-#define CPOLY_LAUNCH_FWD2(TT, FAST)                                       \
-  do {                                                                    \
-    if (th == 8) CPOLY_LAUNCH_FWD(TT, FAST, 8); else CPOLY_LAUNCH_FWD(TT, FAST, 6); \
+#define CPOLY_LAUNCH_FWD(TT, FAST)                                                                                            \
+  do {                                                                                                                        \
+    CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_fwd_tc_kernel<TT, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes)); \
+    dcn_fwd_tc_kernel<TT, FAST><<<grid, NTHREADS, smem_bytes, stream>>>(p);                                                   \
   } while (0)
   if (a.dtype == CPOLY_BF16) {
-    if (om_fast) CPOLY_LAUNCH_FWD2(__nv_bfloat16, true); else CPOLY_LAUNCH_FWD2(__nv_bfloat16, false);
+    if (om_fast) CPOLY_LAUNCH_FWD(__nv_bfloat16, true); else CPOLY_LAUNCH_FWD(__nv_bfloat16, false);
   } else {
-    if (om_fast) CPOLY_LAUNCH_FWD2(float, true); else CPOLY_LAUNCH_FWD2(float, false);
+    if (om_fast) CPOLY_LAUNCH_FWD(float, true); else CPOLY_LAUNCH_FWD(float, false);
   }
-#undef CPOLY_LAUNCH_FWD2
 #undef CPOLY_LAUNCH_FWD
   if (int rc = check_launch("dcn_fwd_tc_kernel")) return rc;
   if (p.split > 1) return dcn_tc_launch_combine(p.partial, a.y.ptr, a.dtype, a.out_scale, a.bias, npix, a.Cout, p.split, a.relu, stream);
