@@ -19,10 +19,12 @@
 //     1. candidate source tiles = tiles of the image whose box meets D; candidate units likewise (ordered block
 //        compactions): with ordinary offsets that is D's own 36 units plus the rim of its neighbours, with far
 //        offsets (|d| of tens of pixels) any tile of the image - no halo limit, no spill list.
-//     2. pass 1 counts, per warp and destination pixel, the corners that land in D (the 32 lanes of a warp hold 32
-//        source pixels of one unit; __match_any_sync groups the lanes that hit the same destination pixel);
-//        a scan gives every (warp, pixel) its slot range; pass 2 repeats the walk and writes (source row, m*w) into
-//        its slot: position = base[warp][pixel] + rank among the matching lanes - a function of the DATA only.
+//     2. pass 1 counts, per (warp, corner, destination pixel), the corners that land in D: the 32 lanes of a warp hold
+//        32 source pixels of one unit, ONE __match_any_sync per unit on the base corner groups the lanes, and the
+//        four corners of a lane go to four separate slot counters (corners of one base pixel are distinct pixels),
+//        so counters are warp-private and need no atomics.  A scan gives every (warp, corner, pixel) its slot range;
+//        pass 2 repeats the walk and writes (source row, m*w) into its slot: position = base + rank among the
+//        matching lanes - a function of the DATA only.
 //     3. eight lanes per destination pixel walk its slot range in order, 16 bytes of gcol per lane and entry,
 //        fp32 accumulation, one store.
 //     A destination tile that receives more than CAP contributions (offset fields that collapse onto one spot) is
