@@ -36,7 +36,7 @@ using namespace tc;
 constexpr int TILE_H = 8, TILE_W = 16, TILE_PX = TILE_H * TILE_W;  // 128 = UMMA M
 constexpr int NUM_TAPS = 9;
 constexpr int A_STAGE_BYTES = TILE_PX * ROW_BYTES;  // 16 KB
-constexpr int MAX_STAGES = 6;
+constexpr int MAX_A_STAGES = 8, MAX_B_STAGES = 4;
 constexpr int EPI_WARPS = 4;
 constexpr int SAMPLER_WARP0 = 6;
 constexpr int SAMPLER_WARPS = 16;
@@ -44,14 +44,19 @@ constexpr int NS = SAMPLER_WARPS * 32;         // sampler threads
 constexpr int NTHREADS = (SAMPLER_WARP0 + SAMPLER_WARPS) * 32;
 constexpr int ROWS_PER_PASS = NS / 8;          // 8 lanes x 16 B cover one 128-byte row
 constexpr int PASSES = TILE_PX / ROWS_PER_PASS;
-constexpr int MAX_ITEMS = (NUM_TAPS * TILE_PX + NS - 1) / NS;  // (pixel, tap) parameter items per sampler thread
+constexpr int GROUPS = 4;                      // sampler groups: group g owns the steps t = g (mod GROUPS)
+constexpr int GROUP_THREADS = NS / GROUPS;     // 128
+constexpr int GROUP_ROWS = GROUP_THREADS / 8;  // 16 rows of the tile per pass (8 lanes x 16 B per row)
+constexpr int GROUP_PASSES = TILE_PX / GROUP_ROWS;   // 8 passes per step
+constexpr int PASS_PAR = GROUP_ROWS * 16;      // parameter bytes between two passes
+constexpr int PARAM_THREADS = EPI_WARPS * 32;  // warps 0-3: thread r owns pixel r of the tile (= TMEM lane r)
 
 // shared-memory map (dynamic, 1024-byte aligned)
 constexpr int SMEM_BAR_OFF = 0;        // mbarriers + tmem pointer
 constexpr int SMEM_VEC_OFF = 1024;     // scale[256] + bias[256] floats
-constexpr int SMEM_POFF_OFF = 3072;    // corner offsets: NUM_TAPS * TILE_PX * 16 B
-constexpr int SMEM_PW_OFF = SMEM_POFF_OFF + NUM_TAPS * TILE_PX * 16;  // corner weights: same size
-constexpr int SMEM_STAGE_OFF = ((SMEM_PW_OFF + NUM_TAPS * TILE_PX * 16 + 1023) / 1024) * 1024;
+constexpr int SMEM_OM_OFF = 3072;      // staged offset/mask tile of the next item: 128 pixels x (128 + 16) bytes
+constexpr int OM_PITCH_F32 = 144, OM_PITCH_BF16 = 80;   // 16-byte aligned rows; 8 consecutive rows cover all 32 banks
+constexpr int SMEM_PAR_OFF = SMEM_OM_OFF + TILE_PX * OM_PITCH_F32;   // two parameter buffers of taps_per_item * 128 * 32 B
 constexpr int SMEM_LIMIT = 226 * 1024;  // 227 KB per CTA minus the alignment slack
 
 struct TcParams {
@@ -69,10 +74,13 @@ struct TcParams {
   int tiles_x, tiles_y, num_tiles, num_items;
   int split, taps_per_item;
   int nchunk;      // channel chunks per tap
-  int stages, b_stage_bytes, stage_bytes;
+  int a_stages, b_stages, b_stage_bytes;   // A ring (16 KB tiles, >= GROUPS stages) and the independent weight ring
+  int b_off;       // byte offset of the weight ring (1024-aligned, after the A ring)
   int acc_cols, tmem_cols;
   int om_esize;    // element size of the fused 32-channel offset/mask tensor (kOmFast kernels)
-  int late_issue;  // sampler: corner loads of the next chunk issued after (1) or before (0) the proxy fence
+  int pbuf_bytes;  // one parameter buffer: corner offsets (taps_per_item * 128 * 16 B) then corner weights (same size)
+  int stage_off;   // byte offset of the operand ring (1024-aligned, after the parameter buffers)
+  long long* trace;  // profiling only (CPOLY_TC_TRACE): clock64 event log of CTA 0, 5 roles x 4096 entries
 };
 
 // ---- blend of the four corner vectors (16 B each) into one 16-B piece of the A row ----------------
@@ -148,28 +156,39 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   // SWIZZLE_128B operand tiles need 1024-byte alignment: align the window ourselves (+1 KB is requested)
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const uint32_t smem_base = smem_u32(smem);
-  const uint32_t bar_fullA = smem_base + SMEM_BAR_OFF;                 // [MAX_STAGES]
-  const uint32_t bar_fullB = bar_fullA + 8 * MAX_STAGES;               // [MAX_STAGES]
-  const uint32_t bar_empty = bar_fullB + 8 * MAX_STAGES;               // [MAX_STAGES]
-  const uint32_t bar_tfull = bar_empty + 8 * MAX_STAGES;               // [2]
+  const uint32_t bar_fullA = smem_base + SMEM_BAR_OFF;                 // [MAX_A_STAGES]
+  const uint32_t bar_empty = bar_fullA + 8 * MAX_A_STAGES;             // [MAX_A_STAGES] A stage consumed
+  const uint32_t bar_fullB = bar_empty + 8 * MAX_A_STAGES;             // [MAX_B_STAGES]
+  const uint32_t bar_emptyB = bar_fullB + 8 * MAX_B_STAGES;            // [MAX_B_STAGES] weight stage consumed
+  const uint32_t bar_tfull = bar_emptyB + 8 * MAX_B_STAGES;            // [2]
   const uint32_t bar_tempty = bar_tfull + 16;                          // [2]
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SMEM_BAR_OFF + 8 * (3 * MAX_STAGES + 4));
+  const uint32_t bar_pfull = bar_tempty + 16;                          // [2] parameter buffer written (PARAM_THREADS arrivals)
+  const uint32_t bar_pempty = bar_pfull + 16;                          // [2] parameter buffer released (one arrival per sampler warp)
+  const uint32_t bar_first = bar_pempty + 16;                          // [NUM_TAPS] first item only: tap k written (PARAM_THREADS arrivals)
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + SMEM_BAR_OFF + 8 * (2 * MAX_A_STAGES + 2 * MAX_B_STAGES + 8 + NUM_TAPS));
   float* scale_s = reinterpret_cast<float*>(smem + SMEM_VEC_OFF);
   float* bias_s = scale_s + 256;
-  const uint32_t poff_s = smem_base + SMEM_POFF_OFF, pw_s = smem_base + SMEM_PW_OFF;
+  const uint32_t om_s = smem_base + SMEM_OM_OFF, par_s = smem_base + SMEM_PAR_OFF;
+  const uint32_t pw_off = (uint32_t)p.pbuf_bytes >> 1;   // corner weights follow the corner offsets inside a buffer
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   // ---- one-time setup
   if (warp == 4 && lane == 0) {
-    for (int s = 0; s < MAX_STAGES; ++s) {
-      mbar_init(bar_fullA + 8 * s, SAMPLER_WARPS);
-      mbar_init(bar_fullB + 8 * s, 1);
+    for (int s = 0; s < MAX_A_STAGES; ++s) {
+      mbar_init(bar_fullA + 8 * s, SAMPLER_WARPS / GROUPS);
       mbar_init(bar_empty + 8 * s, 1);
     }
+    for (int s = 0; s < MAX_B_STAGES; ++s) {
+      mbar_init(bar_fullB + 8 * s, 1);
+      mbar_init(bar_emptyB + 8 * s, 1);
+    }
+    for (int k = 0; k < NUM_TAPS; ++k) mbar_init(bar_first + 8 * k, PARAM_THREADS);
     for (int a = 0; a < 2; ++a) {
       mbar_init(bar_tfull + 8 * a, 1);
       mbar_init(bar_tempty + 8 * a, EPI_WARPS * 32);
+      mbar_init(bar_pfull + 8 * a, PARAM_THREADS);
+      mbar_init(bar_pempty + 8 * a, (uint32_t)(p.taps_per_item * p.nchunk) * (SAMPLER_WARPS / GROUPS));
     }
     fence_mbar_init();
   }
@@ -183,186 +202,93 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   const int chunks_per_item = p.taps_per_item * p.nchunk;
-  const uint32_t nstages = (uint32_t)p.stages;
+  const uint32_t nstages = (uint32_t)p.a_stages, nbstages = (uint32_t)p.b_stages;
   // A CTA walks a CONTIGUOUS range of items: consecutive tiles of a tile row share 43 % of their bilinear footprint
   // (and the tap groups of one tile all of it), so the halo of the next item is already in this SM's L1 - with the
   // round-robin deal of round 1 every item started cold (L1 sector hit rate 83 %, long-scoreboard stalls dominant).
   const int item_beg = (int)(((long long)p.num_items * blockIdx.x) / gridDim.x);
   const int item_end = (int)(((long long)p.num_items * (blockIdx.x + 1)) / gridDim.x);
 
+  const int n_items = item_end - item_beg;
+  int tr_n = 0;
+  auto tr = [&](int role, int tag) {
+    if (p.trace && blockIdx.x == 0 && lane == 0 && tr_n < 2048) { p.trace[role * 4096 + 2 * tr_n] = clock64(); p.trace[role * 4096 + 2 * tr_n + 1] = tag; ++tr_n; }
+  };
+
   if (warp >= SAMPLER_WARP0) {
     // =========================================================================== samplers
+    // The samplers only gather and blend; the per-(pixel, tap) parameters of item j are written by warps 0-3 into
+    // parameter buffer j & 1 while item j-1 is being sampled (bar_pfull / bar_pempty; the CTA's first item is handed
+    // over tap by tap through bar_first so that sampling starts after one tap's worth of parameter math).
+    // The 16 warps form GROUPS = 4 groups of 4; group g builds the WHOLE A tile of the steps t = g (mod 4) of the CTA's
+    // step sequence (step = one 128-byte channel chunk of one tap of one item) in 8 passes of 16 rows.  A warp pays the
+    // per-step costs (stage wait, cursor update, the proxy fence that drains its loads, arrives) once per 8 passes, the
+    // pass loop is straight-line code with immediate offsets, and the groups run out of phase instead of hitting the
+    // LSU in lockstep.  One rolling software pipeline runs across all passes, steps and items of a group: two passes
+    // (8 x 16 B per thread) are in flight while the previous one is blended.
     const int st = threadIdx.x - SAMPLER_WARP0 * 32;
-    const int row_in_pass = st >> 3, cg = st & 7;
-    const int n_param = p.taps_per_item * TILE_PX;
-    float raw_dy[MAX_ITEMS], raw_dx[MAX_ITEMS], raw_m[MAX_ITEMS];
-    uint4 omv[2];   // kOmFast: this thread's 16-byte pieces of the NEXT item's offset/mask tile
-    // raw offsets / mask of one item -> registers (issued one item ahead so the latency hides behind sampling)
-    auto fetch_raw = [&](int item) {
-      int b, ty0, tx0, tap0;
-      item_coords(p, item, b, ty0, tx0, tap0);
-      if constexpr (kOmFast) {
-        const int ppp = p.om_esize * 2;                  // 16-byte pieces per pixel: 32 channels * esize / 16
-        const uint8_t* base = reinterpret_cast<const uint8_t*>(p.offset.ptr);
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const int idx = st + i * NS;
-          const int r = idx / ppp, j = idx - r * ppp;
-          const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
-          omv[i] = make_uint4(0u, 0u, 0u, 0u);
-          if (r < TILE_PX && y < p.H && x < p.W)
-            omv[i] = ldg16(base + ((size_t)((b * p.H + y) * p.W + x) * 32) * p.om_esize + j * 16);
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < MAX_ITEMS; ++i) {
-          const int e = st + i * NS;
-          const int k = tap0 + (e >> 7), r = e & (TILE_PX - 1);
-          const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
-          raw_dy[i] = raw_dx[i] = raw_m[i] = 0.f;
-          if (e < n_param && y < p.H && x < p.W) {
-            const int64_t opix = (int64_t)b * p.offset.sb + (int64_t)y * p.offset.sh + (int64_t)x * p.offset.sw;
-            raw_dy[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k) * p.offset.sc, p.om_dtype);
-            raw_dx[i] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k + 1) * p.offset.sc, p.om_dtype);
-            raw_m[i] = ld_dyn(p.mask.ptr, (int64_t)b * p.mask.sb + (int64_t)k * p.mask.sc + (int64_t)y * p.mask.sh + (int64_t)x * p.mask.sw, p.om_dtype);
-            if (p.offset_bias) { raw_dy[i] += __ldg(p.offset_bias + 2 * k); raw_dx[i] += __ldg(p.offset_bias + 2 * k + 1); }
-            if (p.mask_bias) raw_m[i] += __ldg(p.mask_bias + k);
-          }
-        }
+    const int grp = st / GROUP_THREADS, gt = st - grp * GROUP_THREADS;
+    const int row0 = gt >> 3, cg = gt & 7;
+    const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x);
+    const uint32_t cbyte0 = (uint32_t)(cg * 16);
+    const int total = n_items * chunks_per_item;
+    const uint32_t st_off = (uint32_t)(row0 * ROW_BYTES + ((cg ^ (row0 & 7)) << 4));   // + pass * 16 rows * 128 B
+    const uint32_t par_row = par_s + (uint32_t)row0 * 16u;
+    uint4 c[2][4], pw[2];
+    // cursor: (item, tap, chunk) of a step; `par` / `cbyte` are what the passes need
+    struct Cur { int t, j, kl, cc; uint32_t par, cbyte; };
+    auto seek = [&](Cur& u, int adv) {            // move u by `adv` steps (adv <= GROUPS), waiting for the parameters it lands on
+      u.t += adv;
+      if (u.t >= total) return;
+      u.cc += adv;
+      while (u.cc >= p.nchunk) { u.cc -= p.nchunk; ++u.kl; }
+      while (u.kl >= p.taps_per_item) {           // every item's hand-over is observed in order (phase parity stays unambiguous)
+        if (u.j == 0) mbar_wait(bar_pfull, 0u);   // (the first item was consumed through bar_first)
+        u.kl -= p.taps_per_item; ++u.j;
+        mbar_wait(bar_pfull + 8 * (u.j & 1), (uint32_t)(u.j >> 1) & 1u);
       }
+      if (u.j == 0) mbar_wait(bar_first + 8 * u.kl, 0u);
+      u.par = par_row + (uint32_t)(u.j & 1) * (uint32_t)p.pbuf_bytes + (uint32_t)(u.kl * TILE_PX) * 16u;
+      u.cbyte = cbyte0 + (uint32_t)u.cc * ROW_BYTES;
     };
-    // kOmFast: registers -> shared tile [pixel][32 channels] with an odd word pitch (33 words fp32 / 17 words bf16), then
-    // every thread picks the (dy, dx, mask) of its own (pixel, tap) entries.  The tile aliases the weight-parameter
-    // array, which is dead between the first barrier of an item and the parameter stores.
-    auto stage_raw = [&](int tap0) {
-      const int ppp = p.om_esize * 2;
-      const uint32_t pitch = p.om_esize == 4 ? 132u : 68u;
-#pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        const int idx = st + i * NS;
-        const int r = idx / ppp, j = idx - r * ppp;
-        if (r < TILE_PX) {
-          const uint32_t a = pw_s + (uint32_t)r * pitch + (uint32_t)j * 16u;
-          asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(omv[i].x) : "memory");
-          asm volatile("st.shared.b32 [%0], %1;" ::"r"(a + 4u), "r"(omv[i].y) : "memory");
-          asm volatile("st.shared.b32 [%0], %1;" ::"r"(a + 8u), "r"(omv[i].z) : "memory");
-          asm volatile("st.shared.b32 [%0], %1;" ::"r"(a + 12u), "r"(omv[i].w) : "memory");
-        }
-      }
-      named_bar_sync(1, NS);
-#pragma unroll
-      for (int i = 0; i < MAX_ITEMS; ++i) {
-        const int e = st + i * NS;
-        raw_dy[i] = raw_dx[i] = raw_m[i] = 0.f;
-        if (e < n_param) {
-          const int k = tap0 + (e >> 7), r = e & (TILE_PX - 1);
-          const uint32_t a = pw_s + (uint32_t)r * pitch;
-          uint32_t u0, u1;
-          if (p.om_esize == 4) {
-            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u0) : "r"(a + (uint32_t)(8 * k)));
-            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u1) : "r"(a + (uint32_t)(8 * k + 4)));
-            raw_dy[i] = __uint_as_float(u0); raw_dx[i] = __uint_as_float(u1);
-            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u0) : "r"(a + (uint32_t)(72 + 4 * k)));
-            raw_m[i] = __uint_as_float(u0);
-          } else {
-            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(u0) : "r"(a + (uint32_t)(4 * k)));          // (dy, dx) bf16 pair
-            raw_dy[i] = __uint_as_float(u0 << 16); raw_dx[i] = __uint_as_float(u0 & 0xffff0000u);
-            asm volatile("ld.shared.u16 %0, [%1];" : "=r"(u1) : "r"(a + (uint32_t)(36 + 2 * k)));
-            raw_m[i] = __uint_as_float(u1 << 16);
-          }
-          if (p.offset_bias) { raw_dy[i] += __ldg(p.offset_bias + 2 * k); raw_dx[i] += __ldg(p.offset_bias + 2 * k + 1); }
-          if (p.mask_bias) raw_m[i] += __ldg(p.mask_bias + k);
-        }
-      }
-      named_bar_sync(1, NS);   // the tile is dead: its bytes become weight parameters again
+    auto issue = [&](uint4 (&cb)[4], uint4& pwb, uint32_t par, uint32_t cbyte) {   // parameters + corner loads of one pass
+      const uint4 po = lds16(par);                // BYTE offsets of the four corner vectors
+      pwb = lds16(par + pw_off);
+      cb[0] = ldg16(xb + (po.x + cbyte));
+      cb[1] = ldg16(xb + (po.y + cbyte));
+      cb[2] = ldg16(xb + (po.z + cbyte));
+      cb[3] = ldg16(xb + (po.w + cbyte));
     };
-    RingCursor rc;
-    if (item_beg < item_end) fetch_raw(item_beg);
-    for (int item = item_beg; item < item_end; ++item) {
-      int b, ty0, tx0, tap0;
-      item_coords(p, item, b, ty0, tx0, tap0);
-      const int img_base = b * p.H * p.W * p.Cin;   // element offset; bytes < 2^32 (checked on the host)
-      named_bar_sync(1, NS);  // everyone finished reading the previous item's params
-      if constexpr (kOmFast) stage_raw(tap0);
+    Cur cur{-1, 0, 0, -1, 0u, 0u};
+    seek(cur, grp + 1);                           // the group's first step (grp < GROUPS <= total is not guaranteed: checked below)
+    if (cur.t < total) {
+      issue(c[0], pw[0], cur.par, cur.cbyte);
+      issue(c[1], pw[1], cur.par + PASS_PAR, cur.cbyte);
+    }
+    uint32_t s_idx = (uint32_t)grp % nstages, s_ph = ((uint32_t)grp / nstages) & 1u;
+    while (cur.t < total) {
+      Cur nxt = cur;
+      seek(nxt, GROUPS);
+      const bool more = nxt.t < total;
+      mbar_wait(bar_empty + 8 * s_idx, s_ph ^ 1u);
+      if (warp == SAMPLER_WARP0) tr(0, 1); else if (warp == SAMPLER_WARP0 + SAMPLER_WARPS - 1) tr(4, 1);
+      const uint32_t a_st = smem_base + p.stage_off + s_idx * A_STAGE_BYTES + st_off;
 #pragma unroll
-      for (int i = 0; i < MAX_ITEMS; ++i) {
-        const int e = st + i * NS;
-        if (e >= n_param) continue;
-        const int kl = e >> 7, k = tap0 + kl, r = e & (TILE_PX - 1);
-        const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
-        uint4 po = make_uint4(0u, 0u, 0u, 0u), pw = make_uint4(0u, 0u, 0u, 0u);  // dead corner: offset 0, weight 0
-        if (y < p.H && x < p.W) {
-          const float m = p.mask_is_logit ? sigmoidf_accurate(raw_m[i]) : raw_m[i];
-          const int ki = k / 3;
-          const float py = (float)(y - 1 + ki) + raw_dy[i];
-          const float px = (float)(x - 1 + (k - 3 * ki)) + raw_dx[i];
-          if (py > -1.0f && px > -1.0f && py < (float)p.H && px < (float)p.W) {
-            const float fy = floorf(py), fx = floorf(px);
-            const int y0 = (int)fy, x0 = (int)fx;
-            const float ly = py - fy, lx = px - fx, hy = 1.0f - ly, hx = 1.0f - lx;
-            const bool vy0 = y0 >= 0, vy1 = y0 + 1 <= p.H - 1, vx0 = x0 >= 0, vx1 = x0 + 1 <= p.W - 1;
-            const uint32_t pixb = (uint32_t)p.Cin * (uint32_t)sizeof(T), rowb = (uint32_t)p.W * pixb;
-            const uint32_t o00 = (uint32_t)img_base * (uint32_t)sizeof(T) + (uint32_t)(y0 * p.W + x0) * pixb;  // may wrap for dead corners
-            if (vy0 && vx0) { po.x = o00;               pw.x = Blend<T>::weight(hy * hx * m); }
-            if (vy0 && vx1) { po.y = o00 + pixb;        pw.y = Blend<T>::weight(hy * lx * m); }
-            if (vy1 && vx0) { po.z = o00 + rowb;        pw.z = Blend<T>::weight(ly * hx * m); }
-            if (vy1 && vx1) { po.w = o00 + rowb + pixb; pw.w = Blend<T>::weight(ly * lx * m); }
-          }
-        }
-        sts16(poff_s + (uint32_t)(kl * TILE_PX + r) * 16u, po);
-        sts16(pw_s + (uint32_t)(kl * TILE_PX + r) * 16u, pw);
+      for (int i = 0; i < GROUP_PASSES; ++i) {
+        sts16(a_st + (uint32_t)(i * GROUP_ROWS * ROW_BYTES), Blend<T>::run(c[i & 1], pw[i & 1]));
+        if (i + 2 < GROUP_PASSES) issue(c[i & 1], pw[i & 1], cur.par + (uint32_t)((i + 2) * PASS_PAR), cur.cbyte);
+        else if (more) issue(c[i & 1], pw[i & 1], nxt.par + (uint32_t)((i + 2 - GROUP_PASSES) * PASS_PAR), nxt.cbyte);
       }
-      named_bar_sync(1, NS);
-      if (item + 1 < item_end) fetch_raw(item + 1);
-      // Rolling software pipeline over the item's chunks: the corner loads of chunk q+1 are issued while chunk q
-      // is blended, so every sampler warp keeps one pass (4 x 16 B per thread) in flight at all times instead of
-      // alternating between a load phase and a blend phase.
-      uint4 c[PASSES][4], pw[PASSES];
-      const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.x);
-      auto issue = [&](uint32_t pidx, uint32_t cbyte, int pass) {   // params + corner loads of one (chunk, pass)
-        const uint32_t idx = pidx + (uint32_t)(pass * ROWS_PER_PASS) * 16u;
-        const uint4 po = lds16(poff_s + idx);   // BYTE offsets of the four corner vectors
-        pw[pass] = lds16(pw_s + idx);
-        c[pass][0] = ldg16(xb + (po.x + cbyte));
-        c[pass][1] = ldg16(xb + (po.y + cbyte));
-        c[pass][2] = ldg16(xb + (po.z + cbyte));
-        c[pass][3] = ldg16(xb + (po.w + cbyte));
-      };
-      // (tap, channel chunk) cursor of the NEXT chunk to issue: parameter row index and channel byte offset
-      const uint32_t cbyte0 = (uint32_t)(cg * 16);
-      uint32_t n_pidx = (uint32_t)row_in_pass * 16u, n_cbyte = cbyte0;
-      int n_cc = 0;
-      auto next_chunk = [&]() {
-        n_cbyte += ROW_BYTES;
-        if (++n_cc == p.nchunk) { n_cc = 0; n_cbyte = cbyte0; n_pidx += TILE_PX * 16u; }
-      };
-#pragma unroll
-      for (int pass = 0; pass < PASSES; ++pass) issue(n_pidx, n_cbyte, pass);
-      next_chunk();
-      for (int q = 0; q < chunks_per_item; ++q) {
-        mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u);
-        const uint32_t a_base = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
-        const bool more = q + 1 < chunks_per_item;
-        const bool late = p.late_issue != 0;
-#pragma unroll
-        for (int pass = 0; pass < PASSES; ++pass) {
-          const int r = pass * ROWS_PER_PASS + row_in_pass;
-          sts16(a_base + r * ROW_BYTES + ((cg ^ (r & 7)) << 4), Blend<T>::run(c[pass], pw[pass]));
-          if (more && !late) issue(n_pidx, n_cbyte, pass);
-        }
-        fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy)
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_fullA + 8 * rc.s);
-        // (fence.proxy.async is MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC in SASS: it waits for every load this thread has in
-        //  flight, so loads issued before it are drained at every step; issuing them after it keeps them in flight
-        //  across the wait for the next free stage)
-        if (more && late) {
-#pragma unroll
-          for (int pass = 0; pass < PASSES; ++pass) issue(n_pidx, n_cbyte, pass);
-        }
-        next_chunk();
-        rc.advance(nstages);
+      fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy); drains this thread's loads
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(bar_fullA + 8 * s_idx);
+        mbar_arrive(bar_pempty + 8 * (cur.j & 1));   // this warp has consumed the step's parameters
       }
+      if (warp == SAMPLER_WARP0) tr(0, 2); else if (warp == SAMPLER_WARP0 + SAMPLER_WARPS - 1) tr(4, 2);
+      cur = nxt;
+      s_idx += (uint32_t)GROUPS;
+      while (s_idx >= nstages) { s_idx -= nstages; s_ph ^= 1u; }
     }
   } else if (warp == 4) {
     // =========================================================================== weight loader
@@ -372,20 +298,21 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
     for (int item = item_beg; item < item_end; ++item) {
       const int q0 = (item % p.split) * chunks_per_item;
       for (int q = 0; q < chunks_per_item; ++q) {
-        mbar_wait(bar_empty + 8 * rc.s, rc.ph ^ 1u, 100);
+        mbar_wait(bar_emptyB + 8 * rc.s, rc.ph ^ 1u, 100);
+        tr(1, 1);
         if (elect_one()) {
           mbar_arrive_expect_tx(bar_fullB + 8 * rc.s, (uint32_t)p.b_stage_bytes);
-          bulk_copy_g2s(smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes + A_STAGE_BYTES,
+          bulk_copy_g2s(smem_base + p.b_off + rc.s * p.b_stage_bytes,
                         wsrc + (size_t)(q0 + q) * p.b_stage_bytes, (uint32_t)p.b_stage_bytes, bar_fullB + 8 * rc.s);
         }
         __syncwarp();
-        rc.advance(nstages);
+        rc.advance(nbstages);
       }
     }
   } else if (warp == 5) {
     // =========================================================================== MMA issuer
     const uint32_t idesc = umma_idesc(kTF32, TILE_PX, p.Cout);
-    RingCursor rc;
+    RingCursor rc, rb;
     uint32_t tcount = 0;
     for (int item = item_beg; item < item_end; ++item, ++tcount) {
       const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
@@ -393,53 +320,193 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * (uint32_t)p.acc_cols;
       for (int q = 0; q < chunks_per_item; ++q) {
-        mbar_wait(bar_fullB + 8 * rc.s, rc.ph, 32);
+        mbar_wait(bar_fullB + 8 * rb.s, rb.ph, 32);
+        tr(2, 1);
         mbar_wait(bar_fullA + 8 * rc.s, rc.ph, 32);
+        tr(2, 2);
         tc_fence_after();
-        const uint32_t a_addr = smem_base + SMEM_STAGE_OFF + rc.s * p.stage_bytes;
+        const uint32_t a_addr = smem_base + p.stage_off + rc.s * A_STAGE_BYTES;
         const uint64_t adesc = umma_desc_sw128(a_addr);
-        const uint64_t bdesc = umma_desc_sw128(a_addr + A_STAGE_BYTES);
+        const uint64_t bdesc = umma_desc_sw128(smem_base + p.b_off + rb.s * p.b_stage_bytes);
         if (elect_one()) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)  // 4 x 32 bytes of K per 128-byte row
             umma<kTF32>(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (q | kk) != 0 ? 1u : 0u);
-          umma_commit(bar_empty + 8 * rc.s);       // frees the smem stage when these MMAs retire
+          umma_commit(bar_empty + 8 * rc.s);       // frees the A stage and the weight stage when these MMAs retire
+          umma_commit(bar_emptyB + 8 * rb.s);
           if (q == chunks_per_item - 1) umma_commit(bar_tfull + 8 * acc);   // accumulator complete -> epilogue
         }
         __syncwarp();
+        tr(2, 3);
         rc.advance(nstages);
+        rb.advance(nbstages);
       }
     }
   } else {
-    // =========================================================================== epilogue (warps 0-3)
+    // =========================================================================== parameters + epilogue (warps 0-3)
+    // Thread r owns pixel r of the tile: it computes the 9 (or 3, or 1) parameter entries of that pixel for the NEXT
+    // item, then drains accumulator row r (TMEM lane r) of the CURRENT one.
     T* yg = reinterpret_cast<T*>(p.y);
     const int64_t npix = (int64_t)p.B * p.H * p.W;
+    const int r = threadIdx.x;
+    const int ppp = p.om_esize * 2;                       // kOmFast: 16-byte pieces per pixel (32 channels): 8 or 4
+    const int ppp_shift = p.om_esize == 4 ? 3 : 2;
+    const uint32_t om_pitch = p.om_esize == 4 ? (uint32_t)OM_PITCH_F32 : (uint32_t)OM_PITCH_BF16;
+    // kOmFast: the item's 128 x 32 offset/mask values -> shared memory with coalesced 16-byte async copies (no
+    // registers held while they fly; issued one item ahead)
+    auto om_issue = [&](int item) {
+      if constexpr (kOmFast) {
+        int b, ty0, tx0, tap0;
+        item_coords(p, item, b, ty0, tx0, tap0);
+        const uint8_t* base = reinterpret_cast<const uint8_t*>(p.offset.ptr);
+        for (int idx = r; idx < TILE_PX * ppp; idx += PARAM_THREADS) {
+          const int rr = idx >> ppp_shift, jj = idx & (ppp - 1);
+          const int y = ty0 + (rr >> 4), x = tx0 + (rr & (TILE_W - 1));
+          if (y < p.H && x < p.W) {
+            const uint8_t* src = base + ((size_t)((b * p.H + y) * p.W + x) * 32) * p.om_esize + jj * 16;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(om_s + (uint32_t)rr * om_pitch + (uint32_t)jj * 16u), "l"(src) : "memory");
+          }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+      }
+    };
+    auto produce = [&](int jl) {   // parameters of local item jl -> buffer jl & 1
+      const int item = item_beg + jl;
+      int b, ty0, tx0, tap0;
+      item_coords(p, item, b, ty0, tx0, tap0);
+      const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
+      const bool inside = (y < p.H) && (x < p.W);
+      if (warp == 0) tr(3, 10);
+      float dyv[NUM_TAPS], dxv[NUM_TAPS], mv[NUM_TAPS];
+      if constexpr (kOmFast) {
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        named_bar_sync(1, PARAM_THREADS);                 // every thread's pieces have landed
+        const uint32_t row = om_s + (uint32_t)r * om_pitch;
+        if (p.om_esize == 4) {
+          uint32_t w[28];
+#pragma unroll
+          for (int i = 0; i < 7; ++i) { const uint4 v = lds16(row + 16u * i); w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w; }
+#pragma unroll
+          for (int k = 0; k < NUM_TAPS; ++k) { dyv[k] = __uint_as_float(w[2 * k]); dxv[k] = __uint_as_float(w[2 * k + 1]); mv[k] = __uint_as_float(w[18 + k]); }
+        } else {
+          uint32_t w[16];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { const uint4 v = lds16(row + 16u * i); w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w; }
+#pragma unroll
+          for (int k = 0; k < NUM_TAPS; ++k) {
+            dyv[k] = __uint_as_float(w[k] << 16); dxv[k] = __uint_as_float(w[k] & 0xffff0000u);
+            const uint32_t h = w[9 + (k >> 1)];
+            mv[k] = __uint_as_float((k & 1) ? (h & 0xffff0000u) : (h << 16));
+          }
+        }
+        named_bar_sync(1, PARAM_THREADS);                 // the staging tile is free again
+        if (jl + 1 < n_items) om_issue(item + 1);
+      } else {
+#pragma unroll
+        for (int k = 0; k < NUM_TAPS; ++k) {
+          dyv[k] = dxv[k] = mv[k] = 0.f;
+          if (inside && k >= tap0 && k < tap0 + p.taps_per_item) {
+            const int64_t opix = (int64_t)b * p.offset.sb + (int64_t)y * p.offset.sh + (int64_t)x * p.offset.sw;
+            dyv[k] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k) * p.offset.sc, p.om_dtype);
+            dxv[k] = ld_dyn(p.offset.ptr, opix + (int64_t)(2 * k + 1) * p.offset.sc, p.om_dtype);
+            mv[k] = ld_dyn(p.mask.ptr, (int64_t)b * p.mask.sb + (int64_t)k * p.mask.sc + (int64_t)y * p.mask.sh + (int64_t)x * p.mask.sw, p.om_dtype);
+          }
+        }
+      }
+      // the samplers have released this buffer (it held item jl - 2)
+      if (warp == 0) tr(3, 11);
+      mbar_wait(bar_pempty + 8 * (jl & 1), ((uint32_t)(jl >> 1) & 1u) ^ 1u, 100);
+      if (warp == 0) tr(3, 12);
+      const uint32_t buf = par_s + (uint32_t)(jl & 1) * (uint32_t)p.pbuf_bytes;
+      const uint32_t pixb = (uint32_t)p.Cin * (uint32_t)sizeof(T), rowb = (uint32_t)p.W * pixb;
+      const uint32_t img_byte = (uint32_t)(b * p.H * p.W * p.Cin) * (uint32_t)sizeof(T);   // < 2^32 (checked on the host)
+      // branch-free entry math, three taps per batch so that their dependent chains interleave (one warp per scheduler
+      // has nobody else to hide latency behind)
+      const float Hf = (float)p.H, Wf = (float)p.W;
+      const int tap_end = tap0 + p.taps_per_item;
+#pragma unroll
+      for (int kb = 0; kb < NUM_TAPS; kb += 3) {
+        if (kb + 3 <= tap0 || kb >= tap_end) continue;     // (uniform)
+        uint4 po[3], pw[3];
+#pragma unroll
+        for (int kk = 0; kk < 3; ++kk) {
+          const int k = kb + kk;
+          float dy = dyv[k], dx = dxv[k], mr = mv[k];
+          if (p.offset_bias) { dy += __ldg(p.offset_bias + 2 * k); dx += __ldg(p.offset_bias + 2 * k + 1); }
+          if (p.mask_bias) mr += __ldg(p.mask_bias + k);
+          float m = p.mask_is_logit ? __fdividef(1.0f, 1.0f + __expf(-mr)) : mr;   // <= 2e-7 from the exact sigmoid
+          const float py = (float)(y - 1 + k / 3) + dy;
+          const float px = (float)(x - 1 + k % 3) + dx;
+          const bool ok = inside && py > -1.0f && px > -1.0f && py < Hf && px < Wf;
+          m = ok ? m : 0.0f;
+          const float fy = floorf(py), fx = floorf(px);
+          const int y0 = ok ? (int)fy : 0, x0 = ok ? (int)fx : 0;
+          const float ly = py - fy, lx = px - fx, hy = 1.0f - ly, hx = 1.0f - lx;
+          const bool vy0 = ok && y0 >= 0, vy1 = ok && y0 + 1 <= p.H - 1, vx0 = x0 >= 0, vx1 = x0 + 1 <= p.W - 1;
+          const uint32_t o00 = img_byte + (uint32_t)(y0 * p.W + x0) * pixb;  // may wrap for dead corners (replaced by 0 below)
+          const float lym = ly * m, hym = hy * m;
+          po[kk].x = (vy0 && vx0) ? o00 : 0u;               pw[kk].x = (vy0 && vx0) ? Blend<T>::weight(hym * hx) : 0u;
+          po[kk].y = (vy0 && vx1) ? o00 + pixb : 0u;        pw[kk].y = (vy0 && vx1) ? Blend<T>::weight(hym * lx) : 0u;
+          po[kk].z = (vy1 && vx0) ? o00 + rowb : 0u;        pw[kk].z = (vy1 && vx0) ? Blend<T>::weight(lym * hx) : 0u;
+          po[kk].w = (vy1 && vx1) ? o00 + rowb + pixb : 0u; pw[kk].w = (vy1 && vx1) ? Blend<T>::weight(lym * lx) : 0u;
+        }
+#pragma unroll
+        for (int kk = 0; kk < 3; ++kk) {
+          const int k = kb + kk;
+          if (k < tap0 || k >= tap_end) continue;
+          const uint32_t e = buf + (uint32_t)((k - tap0) * TILE_PX + r) * 16u;
+          sts16(e, po[kk]);
+          sts16(e + pw_off, pw[kk]);
+          if (jl == 0) mbar_arrive(bar_first + 8 * (k - tap0));   // the CTA's first item is handed over tap by tap
+        }
+      }
+      mbar_arrive(bar_pfull + 8 * (jl & 1));   // release: the stores above are visible to the samplers that acquire it
+      if (warp == 0) tr(3, 13);
+    };
+    // order: the parameters of item j+2 go first (the samplers look one step ahead and reach them before item j+1 is
+    // finished), the epilogue of item j second (its accumulator is not needed again before item j+2's first MMA)
+    if (n_items > 0) { om_issue(item_beg); produce(0); }
+    if (n_items > 1) produce(1);
     uint32_t tcount = 0;
     for (int item = item_beg; item < item_end; ++item, ++tcount) {
+      if (item + 2 < item_end) produce((int)tcount + 2);
       const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
       int b, ty0, tx0, tap0;
       item_coords(p, item, b, ty0, tx0, tap0);
-      const int r = warp * 32 + lane;
       const int y = ty0 + (r >> 4), x = tx0 + (r & (TILE_W - 1));
       const bool valid = (y < p.H) && (x < p.W);
       const int64_t pix = ((int64_t)b * p.H + y) * p.W + x;
       mbar_wait(bar_tfull + 8 * acc, accph, 1000);
+      if (warp == 0) tr(3, 20);
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + acc * (uint32_t)p.acc_cols;
       if (p.split == 1) {
         T* yrow = yg + pix * p.Cout;
-        for (int c0 = 0; c0 < p.Cout; c0 += 16) {
-          uint32_t raw[16];
-          tmem_ld16(t_row + (uint32_t)c0, raw);
+        for (int c0 = 0; c0 < p.Cout; c0 += 32) {   // two 16-column TMEM loads in flight per wait
+          uint32_t raw[2][16];
+          const bool two = c0 + 16 < p.Cout;
+          tmem_ld16(t_row + (uint32_t)c0, raw[0]);
+          if (two) tmem_ld16(t_row + (uint32_t)(c0 + 16), raw[1]);
           tmem_ld_wait();
-          if (valid) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            if (!valid || (h == 1 && !two)) continue;
+            const int cb = c0 + 16 * h;
             float v[16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              v[j] = fmaf(__uint_as_float(raw[j]), scale_s[c0 + j], bias_s[c0 + j]);
-              if (p.relu) v[j] = fmaxf(v[j], 0.f);
+            for (int j4 = 0; j4 < 4; ++j4) {
+              const float4 sc = *reinterpret_cast<const float4*>(scale_s + cb + 4 * j4);
+              const float4 bi = *reinterpret_cast<const float4*>(bias_s + cb + 4 * j4);
+              v[4 * j4 + 0] = fmaf(__uint_as_float(raw[h][4 * j4 + 0]), sc.x, bi.x);
+              v[4 * j4 + 1] = fmaf(__uint_as_float(raw[h][4 * j4 + 1]), sc.y, bi.y);
+              v[4 * j4 + 2] = fmaf(__uint_as_float(raw[h][4 * j4 + 2]), sc.z, bi.z);
+              v[4 * j4 + 3] = fmaf(__uint_as_float(raw[h][4 * j4 + 3]), sc.w, bi.w);
             }
-            OutConv<T>::store(yrow + c0, v);
+            if (p.relu) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+            }
+            OutConv<T>::store(yrow + cb, v);
           }
         }
       } else {
@@ -457,6 +524,7 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       }
       tc_fence_before();
       mbar_arrive(bar_tempty + 8 * acc);
+      if (warp == 0) tr(3, 21);
     }
   }
 
@@ -621,19 +689,25 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   p.num_items = p.num_tiles * p.split;
   p.nchunk = a.Cin / (ROW_BYTES / esize);
   p.b_stage_bytes = a.Cout * ROW_BYTES;
-  p.stage_bytes = A_STAGE_BYTES + p.b_stage_bytes;
-  int stages = (SMEM_LIMIT - SMEM_STAGE_OFF) / p.stage_bytes;
-  if (stages > MAX_STAGES) stages = MAX_STAGES;
-  // 4 stages are as fast as 6 (r02 sweep: 2 / 3 / 4 / 6 stages = 79.8 / 77.9 / 78.0 / 79.9 us on 64->64 @256x512) and
-  // leave 48 KB more of the SM's 256 KB to L1, which is what the corner gathers live on
-  int want = 4;
-  if (const char* e = getenv("CPOLY_TC_STAGES")) want = atoi(e);  // profiling knob
-  if (want >= 2 && want < stages) stages = want;
-  CPOLY_REQUIRE(stages >= 2, CPOLY_EUNSUPPORTED, "not enough shared memory for a 2-stage pipeline");
-  p.stages = stages;
+  p.pbuf_bytes = p.taps_per_item * TILE_PX * 32;
+  p.stage_off = ((SMEM_PAR_OFF + 2 * p.pbuf_bytes + 1023) / 1024) * 1024;
+  // A ring: at least one stage per sampler group, two when they fit; weight ring: 2..4 stages of Cout x 128 B
+  const int room = SMEM_LIMIT - p.stage_off;
+  int b_stages = 3, a_stages = 2 * GROUPS;
+  if (const char* e = getenv("CPOLY_TC_STAGES")) a_stages = atoi(e);    // profiling knobs
+  if (const char* e = getenv("CPOLY_TC_BSTAGES")) b_stages = atoi(e);
+  if (b_stages < 2) b_stages = 2;
+  if (b_stages > MAX_B_STAGES) b_stages = MAX_B_STAGES;
+  if (a_stages > MAX_A_STAGES) a_stages = MAX_A_STAGES;
+  if (a_stages < GROUPS) a_stages = GROUPS;
+  while (b_stages > 2 && GROUPS * A_STAGE_BYTES + b_stages * p.b_stage_bytes > room) --b_stages;
+  while (a_stages > GROUPS && a_stages * A_STAGE_BYTES + b_stages * p.b_stage_bytes > room) --a_stages;
+  CPOLY_REQUIRE(a_stages * A_STAGE_BYTES + b_stages * p.b_stage_bytes <= room, CPOLY_EUNSUPPORTED, "not enough shared memory for the operand rings");
+  p.a_stages = a_stages; p.b_stages = b_stages;
+  p.b_off = p.stage_off + a_stages * A_STAGE_BYTES;
   p.acc_cols = a.Cout;
   p.tmem_cols = pow2_at_least(2 * a.Cout);
-  const int smem_bytes = SMEM_STAGE_OFF + stages * p.stage_bytes + 1024;  // +1 KB alignment slack
+  const int smem_bytes = p.b_off + b_stages * p.b_stage_bytes + 1024;  // +1 KB alignment slack
 
   int dev = 0, sms = 0;
   CPOLY_CUDA_OK(cudaGetDevice(&dev));
@@ -642,8 +716,14 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   // offsets + mask as ONE dense 32-channel NHWC tensor (channels 0..17 / 18..26)?  -> coalesced staging
   const int oes = a.om_dtype == CPOLY_BF16 ? 2 : 4;
   p.om_esize = oes;
-  p.late_issue = 1;
-  if (const char* e = getenv("CPOLY_TC_LATE")) p.late_issue = atoi(e) != 0;
+  p.trace = nullptr;
+  static long long* trace_buf = nullptr;
+  const bool tracing = getenv("CPOLY_TC_TRACE") != nullptr;
+  if (tracing) {
+    if (!trace_buf) cudaMalloc(&trace_buf, 5 * 4096 * sizeof(long long));
+    cudaMemsetAsync(trace_buf, 0, 5 * 4096 * sizeof(long long), stream);
+    p.trace = trace_buf;
+  }
   const cpoly_tensor4 &o = a.offset, &m = a.mask;
   bool om_fast = o.sc == 1 && o.sw == 32 && o.sh == (int64_t)a.W * 32 && o.sb == (int64_t)a.H * a.W * 32 && m.sc == 1 && m.sw == 32 &&
                  m.sh == o.sh && m.sb == o.sb && reinterpret_cast<const uint8_t*>(m.ptr) == reinterpret_cast<const uint8_t*>(o.ptr) + 18 * oes &&
@@ -661,6 +741,18 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   }
 #undef CPOLY_LAUNCH_FWD
   if (int rc = check_launch("dcn_fwd_tc_kernel")) return rc;
+  if (tracing) {   // debugging aid only: dumps CTA 0's event log (role, tag, cycles since the first event) to stderr
+    static int dumps = 0;
+    cudaStreamSynchronize(stream);
+    if (dumps++ == atoi(getenv("CPOLY_TC_TRACE"))) {
+      static long long h[5 * 4096];
+      cudaMemcpy(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost);
+      long long t0 = 0;
+      for (int r = 0; r < 5; ++r) if (h[r * 4096] && (!t0 || h[r * 4096] < t0)) t0 = h[r * 4096];
+      for (int r = 0; r < 5; ++r)
+        for (int i = 0; i < 2048 && h[r * 4096 + 2 * i]; ++i) fprintf(stderr, "TRACE %d %lld %lld\n", r, h[r * 4096 + 2 * i + 1], h[r * 4096 + 2 * i] - t0);
+    }
+  }
   if (p.split > 1) return dcn_tc_launch_combine(p.partial, a.y.ptr, a.dtype, a.out_scale, a.bias, npix, a.Cout, p.split, a.relu, stream);
   return CPOLY_OK;
 }

@@ -203,7 +203,8 @@ def test_fused_adam_step_is_seen_by_the_next_forward():
     with torch.no_grad():
         om = m.conv_offset_mask(x)
         want = cp.dcn_v2_conv(x, om[:, :18], torch.sigmoid(om[:, 18:]), m.weight.detach().clone(), m.bias.detach().clone(), 1, 1, 1, 1)
-    gate(y1.detach().float().cpu().numpy(), want.float().cpu().numpy(), 1e-5, "forward after fused Adam")
+    # (a stale weight image is an O(1) error; 1e-4 leaves room for the in-kernel sigmoid flipping a TF32 rounding)
+    gate(y1.detach().float().cpu().numpy(), want.float().cpu().numpy(), 1e-4, "forward after fused Adam")
     assert not torch.allclose(y1.detach(), y0.detach())
     # no-grad inference after an out-of-band update: the cache is dropped by hand
     with torch.no_grad():
@@ -211,7 +212,7 @@ def test_fused_adam_step_is_seen_by_the_next_forward():
         cp.invalidate_packed_weights(m)
         y2 = m(x)
         want2 = cp.dcn_v2_conv(x, om[:, :18], torch.sigmoid(om[:, 18:]), m.weight.detach().clone(), m.bias.detach().clone(), 1, 1, 1, 1)
-    gate(y2.float().cpu().numpy(), want2.float().cpu().numpy(), 1e-5, "forward after invalidate")
+    gate(y2.float().cpu().numpy(), want2.float().cpu().numpy(), 1e-4, "forward after invalidate")
 
 
 def test_nchw_input_is_accepted():
