@@ -693,7 +693,9 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   p.stage_off = ((SMEM_PAR_OFF + 2 * p.pbuf_bytes + 1023) / 1024) * 1024;
   // A ring: at least one stage per sampler group, two when they fit; weight ring: 2..4 stages of Cout x 128 B
   const int room = SMEM_LIMIT - p.stage_off;
-  int b_stages = 3, a_stages = 2 * GROUPS;
+  // 4 + 2 measured fastest on every neck layer (r02: 8+3 -> 77.7 us, 4+2 -> 72.8 us graph-replayed on 64->64 @256x512): what the
+  // rings do not take stays L1, which the corner gathers live on
+  int b_stages = 2, a_stages = GROUPS;
   if (const char* e = getenv("CPOLY_TC_STAGES")) a_stages = atoi(e);    // profiling knobs
   if (const char* e = getenv("CPOLY_TC_BSTAGES")) b_stages = atoi(e);
   if (b_stages < 2) b_stages = 2;
