@@ -26,6 +26,7 @@ EXPORTED_SYMBOLS = (
     "cpoly_rasterise_workspace_bytes", "cpoly_rasterise", "cpoly_poly_iou_forward", "cpoly_poly_iou_backward",
     "cpoly_stem_pack_weights", "cpoly_stem_conv7x7_forward", "cpoly_maxpool2x2_nhwc_forward",
     "cpoly_offset_conv_packed_bytes", "cpoly_offset_conv_pack_weights", "cpoly_offset_conv_forward",
+    "cpoly_decode_static_max_bytes", "cpoly_decode_static",
 )
 
 
@@ -131,6 +132,10 @@ def lib():
         L.cpoly_decode_workspace_bytes.argtypes = [c_int32] * 5
         L.cpoly_decode.restype = c_int32
         L.cpoly_decode.argtypes = [POINTER(DecodeArgs), c_void_p]
+        L.cpoly_decode_static_max_bytes.restype = c_size_t
+        L.cpoly_decode_static_max_bytes.argtypes = []
+        L.cpoly_decode_static.restype = c_int32
+        L.cpoly_decode_static.argtypes = [POINTER(DecodeArgs), c_void_p]
         L.cpoly_rasterise_workspace_bytes.restype = c_size_t
         L.cpoly_rasterise_workspace_bytes.argtypes = [c_int32] * 2
         L.cpoly_rasterise.restype = c_int32
@@ -153,7 +158,7 @@ def lib():
         L.cpoly_offset_conv_pack_weights.argtypes = [c_void_p, c_void_p, c_int32, c_int32, c_void_p]
         L.cpoly_offset_conv_forward.restype = c_int32
         L.cpoly_offset_conv_forward.argtypes = [POINTER(OffsetConvArgs), c_void_p]
-        if L.cpoly_abi_version() != 8:
+        if L.cpoly_abi_version() != 9:
             raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
         _lib = L
     return _lib

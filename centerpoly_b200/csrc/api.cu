@@ -163,6 +163,23 @@ int cpoly_decode(const cpoly_decode_args* a, cpoly_stream_t stream) {
   return decode_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+size_t cpoly_decode_static_max_bytes(void) { return CPOLY_DECODE_STATIC_BYTES; }
+
+int cpoly_decode_static(const cpoly_decode_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->C > 0 && a->H > 0 && a->W > 0 && a->K >= 1, CPOLY_EINVAL, "bad heat dims");
+  const size_t need = cpoly_decode_workspace_bytes(a->B, a->C, a->H, a->W, a->K);
+  CPOLY_REQUIRE(need <= (size_t)CPOLY_DECODE_STATIC_BYTES, CPOLY_EWORKSPACE,
+                "cpoly_decode_static: B=%d C=%d H=%d W=%d needs %zu bytes of scratch, the built-in array holds %zu; use cpoly_decode "
+                "with a caller-allocated workspace", a->B, a->C, a->H, a->W, need, (size_t)CPOLY_DECODE_STATIC_BYTES);
+  cpoly_decode_args b = *a;
+  void* scratch = nullptr;
+  if (int rc = decode_static_scratch(&scratch)) return rc;
+  b.workspace = scratch;
+  b.workspace_bytes = CPOLY_DECODE_STATIC_BYTES;
+  return cpoly_decode(&b, stream);
+}
+
 size_t cpoly_rasterise_workspace_bytes(int32_t B, int32_t K) {
   if (B <= 0 || K <= 0) return 256;
   return raster_workspace_bytes(B, K);

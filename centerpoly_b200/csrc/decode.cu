@@ -26,6 +26,8 @@
 // (class, y, x) whenever scores are tie-free; heat must be non-negative (it is post-sigmoid).
 #include <math_constants.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace cpoly {
@@ -739,6 +741,33 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
   if (bf) decode_gather_kernel<__nv_bfloat16><<<gblocks, DNT, 0, stream>>>(p);
   else decode_gather_kernel<float><<<gblocks, DNT, 0, stream>>>(p);
   return check_launch("decode_gather_kernel");
+}
+
+// ---- allocation-free variant: the scratch is a file-scope device array -------------------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, serving loops, harnesses that forbid it).
+// Every GPU that loads the library holds these 4 MiB until the process exits.  Every call on a device shares the array:
+// two cpoly_decode_static calls that overlap on the GPU (different streams) race.  The array keeps the last call's
+// contents; decode_launch clears the only part that must start at zero (candidate counters + threshold bins) itself.
+static __device__ __align__(256) unsigned char g_decode_static_scratch[CPOLY_DECODE_STATIC_BYTES];
+
+// In host code `g_decode_static_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, looked up once per device with that device current.
+int decode_static_scratch(void** ptr) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static void* addr[MAX_DEV] = {};
+  int dev = -1;
+  CPOLY_CUDA_OK(cudaGetDevice(&dev));
+  CPOLY_REQUIRE(dev >= 0 && dev < MAX_DEV, CPOLY_EUNSUPPORTED, "device ordinal %d outside the static-scratch table", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void* q = nullptr;
+    CPOLY_CUDA_OK(cudaGetSymbolAddress(&q, g_decode_static_scratch));
+    CPOLY_REQUIRE(q && (reinterpret_cast<uintptr_t>(q) & 255) == 0, CPOLY_ECUDA, "static decode scratch has no aligned device address");
+    addr[dev] = q;
+  }
+  *ptr = addr[dev];
+  return CPOLY_OK;
 }
 
 }  // namespace cpoly

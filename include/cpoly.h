@@ -55,7 +55,7 @@
 extern "C" {
 #endif
 
-#define CPOLY_ABI_VERSION 8
+#define CPOLY_ABI_VERSION 9
 
 /* element types */
 #define CPOLY_F32 0
@@ -214,6 +214,20 @@ typedef struct {
 
 size_t cpoly_decode_workspace_bytes(int32_t B, int32_t C, int32_t H, int32_t W, int32_t K);
 int cpoly_decode(const cpoly_decode_args* args, cpoly_stream_t stream);
+
+/* ---- cpoly_decode without any allocation (ABI v9) ----------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Same inputs, outputs and results as cpoly_decode; `args->workspace` / `workspace_bytes` are ignored: the scratch is a
+ * file-scope `static __device__` array of CPOLY_DECODE_STATIC_BYTES (4 MiB) inside the library, which every GPU that
+ * loads libcpoly.so holds until the process exits.  Shapes whose cpoly_decode_workspace_bytes(B,C,H,W,K) exceeds that
+ * (e.g. B > 15 at the 128x256 x 8-class map of the headline frame) are rejected with CPOLY_EWORKSPACE - use cpoly_decode.
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  The first call on each device
+ * looks the array's address up (cudaGetSymbolAddress): make that call outside a capture.  All calls on a device share
+ * the array: calls that overlap on the GPU (different streams) race - serialise them on one stream or with events. */
+#define CPOLY_DECODE_STATIC_BYTES (4u << 20)
+size_t cpoly_decode_static_max_bytes(void);
+int cpoly_decode_static(const cpoly_decode_args* args, cpoly_stream_t stream);
 
 /* --------------------------------------------------------------------------- instance rasterisation */
 
