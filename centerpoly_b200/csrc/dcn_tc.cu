@@ -80,6 +80,7 @@ struct TcParams {
   int om_esize;    // element size of the fused 32-channel offset/mask tensor (kOmFast kernels)
   int pbuf_bytes;  // one parameter buffer: corner offsets (taps_per_item * 128 * 16 B) then corner weights (same size)
   int stage_off;   // byte offset of the operand ring (1024-aligned, after the parameter buffers)
+  int pf_halo, pf_dist;   // L1 prefetch of a coming item's window: halo in pixels (< 0: off), distance in items
   long long* trace;  // profiling only (CPOLY_TC_TRACE): clock64 event log of CTA 0, 5 roles x 4096 entries
 };
 
@@ -465,10 +466,28 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
     };
     // order: the parameters of item j+2 go first (the samplers look one step ahead and reach them before item j+1 is
     // finished), the epilogue of item j second (its accumulator is not needed again before item j+2's first MMA)
+    // pull the bilinear footprint (tile + halo) of a coming item towards this SM's L1: a sampler wait covers 32 cache
+    // lines and is as long as the slowest of them, so even the compulsory misses put an L2 round trip into most waits
+    auto prefetch = [&](int jl) {
+      if (p.pf_halo < 0 || jl >= n_items) return;
+      int b, ty0, tx0, tap0;
+      item_coords(p, item_beg + jl, b, ty0, tx0, tap0);
+      const int hw = p.pf_halo, ww = TILE_W + 2 * hw, wh = TILE_H + 2 * hw;
+      const int lpp = (p.Cin * (int)sizeof(T)) >> 7;                     // 128-byte lines per pixel
+      const uint8_t* img = reinterpret_cast<const uint8_t*>(p.x) + (size_t)b * p.H * p.W * p.Cin * sizeof(T);
+      for (int i = r; i < ww * wh * lpp; i += PARAM_THREADS) {
+        const int px = i / lpp, l = i - px * lpp;
+        const int wy = px / ww, wx = px - wy * ww;
+        const int yy = ty0 - hw + wy, xx = tx0 - hw + wx;
+        if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W)
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(img + ((size_t)(yy * p.W + xx) * p.Cin) * sizeof(T) + l * 128));
+      }
+    };
     if (n_items > 0) { om_issue(item_beg); produce(0); }
     if (n_items > 1) produce(1);
     uint32_t tcount = 0;
     for (int item = item_beg; item < item_end; ++item, ++tcount) {
+      prefetch((int)tcount + p.pf_dist);
       if (item + 2 < item_end) produce((int)tcount + 2);
       const uint32_t acc = tcount & 1u, accph = (tcount >> 1) & 1u;
       int b, ty0, tx0, tap0;
@@ -718,6 +737,9 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   // offsets + mask as ONE dense 32-channel NHWC tensor (channels 0..17 / 18..26)?  -> coalesced staging
   const int oes = a.om_dtype == CPOLY_BF16 ? 2 : 4;
   p.om_esize = oes;
+  p.pf_halo = -1; p.pf_dist = 1;
+  if (const char* e = getenv("CPOLY_TC_PF")) p.pf_halo = atoi(e);     // profiling knobs
+  if (const char* e = getenv("CPOLY_TC_PFD")) p.pf_dist = atoi(e);
   p.trace = nullptr;
   static long long* trace_buf = nullptr;
   const bool tracing = getenv("CPOLY_TC_TRACE") != nullptr;
@@ -731,9 +753,14 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
                  m.sh == o.sh && m.sb == o.sb && reinterpret_cast<const uint8_t*>(m.ptr) == reinterpret_cast<const uint8_t*>(o.ptr) + 18 * oes &&
                  (reinterpret_cast<uintptr_t>(o.ptr) & 15) == 0 && (int64_t)a.B * a.H * a.W < (1LL << 26);
   if (const char* e = getenv("CPOLY_TC_OM")) om_fast = om_fast && atoi(e) != 0;   // profiling knob: CPOLY_TC_OM=0 keeps the strided loads
+  // shared-memory carveout: just what the CTA needs, so that the rest of the SM's 256 KB is L1 for the corner gathers
+  int carve = (int)(((long long)(smem_bytes + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+  if (carve > 100) carve = 100;
+  if (const char* e = getenv("CPOLY_TC_CARVE")) carve = atoi(e);   // profiling knob (-1: driver default)
 #define CPOLY_LAUNCH_FWD(TT, FAST)                                                                                            \
   do {                                                                                                                        \
     CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_fwd_tc_kernel<TT, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes)); \
+    if (carve >= 0) CPOLY_CUDA_OK(cudaFuncSetAttribute(dcn_fwd_tc_kernel<TT, FAST>, cudaFuncAttributePreferredSharedMemoryCarveout, carve)); \
     dcn_fwd_tc_kernel<TT, FAST><<<grid, NTHREADS, smem_bytes, stream>>>(p);                                                   \
   } while (0)
   if (a.dtype == CPOLY_BF16) {
