@@ -48,7 +48,7 @@ constexpr int GROUPS = 4;                      // sampler groups: group g owns t
 constexpr int GROUP_THREADS = NS / GROUPS;     // 128
 constexpr int GROUP_ROWS = GROUP_THREADS / 8;  // 16 rows of the tile per pass (8 lanes x 16 B per row)
 constexpr int GROUP_PASSES = TILE_PX / GROUP_ROWS;   // 8 passes per step
-constexpr int PASS_PAR = GROUP_ROWS * 16;      // parameter bytes between two passes
+constexpr int PASS_OFF = GROUP_ROWS * 4;       // bytes of corner-offset words between two passes
 constexpr int PARAM_THREADS = EPI_WARPS * 32;  // warps 0-3: thread r owns pixel r of the tile (= TMEM lane r)
 
 // shared-memory map (dynamic, 1024-byte aligned)
@@ -56,7 +56,7 @@ constexpr int SMEM_BAR_OFF = 0;        // mbarriers + tmem pointer
 constexpr int SMEM_VEC_OFF = 1024;     // scale[256] + bias[256] floats
 constexpr int SMEM_OM_OFF = 3072;      // staged offset/mask tile of the next item: 128 pixels x (128 + 16) bytes
 constexpr int OM_PITCH_F32 = 144, OM_PITCH_BF16 = 80;   // 16-byte aligned rows; 8 consecutive rows cover all 32 banks
-constexpr int SMEM_PAR_OFF = SMEM_OM_OFF + TILE_PX * OM_PITCH_F32;   // two parameter buffers of taps_per_item * 128 * 32 B
+constexpr int SMEM_PAR_OFF = SMEM_OM_OFF + TILE_PX * OM_PITCH_F32;   // two parameter buffers of taps_per_item * 128 * (4 + 8 | 16) B
 constexpr int SMEM_LIMIT = 226 * 1024;  // 227 KB per CTA minus the alignment slack
 
 struct TcParams {
@@ -76,9 +76,10 @@ struct TcParams {
   int nchunk;      // channel chunks per tap
   int a_stages, b_stages, b_stage_bytes;   // A ring (16 KB tiles, >= GROUPS stages) and the independent weight ring
   int b_off;       // byte offset of the weight ring (1024-aligned, after the A ring)
+  int st_off;      // byte offset of the 16 KB output staging tile (after the weight ring)
   int acc_cols, tmem_cols;
   int om_esize;    // element size of the fused 32-channel offset/mask tensor (kOmFast kernels)
-  int pbuf_bytes;  // one parameter buffer: corner offsets (taps_per_item * 128 * 16 B) then corner weights (same size)
+  int pbuf_bytes;  // one parameter buffer: taps_per_item * 128 base-offset words, then as many weight entries (8 B bf16 / 16 B fp32)
   int stage_off;   // byte offset of the operand ring (1024-aligned, after the parameter buffers)
   int pf_halo, pf_dist;   // L1 prefetch of a coming item's window: halo in pixels (< 0: off), distance in items
   long long* trace;  // profiling only (CPOLY_TC_TRACE): clock64 event log of CTA 0, 5 roles x 4096 entries
@@ -91,6 +92,20 @@ struct TcParams {
 template <typename T> struct Blend;
 template <> struct Blend<__nv_bfloat16> {
   static constexpr int kVec = 8;  // channels per 16 bytes
+  // parameter entry: the four mask * bilinear weights as 4 x bf16 (8 bytes); the (w, w) pairs of the packed FMAs are made
+  // with one PRMT each at blend time
+  using Packed = uint2;
+  static constexpr int kWBytes = 8;
+  __device__ static __forceinline__ Packed pack(float w0, float w1, float w2, float w3) { return make_uint2(pack_bf16x2(w0, w1), pack_bf16x2(w2, w3)); }
+  __device__ static __forceinline__ Packed lds(uint32_t a) {
+    uint2 v;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+    return v;
+  }
+  __device__ static __forceinline__ void sts(uint32_t a, Packed v) { asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a), "r"(v.x), "r"(v.y) : "memory"); }
+  __device__ static __forceinline__ uint4 run(const uint4 (&c)[4], const Packed w) {
+    return run(c, make_uint4(__byte_perm(w.x, 0u, 0x1010), __byte_perm(w.x, 0u, 0x3232), __byte_perm(w.y, 0u, 0x1010), __byte_perm(w.y, 0u, 0x3232)));
+  }
   __device__ static __forceinline__ uint32_t weight(float w) { return pack_bf16x2(w, w); }
   __device__ static __forceinline__ uint4 run(const uint4 (&c)[4], const uint4 w) {
     uint4 out;
@@ -103,6 +118,11 @@ template <> struct Blend<__nv_bfloat16> {
 };
 template <> struct Blend<float> {
   static constexpr int kVec = 4;
+  using Packed = uint4;   // 4 x fp32
+  static constexpr int kWBytes = 16;
+  __device__ static __forceinline__ Packed pack(float w0, float w1, float w2, float w3) { return make_uint4(__float_as_uint(w0), __float_as_uint(w1), __float_as_uint(w2), __float_as_uint(w3)); }
+  __device__ static __forceinline__ Packed lds(uint32_t a) { return lds16(a); }
+  __device__ static __forceinline__ void sts(uint32_t a, Packed v) { sts16(a, v); }
   __device__ static __forceinline__ uint32_t weight(float w) { return __float_as_uint(w); }
   __device__ static __forceinline__ uint4 run(const uint4 (&c)[4], const uint4 w) {
     const float w0 = __uint_as_float(w.x), w1 = __uint_as_float(w.y), w2 = __uint_as_float(w.z), w3 = __uint_as_float(w.w);
@@ -117,6 +137,10 @@ template <> struct Blend<float> {
 
 template <typename T> struct OutConv;
 template <> struct OutConv<__nv_bfloat16> {
+  __device__ static __forceinline__ void pieces(const float (&v)[16], uint4 (&o)[2]) {
+    o[0] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+    o[1] = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]), pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
+  }
   // 16 fp32 values -> 32 bytes
   __device__ static __forceinline__ void store(__nv_bfloat16* dst, const float (&v)[16]) {
     uint4 a, b;
@@ -127,6 +151,10 @@ template <> struct OutConv<__nv_bfloat16> {
   }
 };
 template <> struct OutConv<float> {
+  __device__ static __forceinline__ void pieces(const float (&v)[16], uint4 (&o)[4]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = make_uint4(__float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]), __float_as_uint(v[4 * j + 2]), __float_as_uint(v[4 * j + 3]));
+  }
   __device__ static __forceinline__ void store(float* dst, const float (&v)[16]) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) reinterpret_cast<float4*>(dst)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
@@ -170,7 +198,8 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
   float* scale_s = reinterpret_cast<float*>(smem + SMEM_VEC_OFF);
   float* bias_s = scale_s + 256;
   const uint32_t om_s = smem_base + SMEM_OM_OFF, par_s = smem_base + SMEM_PAR_OFF;
-  const uint32_t pw_off = (uint32_t)p.pbuf_bytes >> 1;   // corner weights follow the corner offsets inside a buffer
+  const uint32_t pw_off = (uint32_t)(p.taps_per_item * TILE_PX) * 4u;   // the weight entries follow the base-offset words inside a buffer
+  const uint32_t pixb = (uint32_t)p.Cin * (uint32_t)sizeof(T), rowb = (uint32_t)p.W * pixb;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -234,10 +263,11 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
     const uint32_t cbyte0 = (uint32_t)(cg * 16);
     const int total = n_items * chunks_per_item;
     const uint32_t st_off = (uint32_t)(row0 * ROW_BYTES + ((cg ^ (row0 & 7)) << 4));   // + pass * 16 rows * 128 B
-    const uint32_t par_row = par_s + (uint32_t)row0 * 16u;
-    uint4 c[2][4], pw[2];
+    uint4 c[2][4];
+    typename Blend<T>::Packed pw[2];
+    constexpr uint32_t kWB = Blend<T>::kWBytes, PASS_W = GROUP_ROWS * kWB;
     // cursor: (item, tap, chunk) of a step; `par` / `cbyte` are what the passes need
-    struct Cur { int t, j, kl, cc; uint32_t par, cbyte; };
+    struct Cur { int t, j, kl, cc; uint32_t par, parw, cbyte; };
     auto seek = [&](Cur& u, int adv) {            // move u by `adv` steps (adv <= GROUPS), waiting for the parameters it lands on
       u.t += adv;
       if (u.t >= total) return;
@@ -249,22 +279,30 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
         mbar_wait(bar_pfull + 8 * (u.j & 1), (uint32_t)(u.j >> 1) & 1u);
       }
       if (u.j == 0) mbar_wait(bar_first + 8 * u.kl, 0u);
-      u.par = par_row + (uint32_t)(u.j & 1) * (uint32_t)p.pbuf_bytes + (uint32_t)(u.kl * TILE_PX) * 16u;
+      const uint32_t buf = par_s + (uint32_t)(u.j & 1) * (uint32_t)p.pbuf_bytes, e = (uint32_t)(u.kl * TILE_PX + row0);
+      u.par = buf + e * 4u;
+      u.parw = buf + pw_off + e * kWB;
       u.cbyte = cbyte0 + (uint32_t)u.cc * ROW_BYTES;
     };
-    auto issue = [&](uint4 (&cb)[4], uint4& pwb, uint32_t par, uint32_t cbyte) {   // parameters + corner loads of one pass
-      const uint4 po = lds16(par);                // BYTE offsets of the four corner vectors
-      pwb = lds16(par + pw_off);
-      cb[0] = ldg16(xb + (po.x + cbyte));
-      cb[1] = ldg16(xb + (po.y + cbyte));
-      cb[2] = ldg16(xb + (po.z + cbyte));
-      cb[3] = ldg16(xb + (po.w + cbyte));
+    // parameters + corner loads of one pass.  Entry = one word (byte offset of the clamped base corner | bit 0: the
+    // x+1 corner is a different pixel | bit 1: the y+1 corner is) + the four weights; a corner that falls outside the
+    // image has weight 0 and re-reads an in-range neighbour.
+    auto issue = [&](uint4 (&cb)[4], typename Blend<T>::Packed& pwb, const Cur& u, int pass) {
+      uint32_t w;
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(u.par + (uint32_t)(pass * PASS_OFF)));
+      pwb = Blend<T>::lds(u.parw + (uint32_t)pass * PASS_W);
+      const uint32_t o00 = (w & ~3u) + u.cbyte;
+      const uint32_t dx = (w & 1u) ? pixb : 0u, dy = (w & 2u) ? rowb : 0u;
+      cb[0] = ldg16(xb + o00);
+      cb[1] = ldg16(xb + (o00 + dx));
+      cb[2] = ldg16(xb + (o00 + dy));
+      cb[3] = ldg16(xb + (o00 + dy + dx));
     };
-    Cur cur{-1, 0, 0, -1, 0u, 0u};
+    Cur cur{-1, 0, 0, -1, 0u, 0u, 0u};
     seek(cur, grp + 1);                           // the group's first step (grp < GROUPS <= total is not guaranteed: checked below)
     if (cur.t < total) {
-      issue(c[0], pw[0], cur.par, cur.cbyte);
-      issue(c[1], pw[1], cur.par + PASS_PAR, cur.cbyte);
+      issue(c[0], pw[0], cur, 0);
+      issue(c[1], pw[1], cur, 1);
     }
     uint32_t s_idx = (uint32_t)grp % nstages, s_ph = ((uint32_t)grp / nstages) & 1u;
     while (cur.t < total) {
@@ -277,8 +315,8 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
 #pragma unroll
       for (int i = 0; i < GROUP_PASSES; ++i) {
         sts16(a_st + (uint32_t)(i * GROUP_ROWS * ROW_BYTES), Blend<T>::run(c[i & 1], pw[i & 1]));
-        if (i + 2 < GROUP_PASSES) issue(c[i & 1], pw[i & 1], cur.par + (uint32_t)((i + 2) * PASS_PAR), cur.cbyte);
-        else if (more) issue(c[i & 1], pw[i & 1], nxt.par + (uint32_t)((i + 2 - GROUP_PASSES) * PASS_PAR), nxt.cbyte);
+        if (i + 2 < GROUP_PASSES) issue(c[i & 1], pw[i & 1], cur, i + 2);
+        else if (more) issue(c[i & 1], pw[i & 1], nxt, i + 2 - GROUP_PASSES);
       }
       fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core (async proxy); drains this thread's loads
       __syncwarp();
@@ -419,7 +457,6 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       mbar_wait(bar_pempty + 8 * (jl & 1), ((uint32_t)(jl >> 1) & 1u) ^ 1u, 100);
       if (warp == 0) tr(3, 12);
       const uint32_t buf = par_s + (uint32_t)(jl & 1) * (uint32_t)p.pbuf_bytes;
-      const uint32_t pixb = (uint32_t)p.Cin * (uint32_t)sizeof(T), rowb = (uint32_t)p.W * pixb;
       const uint32_t img_byte = (uint32_t)(b * p.H * p.W * p.Cin) * (uint32_t)sizeof(T);   // < 2^32 (checked on the host)
       // branch-free entry math, three taps per batch so that their dependent chains interleave (one warp per scheduler
       // has nobody else to hide latency behind)
@@ -428,7 +465,8 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
 #pragma unroll
       for (int kb = 0; kb < NUM_TAPS; kb += 3) {
         if (kb + 3 <= tap0 || kb >= tap_end) continue;     // (uniform)
-        uint4 po[3], pw[3];
+        uint32_t po[3];
+        typename Blend<T>::Packed pw[3];
 #pragma unroll
         for (int kk = 0; kk < 3; ++kk) {
           const int k = kb + kk;
@@ -441,23 +479,23 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
           const bool ok = inside && py > -1.0f && px > -1.0f && py < Hf && px < Wf;
           m = ok ? m : 0.0f;
           const float fy = floorf(py), fx = floorf(px);
-          const int y0 = ok ? (int)fy : 0, x0 = ok ? (int)fx : 0;
+          const int y0 = ok ? (int)fy : 0, x0 = ok ? (int)fx : 0;          // in [-1, H-1] x [-1, W-1]
           const float ly = py - fy, lx = px - fx, hy = 1.0f - ly, hx = 1.0f - lx;
-          const bool vy0 = ok && y0 >= 0, vy1 = ok && y0 + 1 <= p.H - 1, vx0 = x0 >= 0, vx1 = x0 + 1 <= p.W - 1;
-          const uint32_t o00 = img_byte + (uint32_t)(y0 * p.W + x0) * pixb;  // may wrap for dead corners (replaced by 0 below)
-          const float lym = ly * m, hym = hy * m;
-          po[kk].x = (vy0 && vx0) ? o00 : 0u;               pw[kk].x = (vy0 && vx0) ? Blend<T>::weight(hym * hx) : 0u;
-          po[kk].y = (vy0 && vx1) ? o00 + pixb : 0u;        pw[kk].y = (vy0 && vx1) ? Blend<T>::weight(hym * lx) : 0u;
-          po[kk].z = (vy1 && vx0) ? o00 + rowb : 0u;        pw[kk].z = (vy1 && vx0) ? Blend<T>::weight(lym * hx) : 0u;
-          po[kk].w = (vy1 && vx1) ? o00 + rowb + pixb : 0u; pw[kk].w = (vy1 && vx1) ? Blend<T>::weight(lym * lx) : 0u;
+          const bool vy0 = y0 >= 0, vy1 = y0 + 1 <= p.H - 1, vx0 = x0 >= 0, vx1 = x0 + 1 <= p.W - 1;
+          // base corner clamped into the image; the +1 corners are distinct pixels only when both neighbours exist, else
+          // they re-read the base row / column (their weight, or the base's, is zero then)
+          const int yb = vy0 ? y0 : 0, xq = vx0 ? x0 : 0;
+          po[kk] = (img_byte + (uint32_t)(yb * p.W + xq) * pixb) | ((vx0 && vx1) ? 1u : 0u) | ((vy0 && vy1) ? 2u : 0u);
+          const float lym = vy1 ? ly * m : 0.0f, hym = vy0 ? hy * m : 0.0f;
+          pw[kk] = Blend<T>::pack(vx0 ? hym * hx : 0.0f, vx1 ? hym * lx : 0.0f, vx0 ? lym * hx : 0.0f, vx1 ? lym * lx : 0.0f);
         }
 #pragma unroll
         for (int kk = 0; kk < 3; ++kk) {
           const int k = kb + kk;
           if (k < tap0 || k >= tap_end) continue;
-          const uint32_t e = buf + (uint32_t)((k - tap0) * TILE_PX + r) * 16u;
-          sts16(e, po[kk]);
-          sts16(e + pw_off, pw[kk]);
+          const uint32_t e = (uint32_t)((k - tap0) * TILE_PX + r);
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(buf + e * 4u), "r"(po[kk]) : "memory");
+          Blend<T>::sts(buf + pw_off + e * (uint32_t)Blend<T>::kWBytes, pw[kk]);
           if (jl == 0) mbar_arrive(bar_first + 8 * (k - tap0));   // the CTA's first item is handed over tap by tap
         }
       }
@@ -500,33 +538,57 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
       tc_fence_after();
       const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + acc * (uint32_t)p.acc_cols;
       if (p.split == 1) {
-        T* yrow = yg + pix * p.Cout;
-        for (int c0 = 0; c0 < p.Cout; c0 += 32) {   // two 16-column TMEM loads in flight per wait
-          uint32_t raw[2][16];
-          const bool two = c0 + 16 < p.Cout;
-          tmem_ld16(t_row + (uint32_t)c0, raw[0]);
-          if (two) tmem_ld16(t_row + (uint32_t)(c0 + 16), raw[1]);
-          tmem_ld_wait();
+        // Rows go through a swizzled 16 KB staging tile (128 rows x one 128-byte channel chunk) and leave as coalesced
+        // 16-byte stores, 4 whole rows per warp instruction: a row-per-lane STG.128 touches 32 lines per instruction
+        // (114 L1 tag requests per step on the 64-channel layer, a tenth of the LSU traffic of the whole CTA).
+        constexpr int CE = ROW_BYTES / (int)sizeof(T);          // channels per staging chunk: 64 bf16 / 32 fp32
+        constexpr int PG = 16 * (int)sizeof(T) / 16;            // 16-byte pieces per 16 channels: 2 / 4
+        const uint32_t stg = smem_base + (uint32_t)p.st_off;
+        uint8_t* ybase = reinterpret_cast<uint8_t*>(yg);
+        for (int cc = 0; cc < p.Cout; cc += CE) {
+          const int width = (p.Cout - cc < CE) ? p.Cout - cc : CE;
+          for (int c0 = cc; c0 < cc + width; c0 += 32) {   // two 16-column TMEM loads in flight per wait
+            uint32_t raw[2][16];
+            const bool two = c0 + 16 < cc + width;
+            tmem_ld16(t_row + (uint32_t)c0, raw[0]);
+            if (two) tmem_ld16(t_row + (uint32_t)(c0 + 16), raw[1]);
+            tmem_ld_wait();
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            if (!valid || (h == 1 && !two)) continue;
-            const int cb = c0 + 16 * h;
-            float v[16];
+            for (int h = 0; h < 2; ++h) {
+              if (h == 1 && !two) continue;
+              const int cb = c0 + 16 * h;
+              float v[16];
 #pragma unroll
-            for (int j4 = 0; j4 < 4; ++j4) {
-              const float4 sc = *reinterpret_cast<const float4*>(scale_s + cb + 4 * j4);
-              const float4 bi = *reinterpret_cast<const float4*>(bias_s + cb + 4 * j4);
-              v[4 * j4 + 0] = fmaf(__uint_as_float(raw[h][4 * j4 + 0]), sc.x, bi.x);
-              v[4 * j4 + 1] = fmaf(__uint_as_float(raw[h][4 * j4 + 1]), sc.y, bi.y);
-              v[4 * j4 + 2] = fmaf(__uint_as_float(raw[h][4 * j4 + 2]), sc.z, bi.z);
-              v[4 * j4 + 3] = fmaf(__uint_as_float(raw[h][4 * j4 + 3]), sc.w, bi.w);
+              for (int j4 = 0; j4 < 4; ++j4) {
+                const float4 sc = *reinterpret_cast<const float4*>(scale_s + cb + 4 * j4);
+                const float4 bi = *reinterpret_cast<const float4*>(bias_s + cb + 4 * j4);
+                v[4 * j4 + 0] = fmaf(__uint_as_float(raw[h][4 * j4 + 0]), sc.x, bi.x);
+                v[4 * j4 + 1] = fmaf(__uint_as_float(raw[h][4 * j4 + 1]), sc.y, bi.y);
+                v[4 * j4 + 2] = fmaf(__uint_as_float(raw[h][4 * j4 + 2]), sc.z, bi.z);
+                v[4 * j4 + 3] = fmaf(__uint_as_float(raw[h][4 * j4 + 3]), sc.w, bi.w);
+              }
+              if (p.relu) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+              }
+              uint4 pc[PG];
+              OutConv<T>::pieces(v, pc);
+              const int p0 = ((cb - cc) / 16) * PG;
+#pragma unroll
+              for (int i = 0; i < PG; ++i) sts16(stg + (uint32_t)(r * ROW_BYTES) + (uint32_t)(((p0 + i) ^ (r & 7)) << 4), pc[i]);
             }
-            if (p.relu) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
-            }
-            OutConv<T>::store(yrow + cb, v);
           }
+          named_bar_sync(2, PARAM_THREADS);
+          const int np = width * (int)sizeof(T) / 16;          // pieces per row in this chunk (8 for a full chunk)
+          for (int q = r; q < TILE_PX * np; q += PARAM_THREADS) {
+            const int row = (np == 8) ? (q >> 3) : q / np, j = q - row * np;
+            const int yy = ty0 + (row >> 4), xx = tx0 + (row & (TILE_W - 1));
+            if (yy < p.H && xx < p.W) {
+              const uint4 val = lds16(stg + (uint32_t)(row * ROW_BYTES) + (uint32_t)((j ^ (row & 7)) << 4));
+              *reinterpret_cast<uint4*>(ybase + ((((int64_t)b * p.H + yy) * p.W + xx) * p.Cout + cc) * (int64_t)sizeof(T) + j * 16) = val;
+            }
+          }
+          named_bar_sync(2, PARAM_THREADS);                     // the staging tile is free again
         }
       } else {
         float* prow = p.partial + ((int64_t)(item % p.split) * npix + pix) * p.Cout;
@@ -708,12 +770,13 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   p.num_items = p.num_tiles * p.split;
   p.nchunk = a.Cin / (ROW_BYTES / esize);
   p.b_stage_bytes = a.Cout * ROW_BYTES;
-  p.pbuf_bytes = p.taps_per_item * TILE_PX * 32;
+  p.pbuf_bytes = p.taps_per_item * TILE_PX * (4 + (a.dtype == CPOLY_BF16 ? 8 : 16));
   p.stage_off = ((SMEM_PAR_OFF + 2 * p.pbuf_bytes + 1023) / 1024) * 1024;
   // A ring: at least one stage per sampler group, two when they fit; weight ring: 2..4 stages of Cout x 128 B
-  const int room = SMEM_LIMIT - p.stage_off;
-  // 4 + 2 measured fastest on every neck layer (r02: 8+3 -> 77.7 us, 4+2 -> 72.8 us graph-replayed on 64->64 @256x512): what the
-  // rings do not take stays L1, which the corner gathers live on
+  const int room = SMEM_LIMIT - p.stage_off - A_STAGE_BYTES;   // (the output staging tile)
+  // One A stage per sampler group and two weight stages: with the 12-byte parameter entries more A stages measured
+  // SLOWER (4 / 5 / 6 / 8 stages: 63.5 / 63.5 / 65.6 / 69.7 us) - the sampler is bound by L1 / LSU throughput, not by
+  // waiting for a free stage, and every 32 KB of shared memory is 32 KB less L1 (carveout steps 132 / 164 / 196 / 228 KB).
   int b_stages = 2, a_stages = GROUPS;
   if (const char* e = getenv("CPOLY_TC_STAGES")) a_stages = atoi(e);    // profiling knobs
   if (const char* e = getenv("CPOLY_TC_BSTAGES")) b_stages = atoi(e);
@@ -726,9 +789,10 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   CPOLY_REQUIRE(a_stages * A_STAGE_BYTES + b_stages * p.b_stage_bytes <= room, CPOLY_EUNSUPPORTED, "not enough shared memory for the operand rings");
   p.a_stages = a_stages; p.b_stages = b_stages;
   p.b_off = p.stage_off + a_stages * A_STAGE_BYTES;
+  p.st_off = ((p.b_off + b_stages * p.b_stage_bytes + 1023) / 1024) * 1024;
   p.acc_cols = a.Cout;
   p.tmem_cols = pow2_at_least(2 * a.Cout);
-  const int smem_bytes = p.b_off + b_stages * p.b_stage_bytes + 1024;  // +1 KB alignment slack
+  const int smem_bytes = p.st_off + A_STAGE_BYTES + 1024;  // +1 KB alignment slack
 
   int dev = 0, sms = 0;
   CPOLY_CUDA_OK(cudaGetDevice(&dev));
