@@ -20,6 +20,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <cuda.h>
+
 #include "tc_common.cuh"
 
 namespace cpoly {
@@ -275,6 +277,168 @@ __global__ void __launch_bounds__(OT_THREADS) offset_conv3x3_tc_kernel(const Off
   if (warp == 0) { tc_fence_after(); tmem_dealloc(tmem_acc, 32u); }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// TMA-fed, pipelined version (default when the driver offers cuTensorMapEncodeTiled).  Same operand layout and MMAs as
+// offset_conv3x3_tc_kernel, but the three shifted windows arrive as three `cp.async.bulk.tensor.4d` box loads
+// (64 channels x 16 pixels x 10 rows, SWIZZLE_128B, out-of-image pixels zero-filled by the TMA unit = the convolution's
+// padding) issued by one thread, into a two-stage ring; one persistent CTA per SM:
+//   warp 4     producer + MMA issuer (one elected lane): load of item t+1 is in flight while the 36 MMAs of item t run
+//   warps 0-3  epilogue: accumulator (two of them, 2 x 32 TMEM columns) -> + bias -> NHWC stores, overlapping the next tile
+// The cp.async version spent its time issuing 30 16-byte copies per thread and then waiting for them with nothing else
+// to do (22 us for the 64-channel 256x512 layer, launch list of r02).
+constexpr int OP_THREADS = 160;
+constexpr int OP_MAX_STAGES = 3;
+// one 64-channel chunk: the weights stay resident and three window stages fit (216 KB); more chunks: a weight chunk
+// travels with every item, two stages of windows + weights (192 KB)
+constexpr int OP_SMEM_1 = 3 * OT_WIN_BYTES + OC_WGT_BYTES + 1024, OP_SMEM_N = 2 * (OT_WIN_BYTES + OC_WGT_BYTES) + 1024;
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* tmap, int c0, int c1, int c2, int c3, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar)
+      : "memory");
+}
+
+__global__ void __launch_bounds__(OP_THREADS) offset_conv3x3_tma_kernel(const OffsetConvParams p, const __grid_constant__ CUtensorMap tmap) {
+  using namespace tc;
+  extern __shared__ uint8_t op_smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2 * OP_MAX_STAGES + 4];   // full[3], empty[3], accfull[2], accempty[2]
+  __shared__ uint32_t tmem_ptr_s;
+  uint8_t* smem = op_smem_raw + ((1024u - (smem_u32(op_smem_raw) & 1023u)) & 1023u);
+  const uint32_t stage0 = smem_u32(smem);
+  const uint32_t bar_full = smem_u32(&bars[0]), bar_empty = smem_u32(&bars[OP_MAX_STAGES]), bar_afull = smem_u32(&bars[2 * OP_MAX_STAGES]),
+                 bar_aempty = smem_u32(&bars[2 * OP_MAX_STAGES + 2]);
+  const int NS = p.wgt_stages;                                        // window stages (3 when one chunk, else 2)
+  const uint32_t wgt0 = stage0 + (uint32_t)(NS * OT_WIN_BYTES);       // weight slots follow the windows
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tiles_per_img = p.tiles_x * p.tiles_y;
+  const int my_tiles = ((int)blockIdx.x < p.num_tiles) ? (p.num_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const int n_items = my_tiles * p.nchunk;
+
+  if (tid == 0) {
+    for (int i = 0; i < OP_MAX_STAGES; ++i) {
+      mbar_init(bar_full + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_afull + 8 * i, 1);
+      mbar_init(bar_aempty + 8 * i, 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 4) tmem_alloc(smem_u32(&tmem_ptr_s), 64u);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_ptr_s;
+
+  if (warp == 4) {
+    // ============================================================ producer + MMA issuer
+    const uint32_t idesc = umma_idesc(false, 128, OC_N);
+    // item t -> window stage t % NS; with several chunks a weight chunk travels with the item into the stage's slot
+    auto issue_load = [&](int t) {
+      const int s = t % NS;
+      const int tile = (int)blockIdx.x + (t / p.nchunk) * (int)gridDim.x, cc = t % p.nchunk;
+      const int b = tile / tiles_per_img, trem = tile - b * tiles_per_img;
+      const int ty0 = (trem / p.tiles_x) * OC_TH, tx0 = (trem % p.tiles_x) * OC_TW;
+      const bool wload = p.nchunk > 1 || t == 0;
+      const uint32_t dst = stage0 + (uint32_t)(s * OT_WIN_BYTES);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(bar_full + 8 * s, (uint32_t)(OT_WIN_BYTES + (wload ? OC_WGT_BYTES : 0)));
+#pragma unroll
+        for (int sh = 0; sh < 3; ++sh) tma_load_4d(dst + (uint32_t)(sh * OT_WIN1), &tmap, cc * OC_KC, tx0 - 1 + sh, ty0 - 1, b, bar_full + 8 * s);
+        if (wload)
+          bulk_copy_g2s(wgt0 + (uint32_t)((p.nchunk > 1 ? s : 0) * OC_WGT_BYTES), p.wpacked + (size_t)cc * (OC_WGT_BYTES / 16), (uint32_t)OC_WGT_BYTES,
+                        bar_full + 8 * s);
+      }
+      __syncwarp();
+    };
+    for (int t = 0; t < NS - 1 && t < n_items; ++t) issue_load(t);
+    for (int t = 0; t < n_items; ++t) {
+      const int s = t % NS, cc = t % p.nchunk, tl = t / p.nchunk, acc = tl & 1;
+      if (t + NS - 1 < n_items) {
+        // the stage of item t + NS - 1 is the one item t - 1 used: its MMAs (committed one iteration ago) must have read it
+        if (t >= 1) mbar_wait(bar_empty + 8 * ((t - 1) % NS), (uint32_t)((t - 1) / NS) & 1u, 20);
+        issue_load(t + NS - 1);
+      }
+      mbar_wait(bar_full + 8 * s, (uint32_t)(t / NS) & 1u, 20);
+      if (cc == 0 && tl >= 2) mbar_wait(bar_aempty + 8 * acc, (uint32_t)((tl >> 1) - 1) & 1u, 20);   // epilogue drained this accumulator
+      tc_fence_after();
+      const uint32_t win = stage0 + (uint32_t)(s * OT_WIN_BYTES), wgt = wgt0 + (uint32_t)((p.nchunk > 1 ? s : 0) * OC_WGT_BYTES),
+                     d_tmem = tmem_base + (uint32_t)(acc * OC_N);
+      if (elect_one()) {
+#pragma unroll 1
+        for (int tap = 0; tap < 9; ++tap) {
+          const int ti = tap / 3, tj = tap - 3 * ti;
+          const uint64_t adesc = umma_desc_sw128(win + tj * OT_WIN1 + ti * (OC_TW * 128));
+          const uint64_t bdesc = umma_desc_sw128(wgt + tap * (OC_N * 128));
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            umma<false>(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (cc | tap | kk) != 0 ? 1u : 0u);
+        }
+        umma_commit(bar_empty + 8 * s);
+        if (cc == p.nchunk - 1) umma_commit(bar_afull + 8 * acc);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ============================================================ epilogue (warps 0-3: TMEM lanes 32 * warp ..)
+    float bias_r[OC_N];
+#pragma unroll
+    for (int n = 0; n < OC_N; ++n) bias_r[n] = __ldg(p.bias + n);
+    for (int tl = 0; tl < my_tiles; ++tl) {
+      const int acc = tl & 1;
+      const int tile = (int)blockIdx.x + tl * (int)gridDim.x;
+      const int b = tile / tiles_per_img, trem = tile - b * tiles_per_img;
+      const int ty0 = (trem / p.tiles_x) * OC_TH, tx0 = (trem % p.tiles_x) * OC_TW;
+      const int r = warp * 32 + lane;                          // TMEM lane = M row = pixel (r / 16, r % 16) of the tile
+      const int y = ty0 + (r >> 4), x = tx0 + (r & 15);
+      mbar_wait(bar_afull + 8 * acc, (uint32_t)(tl >> 1) & 1u, 50);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc * OC_N);
+      uint32_t v0[16], v1[16];
+      tmem_ld16(t_row, v0);
+      tmem_ld16(t_row + 16u, v1);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(bar_aempty + 8 * acc);                       // the values are in registers: the accumulator is free
+      if (y < p.H && x < p.W) {
+        const size_t pix = (size_t)(b * p.H + y) * p.W + x;
+        float o[32];
+#pragma unroll
+        for (int n = 0; n < 16; ++n) { o[n] = __uint_as_float(v0[n]) + bias_r[n]; o[16 + n] = __uint_as_float(v1[n]) + bias_r[16 + n]; }
+        if (p.out_bf16) {
+          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.om) + pix * OC_N);
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            dst[q] = make_uint4(pack_bf16x2(o[8 * q], o[8 * q + 1]), pack_bf16x2(o[8 * q + 2], o[8 * q + 3]), pack_bf16x2(o[8 * q + 4], o[8 * q + 5]),
+                                pack_bf16x2(o[8 * q + 6], o[8 * q + 7]));
+        } else {
+          float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.om) + pix * OC_N);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) dst[q] = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) { tc_fence_after(); tmem_dealloc(tmem_base, 64u); }
+}
+
+typedef CUresult (*OcEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+OcEncodeTiledFn oc_encode_tiled_fn() {
+  static OcEncodeTiledFn fn = []() -> OcEncodeTiledFn {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return reinterpret_cast<OcEncodeTiledFn>(sym);
+  }();
+  return fn;
+}
 // conv_offset_mask.weight (n_out <= 32, Cin, 3, 3), any float dtype as fp32 -> [Cin/64][9][32][8 pieces] bf16, piece j of
 // row n stored at j ^ (n & 7); rows >= n_out are zero.
 __global__ void offset_conv_pack_kernel(const float* __restrict__ w, uint4* __restrict__ out, int Cin, int n_out) {
@@ -322,6 +486,25 @@ int offset_conv_launch(const cpoly_offset_conv_args& a, cudaStream_t stream) {
   CPOLY_CUDA_OK(cudaGetDevice(&dev));
   CPOLY_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   const char* e = getenv("CPOLY_OFFSET_CONV");
+  const bool aligned = (reinterpret_cast<uintptr_t>(a.x) & 15) == 0 && (int64_t)a.H * a.W * a.Cin * 2 < (1LL << 40);
+  if (!e && aligned && oc_encode_tiled_fn()) {     // default: TMA-fed pipeline; CPOLY_OFFSET_CONV=cpasync | mma keep the older kernels
+    CUtensorMap tmap;
+    const cuuint64_t dims[4] = {(cuuint64_t)a.Cin, (cuuint64_t)a.W, (cuuint64_t)a.H, (cuuint64_t)a.B};
+    const cuuint64_t strides[3] = {(cuuint64_t)a.Cin * 2, (cuuint64_t)a.W * a.Cin * 2, (cuuint64_t)a.H * a.W * a.Cin * 2};
+    const cuuint32_t box[4] = {(cuuint32_t)OC_KC, (cuuint32_t)OC_TW, (cuuint32_t)OC_WH, 1u};
+    const cuuint32_t estr[4] = {1u, 1u, 1u, 1u};
+    const CUresult cr = oc_encode_tiled_fn()(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(a.x), dims, strides, box, estr,
+                                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CPOLY_REQUIRE(cr == CUDA_SUCCESS, CPOLY_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)cr);
+    p.wgt_stages = p.nchunk == 1 ? 3 : 2;           // (window stages of this kernel)
+    if (const char* st = getenv("CPOLY_OC_STAGES")) { if (atoi(st) == 2) p.wgt_stages = 2; }   // profiling knob
+    const int smem = p.nchunk == 1 ? p.wgt_stages * OT_WIN_BYTES + OC_WGT_BYTES + 1024 : OP_SMEM_N;
+    CPOLY_CUDA_OK(cudaFuncSetAttribute(offset_conv3x3_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OP_SMEM_1 > OP_SMEM_N ? OP_SMEM_1 : OP_SMEM_N));
+    const int grid = p.num_tiles < sms ? p.num_tiles : sms;
+    offset_conv3x3_tma_kernel<<<grid, OP_THREADS, smem, stream>>>(p, tmap);
+    return check_launch("offset_conv3x3_tma_kernel");
+  }
   if (!(e && strcmp(e, "mma") == 0)) {            // default: tcgen05; CPOLY_OFFSET_CONV=mma keeps the warp-level kernel
     p.wgt_stages = 1;
     CPOLY_CUDA_OK(cudaFuncSetAttribute(offset_conv3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, OT_SMEM));
