@@ -302,6 +302,9 @@ def train_step_bench(torch, dist, world, rank, steps=5, warmup=3, batch=16):
     net = PolydetDLA34().cuda().to(memory_format=torch.channels_last)
     calibrate_random_init(net, 128, 256)
     use_training_upsamplers(net)
+    if os.environ.get("CPOLY_NATIVE_BN") != "1":        # A/B knob: keep PyTorch's BatchNorm kernels
+        from centerpoly_b200.batchnorm import use_training_batchnorm
+        use_training_batchnorm(net)                      # 55 BatchNorm2d (+ the ReLU of Sequential(BN, ReLU)) on csrc/batchnorm.cu
     trainer = DataParallelTrainer(net, lr=2e-4, dtype=torch.bfloat16, loss_fn=polydet_l1_iou_loss)
     data = synthetic_batch(batch, 512, 1024, device="cuda", seed=1000 + rank, rep="polar")
     data["input"] = data["input"].contiguous(memory_format=torch.channels_last)

@@ -27,6 +27,7 @@ EXPORTED_SYMBOLS = (
     "cpoly_stem_pack_weights", "cpoly_stem_conv7x7_forward", "cpoly_maxpool2x2_nhwc_forward",
     "cpoly_offset_conv_packed_bytes", "cpoly_offset_conv_pack_weights", "cpoly_offset_conv_forward",
     "cpoly_decode_static_max_bytes", "cpoly_decode_static",
+    "cpoly_bn_eligible", "cpoly_bn_workspace_bytes", "cpoly_bn_train_forward", "cpoly_bn_train_backward",
 )
 
 
@@ -90,6 +91,19 @@ class OffsetConvArgs(Structure):
         ("x", c_void_p), ("weight_packed", c_void_p), ("bias", c_void_p), ("om", c_void_p)]
 
 
+class BnFwdArgs(Structure):
+    _fields_ = [("N", c_int64), ("C", c_int32), ("dtype", c_int32), ("relu", c_int32), ("reserved0", c_int32),
+                ("x", c_void_p), ("y", c_void_p), ("weight", c_void_p), ("bias", c_void_p), ("running_mean", c_void_p),
+                ("running_var", c_void_p), ("momentum", c_float), ("eps", c_float), ("save", c_void_p),
+                ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+
+
+class BnBwdArgs(Structure):
+    _fields_ = [("N", c_int64), ("C", c_int32), ("dtype", c_int32), ("relu", c_int32), ("reserved0", c_int32),
+                ("x", c_void_p), ("gy", c_void_p), ("gx", c_void_p), ("save", c_void_p), ("gweight", c_void_p),
+                ("gbias", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+
+
 class UpsampleBwdArgs(Structure):
     _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "f", "dtype")] + [
         ("x", Tensor4), ("gy", Tensor4), ("weight", c_void_p), ("gx", Tensor4), ("gweight", c_void_p)]
@@ -136,6 +150,14 @@ def lib():
         L.cpoly_decode_static_max_bytes.argtypes = []
         L.cpoly_decode_static.restype = c_int32
         L.cpoly_decode_static.argtypes = [POINTER(DecodeArgs), c_void_p]
+        L.cpoly_bn_eligible.restype = c_int32
+        L.cpoly_bn_eligible.argtypes = [c_int32, c_int32]
+        L.cpoly_bn_workspace_bytes.restype = c_size_t
+        L.cpoly_bn_workspace_bytes.argtypes = [c_int32]
+        L.cpoly_bn_train_forward.restype = c_int32
+        L.cpoly_bn_train_forward.argtypes = [POINTER(BnFwdArgs), c_void_p]
+        L.cpoly_bn_train_backward.restype = c_int32
+        L.cpoly_bn_train_backward.argtypes = [POINTER(BnBwdArgs), c_void_p]
         L.cpoly_rasterise_workspace_bytes.restype = c_size_t
         L.cpoly_rasterise_workspace_bytes.argtypes = [c_int32] * 2
         L.cpoly_rasterise.restype = c_int32
@@ -158,7 +180,7 @@ def lib():
         L.cpoly_offset_conv_pack_weights.argtypes = [c_void_p, c_void_p, c_int32, c_int32, c_void_p]
         L.cpoly_offset_conv_forward.restype = c_int32
         L.cpoly_offset_conv_forward.argtypes = [POINTER(OffsetConvArgs), c_void_p]
-        if L.cpoly_abi_version() != 9:
+        if L.cpoly_abi_version() != 10:
             raise RuntimeError("libcpoly.so ABI version mismatch; rebuild with `python -m centerpoly_b200.build --force`")
         _lib = L
     return _lib

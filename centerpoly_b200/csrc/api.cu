@@ -163,6 +163,33 @@ int cpoly_decode(const cpoly_decode_args* a, cpoly_stream_t stream) {
   return decode_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int cpoly_bn_eligible(int32_t C, int32_t dtype) { return bn_eligible(C, dtype) ? 1 : 0; }
+size_t cpoly_bn_workspace_bytes(int32_t C) { return bn_workspace_bytes(C); }
+
+int cpoly_bn_train_forward(const cpoly_bn_fwd_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->N >= 0 && a->C > 0, CPOLY_EINVAL, "bad dims");
+  CPOLY_REQUIRE(a->dtype == CPOLY_F32 || a->dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", a->dtype);
+  CPOLY_REQUIRE(a->x && a->y && a->save, CPOLY_EINVAL, "NULL pointer");
+  CPOLY_REQUIRE(((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(a->y)) & 15) == 0, CPOLY_EINVAL, "x / y must be 16-byte aligned");
+  CPOLY_REQUIRE(a->N > 1, CPOLY_EINVAL, "batch norm in training mode needs more than one value per channel");
+  CPOLY_REQUIRE(a->workspace && a->workspace_bytes >= bn_workspace_bytes(a->C) && (reinterpret_cast<uintptr_t>(a->workspace) & 15) == 0, CPOLY_EWORKSPACE,
+                "batch norm workspace too small or misaligned: need %zu bytes", bn_workspace_bytes(a->C));
+  return bn_train_forward_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int cpoly_bn_train_backward(const cpoly_bn_bwd_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->N > 0 && a->C > 0, CPOLY_EINVAL, "bad dims");
+  CPOLY_REQUIRE(a->dtype == CPOLY_F32 || a->dtype == CPOLY_BF16, CPOLY_EINVAL, "unsupported dtype %d", a->dtype);
+  CPOLY_REQUIRE(a->x && a->gy && a->save, CPOLY_EINVAL, "NULL pointer");
+  CPOLY_REQUIRE(((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(a->gy) | reinterpret_cast<uintptr_t>(a->gx)) & 15) == 0, CPOLY_EINVAL,
+                "x / gy / gx must be 16-byte aligned");
+  CPOLY_REQUIRE(a->workspace && a->workspace_bytes >= bn_workspace_bytes(a->C) && (reinterpret_cast<uintptr_t>(a->workspace) & 15) == 0, CPOLY_EWORKSPACE,
+                "batch norm workspace too small or misaligned: need %zu bytes", bn_workspace_bytes(a->C));
+  return bn_train_backward_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
 size_t cpoly_decode_static_max_bytes(void) { return CPOLY_DECODE_STATIC_BYTES; }
 
 int cpoly_decode_static(const cpoly_decode_args* a, cpoly_stream_t stream) {

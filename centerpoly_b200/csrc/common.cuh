@@ -138,7 +138,11 @@ int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream);
 int idaup_upsample_backward_launch(const cpoly_upsample_bwd_args& a, cudaStream_t stream);
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K);
 int decode_launch(const cpoly_decode_args& a, cudaStream_t stream);
-int decode_static_scratch(void** ptr);   // device address of the file-scope scratch of cpoly_decode_static (this device)
+int decode_static_scratch(void** ptr);
+bool bn_eligible(int C, int dtype);
+size_t bn_workspace_bytes(int C);
+int bn_train_forward_launch(const cpoly_bn_fwd_args& a, cudaStream_t stream);
+int bn_train_backward_launch(const cpoly_bn_bwd_args& a, cudaStream_t stream);   // device address of the file-scope scratch of cpoly_decode_static (this device)
 size_t raster_workspace_bytes(int B, int K);
 int raster_launch(const cpoly_raster_args& a, cudaStream_t stream);
 int poly_iou_forward_launch(const cpoly_poly_iou_args& a, cudaStream_t stream);

@@ -55,7 +55,7 @@
 extern "C" {
 #endif
 
-#define CPOLY_ABI_VERSION 9
+#define CPOLY_ABI_VERSION 10
 
 /* element types */
 #define CPOLY_F32 0
@@ -344,6 +344,54 @@ size_t cpoly_offset_conv_packed_bytes(int32_t Cin);   /* 0 when the shape has no
 /* weight: fp32 contiguous (n_out <= 32, Cin, 3, 3) */
 int cpoly_offset_conv_pack_weights(const float* weight, void* packed, int32_t Cin, int32_t n_out, cpoly_stream_t stream);
 int cpoly_offset_conv_forward(const cpoly_offset_conv_args* args, cpoly_stream_t stream);
+
+/* ---- training-mode BatchNorm2d (+ fused ReLU) on dense NHWC activations (ABI v10) -----------------------------------
+ * Replaces `nn.BatchNorm2d(planes, momentum=BN_MOMENTUM)` in training mode at the sites of the DLA-34 / DLAUp / IDAUp
+ * network (src/lib/models/networks/pose_dla_dcn.py:31-47 BasicBlock, :143-160 Root, :231-236 base_layer, :247-252 conv
+ * levels) and the `actf = Sequential(BatchNorm2d, ReLU)` of DeformConv (:345-359; relu = 1 fuses its ReLU).  PyTorch
+ * semantics: batch statistics with the biased variance for the normalisation, running_mean / running_var updated in
+ * place with `momentum` and the UNBIASED variance; backward returns the input gradient, gweight = sum(g * xhat) and
+ * gbias = sum(g) with g = gy * [y > 0] when relu.  x, y, gy, gx: dense NHWC (N = B*H*W rows of C channels), fp32 or
+ * bf16; weight / bias / running stats / save / gweight / gbias fp32.  C / (16 / sizeof(element)) must be a power of two
+ * <= 256 (cpoly_bn_eligible); every reduction runs in a fixed order (bit-reproducible). */
+typedef struct {
+  int64_t N;                 /* rows (B*H*W) */
+  int32_t C;
+  int32_t dtype;             /* CPOLY_F32 or CPOLY_BF16 */
+  int32_t relu;
+  int32_t reserved0;
+  const void* x;
+  void* y;
+  const float* weight;       /* gamma, NULL = 1 */
+  const float* bias;         /* beta, NULL = 0 */
+  float* running_mean;       /* updated in place, may be NULL */
+  float* running_var;
+  float momentum, eps;
+  float* save;               /* out: [4][C] = mean, invstd, scale, shift (kept for the backward) */
+  void* workspace;           /* >= cpoly_bn_workspace_bytes(C), 16-byte aligned */
+  size_t workspace_bytes;
+} cpoly_bn_fwd_args;
+
+typedef struct {
+  int64_t N;
+  int32_t C;
+  int32_t dtype;
+  int32_t relu;
+  int32_t reserved0;
+  const void* x;             /* the forward's input */
+  const void* gy;
+  void* gx;                  /* may be NULL (no input gradient wanted) */
+  const float* save;         /* the forward's save */
+  float* gweight;            /* [C], may be NULL */
+  float* gbias;              /* [C], may be NULL */
+  void* workspace;
+  size_t workspace_bytes;
+} cpoly_bn_bwd_args;
+
+int cpoly_bn_eligible(int32_t C, int32_t dtype);
+size_t cpoly_bn_workspace_bytes(int32_t C);
+int cpoly_bn_train_forward(const cpoly_bn_fwd_args* args, cpoly_stream_t stream);
+int cpoly_bn_train_backward(const cpoly_bn_bwd_args* args, cpoly_stream_t stream);
 
 #ifdef __cplusplus
 }

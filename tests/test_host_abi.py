@@ -18,7 +18,7 @@ def test_library_exports_every_declared_symbol():
     L = ctypes.CDLL(_lib.LIB_PATH)
     for sym in declared:
         assert hasattr(L, sym), sym
-    assert _lib.lib().cpoly_abi_version() == 9
+    assert _lib.lib().cpoly_abi_version() == 10
 
 
 def test_struct_layouts_match_header(tmp_path):

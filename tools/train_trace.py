@@ -10,6 +10,11 @@ torch.backends.cudnn.benchmark = True
 torch.manual_seed(317)
 net = PolydetDLA34().cuda().to(memory_format=torch.channels_last)
 calibrate_random_init(net, 128, 256)
+from centerpoly_b200.neck import use_training_upsamplers
+from centerpoly_b200.batchnorm import use_training_batchnorm
+use_training_upsamplers(net)
+if os.environ.get("CPOLY_NATIVE_BN") != "1":
+    use_training_batchnorm(net)
 tr = DataParallelTrainer(net, lr=2e-4, dtype=torch.bfloat16, loss_fn=polydet_l1_iou_loss)
 batch = synthetic_batch(16, 512, 1024, device="cuda", seed=1, rep="polar")
 batch["input"] = batch["input"].contiguous(memory_format=torch.channels_last)
