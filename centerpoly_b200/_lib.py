@@ -48,7 +48,8 @@ class DcnFwdArgs(Structure):
 
 class DcnBwdArgs(Structure):
     _fields_ = [("f", DcnFwdArgs), ("gout", Tensor4), ("gx", Tensor4), ("goffset", Tensor4), ("gmask", Tensor4),
-                ("gweight", c_void_p), ("gbias", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+                ("gweight", c_void_p), ("gbias", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+                ("gom_dtype", c_int32), ("reserved1", c_int32)]
 
 
 class UpsampleArgs(Structure):

@@ -118,6 +118,7 @@ int cpoly_dcn_backward(const cpoly_dcn_bwd_args* args, cpoly_stream_t stream) {
   CPOLY_REQUIRE(args, CPOLY_EINVAL, "NULL args");
   if (int rc = validate_dcn(args->f, false)) return rc;
   CPOLY_REQUIRE(args->gout.ptr && args->f.weight, CPOLY_EINVAL, "NULL grad_output / weight");
+  CPOLY_REQUIRE(args->gom_dtype == CPOLY_F32 || args->gom_dtype == CPOLY_BF16, CPOLY_EINVAL, "bad gom_dtype %d", args->gom_dtype);
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const bool tcw = use_tc_wgrad(*args), tcd = use_tc_dgrad(*args);
   CPOLY_REQUIRE(args->f.path != CPOLY_PATH_TCGEN05 || ((tcw || !args->gweight) && (tcd || !(args->gx.ptr || args->goffset.ptr || args->gmask.ptr))),

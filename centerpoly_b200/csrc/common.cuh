@@ -57,6 +57,12 @@ __device__ __forceinline__ float ld_dyn(const void* base, int64_t idx, int dtype
                              : __ldg(reinterpret_cast<const float*>(base) + idx);
 }
 
+// write element `idx` of a buffer whose element type is only known at run time (goffset / gmask)
+__device__ __forceinline__ void st_dyn(void* base, int64_t idx, float v, int dtype) {
+  if (dtype == CPOLY_BF16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16(v);
+  else reinterpret_cast<float*>(base)[idx] = v;
+}
+
 __device__ __forceinline__ float sigmoidf_accurate(float v) { return 1.0f / (1.0f + expf(-v)); }
 
 // ---- geometry shared by every DCN kernel ---------------------------------------------------------
@@ -64,6 +70,7 @@ struct DcnGeom {
   int B, Cin, Cout, H, W, Ho, Wo;
   int kh, kw, sh, sw, ph, pw, dh, dw, dg;
   int om_dtype, mask_is_logit;
+  int gom_dtype;   // backward only: element type of goffset / gmask
   const float* offset_bias;
   const float* mask_bias;
 };
@@ -75,7 +82,7 @@ inline DcnGeom make_geom(const cpoly_dcn_fwd_args& a) {
   g.dh = a.dil_h; g.dw = a.dil_w; g.dg = a.deformable_groups;
   g.Ho = (a.H + 2 * a.pad_h - (a.dil_h * (a.kh - 1) + 1)) / a.stride_h + 1;
   g.Wo = (a.W + 2 * a.pad_w - (a.dil_w * (a.kw - 1) + 1)) / a.stride_w + 1;
-  g.om_dtype = a.om_dtype; g.mask_is_logit = a.mask_is_logit;
+  g.om_dtype = a.om_dtype; g.mask_is_logit = a.mask_is_logit; g.gom_dtype = CPOLY_F32;
   g.offset_bias = a.offset_bias; g.mask_bias = a.mask_bias;
   return g;
 }

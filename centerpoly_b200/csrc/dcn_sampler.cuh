@@ -20,6 +20,7 @@ struct Geom {
   const float* mask_bias;
   int B, Cin, Cout, H, W;
   int om_dtype, mask_is_logit;
+  int gom_dtype;   // backward only: element type of goffset / gmask
   int tiles_x, tiles_y, num_tiles;
 };
 

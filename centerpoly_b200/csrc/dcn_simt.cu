@@ -165,8 +165,8 @@ __global__ void __launch_bounds__(NT) dcn_bwd_data_simt_kernel(DcnGeom g, cpoly_
   const T* xp = reinterpret_cast<const T*>(x.ptr);
   const T* gop = reinterpret_cast<const T*>(gout.ptr);
   float* gxp = reinterpret_cast<float*>(gx.ptr);
-  float* goffp = reinterpret_cast<float*>(goffset.ptr);
-  float* gmp = reinterpret_cast<float*>(gmask.ptr);
+  void* goffp = goffset.ptr;
+  void* gmp = gmask.ptr;
 
   // gout addressing of this thread's A-load slots is tap independent
   for (int grp = 0; grp < g.dg; ++grp)
@@ -262,12 +262,12 @@ __global__ void __launch_bounds__(NT) dcn_bwd_data_simt_kernel(DcnGeom g, cpoly_
           if (gmp) {
             float gm = am[i];
             if (g.mask_is_logit) gm *= m * (1.f - m);
-            gmp[(int64_t)b * gmask.sb + (int64_t)(grp * Tn + tap) * gmask.sc + (int64_t)ho * gmask.sh + (int64_t)wo * gmask.sw] = gm;
+            st_dyn(gmp, (int64_t)b * gmask.sb + (int64_t)(grp * Tn + tap) * gmask.sc + (int64_t)ho * gmask.sh + (int64_t)wo * gmask.sw, gm, g.gom_dtype);
           }
           if (goffp) {
             const int64_t ob = (int64_t)b * goffset.sb + (int64_t)ho * goffset.sh + (int64_t)wo * goffset.sw;
-            goffp[ob + (int64_t)(grp * 2 * Tn + 2 * tap) * goffset.sc] = m * ay[i];
-            goffp[ob + (int64_t)(grp * 2 * Tn + 2 * tap + 1) * goffset.sc] = m * ax[i];
+            st_dyn(goffp, ob + (int64_t)(grp * 2 * Tn + 2 * tap) * goffset.sc, m * ay[i], g.gom_dtype);
+            st_dyn(goffp, ob + (int64_t)(grp * 2 * Tn + 2 * tap + 1) * goffset.sc, m * ax[i], g.gom_dtype);
           }
         }
       }
@@ -498,7 +498,8 @@ size_t dcn_backward_simt_workspace(const cpoly_dcn_bwd_args& a) {
 }
 
 int dcn_backward_simt(const cpoly_dcn_bwd_args& a, cudaStream_t stream) {
-  const DcnGeom g = make_geom(a.f);
+  DcnGeom g = make_geom(a.f);
+  g.gom_dtype = a.gom_dtype;
   const int64_t npix = (int64_t)g.B * g.Ho * g.Wo;
   const bool bf = a.f.dtype == CPOLY_BF16;
   if (a.gx.ptr) {

@@ -436,8 +436,8 @@ __global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
     const uint8_t* xb = reinterpret_cast<const uint8_t*>(p.g.x);
     const uint8_t* gb = reinterpret_cast<const uint8_t*>(p.gout);
     const int row_pieces = p.g.Cout * (int)sizeof(T) / 16;
-    float* gmp = reinterpret_cast<float*>(p.gmask.ptr);
-    float* gop = reinterpret_cast<float*>(p.goffset.ptr);
+    void* gmp = p.gmask.ptr;
+    void* gop = p.goffset.ptr;
     RingCursor ra;
     uint32_t nblk = 0;   // blocks processed by this CTA so far (D / gcol buffer cursor)
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
@@ -561,12 +561,12 @@ __global__ void __maxnreg__(80) dcn_dgrad_tc_kernel(const DgradParams p) {
                 if (gmp) {
                   float gm = sm[pass];
                   if (p.g.mask_is_logit) gm *= m * (1.f - m);
-                  gmp[(int64_t)b * p.gmask.sb + (int64_t)k * p.gmask.sc + (int64_t)y * p.gmask.sh + (int64_t)x * p.gmask.sw] = gm;
+                  st_dyn(gmp, (int64_t)b * p.gmask.sb + (int64_t)k * p.gmask.sc + (int64_t)y * p.gmask.sh + (int64_t)x * p.gmask.sw, gm, p.g.gom_dtype);
                 }
                 if (gop) {
                   const int64_t ob = (int64_t)b * p.goffset.sb + (int64_t)y * p.goffset.sh + (int64_t)x * p.goffset.sw;
-                  gop[ob + (int64_t)(2 * k) * p.goffset.sc] = m * sy[pass];
-                  gop[ob + (int64_t)(2 * k + 1) * p.goffset.sc] = m * sx[pass];
+                  st_dyn(gop, ob + (int64_t)(2 * k) * p.goffset.sc, m * sy[pass], p.g.gom_dtype);
+                  st_dyn(gop, ob + (int64_t)(2 * k + 1) * p.goffset.sc, m * sx[pass], p.g.gom_dtype);
                 }
               }
             }
@@ -782,7 +782,7 @@ int dcn_dgrad_tc(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_
   DgradParams p;
   p.g.x = f.x.ptr; p.g.offset = f.offset; p.g.mask = f.mask; p.g.offset_bias = f.offset_bias; p.g.mask_bias = f.mask_bias;
   p.g.B = f.B; p.g.Cin = f.Cin; p.g.Cout = f.Cout; p.g.H = f.H; p.g.W = f.W;
-  p.g.om_dtype = f.om_dtype; p.g.mask_is_logit = f.mask_is_logit;
+  p.g.om_dtype = f.om_dtype; p.g.mask_is_logit = f.mask_is_logit; p.g.gom_dtype = a.gom_dtype;
   p.g.tiles_x = (f.W + TILE_W - 1) / TILE_W; p.g.tiles_y = (f.H + TILE_H - 1) / TILE_H;
   p.g.num_tiles = f.B * p.g.tiles_x * p.g.tiles_y;
   p.gout = a.gout.ptr; p.wpacked = workspace; p.gcol = a.gx.ptr ? c2i_ws : nullptr;

@@ -280,7 +280,9 @@ class _DCNFused(Function):
         x, om, weight, bias = ctx.saved_tensors
         n_off = om.shape[1] // 3 * 2
         needs = ctx.needs_input_grad
-        gom = torch.empty_like(om, dtype=torch.float32) if needs[1] else None
+        # d/d(om) in om's own dtype when that is bf16 (autocast): the kernels round once on store, no 27-channel cast pass
+        gom_dt = torch.bfloat16 if om.dtype == torch.bfloat16 else torch.float32
+        gom = torch.empty_like(om, dtype=gom_dt) if needs[1] else None
         # the kernels write straight into the two channel ranges of d/d(om)
         dev = x.device
         L = _lib.lib()
@@ -297,6 +299,7 @@ class _DCNFused(Function):
             b.gx = _lib.t4(gx)
             b.goffset = _lib.t4(gom[:, :n_off] if gom is not None else None)
             b.gmask = _lib.t4(gom[:, n_off:] if gom is not None else None)
+            b.gom_dtype = _lib.BF16 if gom_dt == torch.bfloat16 else _lib.F32
             b.gweight = gw.data_ptr() if gw is not None else None
             b.gbias = gb.data_ptr() if gb is not None else None
             ws = _lib.workspace(L.cpoly_dcn_backward_workspace_bytes(byref(b)), dev)

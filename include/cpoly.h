@@ -122,7 +122,7 @@ typedef struct {
 typedef struct {
   cpoly_dcn_fwd_args f;  /* forward problem (f.y is ignored) */
   cpoly_tensor4 gout;    /* (B,Cout,Ho,Wo), element type f.dtype */
-  /* outputs — all fp32, any may have ptr == NULL to skip it (ctx.needs_input_grad) */
+  /* outputs — fp32 (goffset / gmask: see gom_dtype), any may have ptr == NULL to skip it (ctx.needs_input_grad) */
   cpoly_tensor4 gx;      /* (B,Cin,H,W)      */
   cpoly_tensor4 goffset; /* like offset      */
   cpoly_tensor4 gmask;   /* like mask; d/d(logit) when f.mask_is_logit */
@@ -130,6 +130,9 @@ typedef struct {
   float* gbias;          /* (Cout) */
   void* workspace;       /* >= cpoly_dcn_backward_workspace_bytes(&args) bytes, 256-byte aligned */
   size_t workspace_bytes;
+  int32_t gom_dtype;     /* ABI v10: element type of goffset / gmask, CPOLY_F32 (0, default) or CPOLY_BF16 - lets an autocast
+                          * training step receive d/d(offset conv output) in the dtype that conv ran in, without a cast pass */
+  int32_t reserved1;
 } cpoly_dcn_bwd_args;
 
 int cpoly_abi_version(void);

@@ -315,3 +315,26 @@ def test_pack_cache_is_not_confused_by_recycled_addresses():
     w.mul_(3.0)
     y1 = cp.dcn_v2_conv(x, off, msk, w, None, 1, 1, 1, 1).float().cpu()
     gate(y1.numpy(), (3.0 * y0).numpy(), 2e-3, "in-place update")
+
+
+def test_fused_module_backward_returns_offset_gradients_in_the_producers_dtype():
+    """bf16 `om` (autocast training): d/d(om) comes back as bf16 straight from the kernels (cpoly_dcn_bwd_args.gom_dtype)
+    and equals the fp32 result up to one bf16 rounding."""
+    from centerpoly_b200.dcn_v2 import _DCNFused
+    torch.manual_seed(23)
+    B, C, H, W = 2, 64, 24, 40
+    x = torch.randn(B, C, H, W, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    om32 = torch.randn(B, 27, H, W, device="cuda")
+    om32[:, :18] *= 1.5
+    om32 = om32.to(torch.bfloat16).float().contiguous(memory_format=torch.channels_last)
+    w = (torch.rand(C, C, 3, 3, device="cuda") - 0.5) * 0.1
+    bias = torch.zeros(C, device="cuda")
+    gy = torch.randn(B, C, H, W, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    res = []
+    for om in (om32, om32.to(torch.bfloat16)):
+        omr = om.clone().requires_grad_(True)
+        y = _DCNFused.apply(x, omr, w, bias, (1, 1), (1, 1), (1, 1), 1)
+        y.backward(gy)
+        assert omr.grad.dtype == om.dtype
+        res.append(omr.grad.float().cpu().numpy())
+    gate(res[1], res[0], 1e-2, "d/d(om) bf16 vs fp32")
