@@ -25,3 +25,6 @@ with profile(activities=[ProfilerActivity.CUDA]) as prof:
     tr.step(batch)
     torch.cuda.synchronize()
 print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40, max_name_column_width=90))
+if os.environ.get("TRACE_FULL_NAMES"):
+    for e in sorted(prof.key_averages(), key=lambda e: -e.device_time_total)[:45]:
+        print(f"{e.device_time_total / 1000:8.3f} ms  n={e.count:4d}  {e.key[:420]}")
