@@ -28,6 +28,7 @@ EXPORTED_SYMBOLS = (
     "cpoly_offset_conv_packed_bytes", "cpoly_offset_conv_pack_weights", "cpoly_offset_conv_forward",
     "cpoly_decode_static_max_bytes", "cpoly_decode_static",
     "cpoly_bn_eligible", "cpoly_bn_workspace_bytes", "cpoly_bn_train_forward", "cpoly_bn_train_backward",
+    "cpoly_idaup_upsample_backward_workspace_bytes",
 )
 
 
@@ -107,7 +108,8 @@ class BnBwdArgs(Structure):
 
 class UpsampleBwdArgs(Structure):
     _fields_ = [(n, c_int32) for n in ("B", "C", "H", "W", "f", "dtype")] + [
-        ("x", Tensor4), ("gy", Tensor4), ("weight", c_void_p), ("gx", Tensor4), ("gweight", c_void_p)]
+        ("x", Tensor4), ("gy", Tensor4), ("weight", c_void_p), ("gx", Tensor4), ("gweight", c_void_p),
+        ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
 
 
 _lib = None
@@ -175,6 +177,8 @@ def lib():
         L.cpoly_maxpool2x2_nhwc_forward.argtypes = [POINTER(MaxPoolArgs), c_void_p]
         L.cpoly_idaup_upsample_backward.restype = c_int32
         L.cpoly_idaup_upsample_backward.argtypes = [POINTER(UpsampleBwdArgs), c_void_p]
+        L.cpoly_idaup_upsample_backward_workspace_bytes.restype = c_size_t
+        L.cpoly_idaup_upsample_backward_workspace_bytes.argtypes = [POINTER(UpsampleBwdArgs)]
         L.cpoly_offset_conv_packed_bytes.restype = c_size_t
         L.cpoly_offset_conv_packed_bytes.argtypes = [c_int32]
         L.cpoly_offset_conv_pack_weights.restype = c_int32

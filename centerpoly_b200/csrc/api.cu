@@ -285,6 +285,11 @@ int cpoly_maxpool2x2_nhwc_forward(const cpoly_maxpool_args* a, cpoly_stream_t st
   return maxpool2x2_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+size_t cpoly_idaup_upsample_backward_workspace_bytes(const cpoly_upsample_bwd_args* a) {
+  if (!a || a->C <= 0 || a->f < 2 || a->B <= 0 || a->H <= 0 || a->W <= 0 || !a->gweight) return 256;
+  return idaup_upsample_backward_workspace(*a);
+}
+
 int cpoly_idaup_upsample_backward(const cpoly_upsample_bwd_args* a, cpoly_stream_t stream) {
   CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
   CPOLY_REQUIRE(a->B >= 0 && a->C > 0 && a->H > 0 && a->W > 0 && a->f >= 2, CPOLY_EINVAL, "bad upsample dims");

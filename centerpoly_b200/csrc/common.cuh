@@ -142,6 +142,7 @@ size_t dcn_col2im_gcol_bytes(const cpoly_dcn_fwd_args& f);
 size_t dcn_col2im_workspace(const cpoly_dcn_bwd_args& a);
 int dcn_col2im_launch(const cpoly_dcn_bwd_args& a, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream);
+size_t idaup_upsample_backward_workspace(const cpoly_upsample_bwd_args& a);
 int idaup_upsample_backward_launch(const cpoly_upsample_bwd_args& a, cudaStream_t stream);
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K);
 int decode_launch(const cpoly_decode_args& a, cudaStream_t stream);

@@ -247,7 +247,7 @@ __global__ void __launch_bounds__(256) upsample_bwd_input_kernel(UpParams p, cpo
 // blockIdx.y = phase, blockIdx.x = pixel chunk; thread = (pixel lane, piece).  fp32 atomics: summation order varies
 // between runs at the 1e-7 level (as in cuDNN's own grouped weight gradient).
 template <typename T, int VEC>
-__global__ void __launch_bounds__(256) upsample_bwd_weight_kernel(UpParams p, cpoly_tensor4 gy, float* __restrict__ gw, int px_per_block) {
+__global__ void __launch_bounds__(256) upsample_bwd_weight_kernel(UpParams p, cpoly_tensor4 gy, float* __restrict__ gw, int px_per_block, float* __restrict__ partial) {
   const int pieces = p.C / VEC;                   // 8, 16 or 32 (power of two <= 32)
   const int K = 2 * p.f, pad = p.f / 2;
   const int py = blockIdx.y / p.f, pxp = blockIdx.y - py * p.f;
@@ -300,6 +300,30 @@ __global__ void __launch_bounds__(256) upsample_bwd_weight_kernel(UpParams p, cp
         for (int o = pieces; o < 32; o <<= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
         acc[dy][dx][j] = a;
       }
+  if (partial) {
+    // deterministic form: the 8 warps' sums are added in warp order, and the block's 4 taps x C values go to
+    // partial[blockIdx.x][tap][C]; upsample_bwd_weight_finalize_kernel adds the blocks in order
+    __shared__ float red[8][4][32 * VEC];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane < pieces) {
+#pragma unroll
+      for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 2; ++dx)
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) red[warp][dy * 2 + dx][lane * VEC + j] = acc[dy][dx][j];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 4 * p.C; i += 256) {
+      const int t = i / p.C, c = i - t * p.C;
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) s += red[w][t][c];
+      const int dy = t >> 1, dx = t & 1;
+      partial[((int64_t)blockIdx.x * K * K + (ky1 + dy * p.f) * K + kx1 + dx * p.f) * p.C + c] = s;
+    }
+    return;
+  }
   if ((threadIdx.x & 31) < pieces) {
 #pragma unroll
     for (int dy = 0; dy < 2; ++dy)
@@ -310,6 +334,15 @@ __global__ void __launch_bounds__(256) upsample_bwd_weight_kernel(UpParams p, cp
         for (int j = 0; j < VEC; ++j) atomicAdd(dst + j, acc[dy][dx][j]);
       }
   }
+}
+
+// gw[t][c] = sum over the pixel blocks, in block order
+__global__ void upsample_bwd_weight_finalize_kernel(const float* __restrict__ partial, float* __restrict__ gw, int n_blocks, int n_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_out) return;
+  float s = 0.f;
+  for (int b = 0; b < n_blocks; ++b) s += partial[(int64_t)b * n_out + i];
+  gw[i] = s;
 }
 
 // any strides / channel counts: one thread per output element
@@ -376,6 +409,23 @@ int idaup_upsample_launch(const cpoly_upsample_args& a, cudaStream_t stream) {
   return check_launch("idaup_upsample_kernel");
 }
 
+// pixel blocks of the deterministic weight gradient: about 4 CTAs per SM over all f^2 phases, >= 8 pixels per thread
+int idaup_bwd_weight_blocks(int B, int H, int W, int C, int f, int dtype) {
+  const int vec = dtype == CPOLY_BF16 ? 8 : 4;
+  const int pieces = C / vec > 0 ? C / vec : 1;
+  const int nlanes = 256 / pieces > 0 ? 256 / pieces : 1;
+  const int64_t npix = (int64_t)B * H * W;
+  int64_t g = (148 * 4) / (f * f);
+  const int64_t cap = (npix + (int64_t)nlanes * 8 - 1) / ((int64_t)nlanes * 8);
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+size_t idaup_upsample_backward_workspace(const cpoly_upsample_bwd_args& a) {
+  return (size_t)idaup_bwd_weight_blocks(a.B, a.H, a.W, a.C, a.f, a.dtype) * 4 * a.f * a.f * a.C * sizeof(float) + 256;
+}
+
 int idaup_upsample_backward_launch(const cpoly_upsample_bwd_args& a, cudaStream_t stream) {
   UpParams p;
   p.B = a.B; p.C = a.C; p.H = a.H; p.W = a.W; p.f = a.f; p.Ho = a.H * a.f; p.Wo = a.W * a.f;
@@ -399,10 +449,25 @@ int idaup_upsample_backward_launch(const cpoly_upsample_bwd_args& a, cudaStream_
   if (a.gweight) {
     const int64_t npix = (int64_t)a.B * a.H * a.W;
     const int nlanes = 256 / pieces;
-    int px_per_block = nlanes * 16;                     // 16 pixels per thread
+    const int n_out = 4 * a.f * a.f * a.C;
+    int gx_blocks = idaup_bwd_weight_blocks(a.B, a.H, a.W, a.C, a.f, a.dtype);
+    const bool det = a.workspace && a.workspace_bytes >= (size_t)gx_blocks * n_out * sizeof(float) && (reinterpret_cast<uintptr_t>(a.workspace) & 15) == 0;
+    if (det) {
+      // a few hundred CTAs in total, each summing its pixel range in registers: no atomics, fixed order (bit-reproducible)
+      int px_per_block = (int)((npix + gx_blocks - 1) / gx_blocks);
+      px_per_block = (px_per_block + nlanes - 1) / nlanes * nlanes;
+      float* partial = reinterpret_cast<float*>(a.workspace);
+      const dim3 grid((unsigned)gx_blocks, (unsigned)(a.f * a.f));
+      if (bf) upsample_bwd_weight_kernel<__nv_bfloat16, 8><<<grid, 256, 0, stream>>>(p, a.gy, a.gweight, px_per_block, partial);
+      else upsample_bwd_weight_kernel<float, 4><<<grid, 256, 0, stream>>>(p, a.gy, a.gweight, px_per_block, partial);
+      if (int rc = check_launch("upsample_bwd_weight_kernel")) return rc;
+      upsample_bwd_weight_finalize_kernel<<<(n_out + 255) / 256, 256, 0, stream>>>(partial, a.gweight, gx_blocks, n_out);
+      return check_launch("upsample_bwd_weight_finalize_kernel");
+    }
+    int px_per_block = nlanes * 16;                     // 16 pixels per thread; fp32 atomics into the zero-initialised gweight
     const dim3 grid((unsigned)((npix + px_per_block - 1) / px_per_block), (unsigned)(a.f * a.f));
-    if (bf) upsample_bwd_weight_kernel<__nv_bfloat16, 8><<<grid, 256, 0, stream>>>(p, a.gy, a.gweight, px_per_block);
-    else upsample_bwd_weight_kernel<float, 4><<<grid, 256, 0, stream>>>(p, a.gy, a.gweight, px_per_block);
+    if (bf) upsample_bwd_weight_kernel<__nv_bfloat16, 8><<<grid, 256, 0, stream>>>(p, a.gy, a.gweight, px_per_block, nullptr);
+    else upsample_bwd_weight_kernel<float, 4><<<grid, 256, 0, stream>>>(p, a.gy, a.gweight, px_per_block, nullptr);
     if (int rc = check_launch("upsample_bwd_weight_kernel")) return rc;
   }
   return CPOLY_OK;

@@ -95,12 +95,15 @@ class _UpsampleFn(torch.autograd.Function):
         need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         with torch.cuda.device(dev):
             gx = torch.empty_like(x, memory_format=torch.channels_last) if need_x else None
-            gwt = torch.zeros_like(wt) if need_w else None
+            gwt = torch.empty_like(wt) if need_w else None
             a = _lib.UpsampleBwdArgs()
             a.B, a.C, a.H, a.W, a.f, a.dtype = B, C, H, W, f, _lib.dtype_code(x)
             a.x, a.gy, a.gx = _lib.t4(x), _lib.t4(gy), _lib.t4(gx)
             a.weight = wt.data_ptr()
             a.gweight = gwt.data_ptr() if need_w else None
+            if need_w:      # fixed-order (bit-reproducible) weight gradient: per-block partial sums in a workspace, no atomics
+                ws = _lib.workspace(_lib.lib().cpoly_idaup_upsample_backward_workspace_bytes(byref(a)), dev)
+                a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
             _lib.check(_lib.lib().cpoly_idaup_upsample_backward(byref(a), _lib.stream_ptr(dev)), "cpoly_idaup_upsample_backward")
             _lib.LAUNCHES["upsample_bwd"] += int(need_x) + int(need_w)
         gw = gwt.t().reshape(ctx.wshape).to(ctx.wdtype) if need_w else None

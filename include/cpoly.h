@@ -184,9 +184,14 @@ typedef struct {
   cpoly_tensor4 gy;       /* (B,C,H*f,W*f) gradient of the output                      */
   const float* weight;    /* (4f^2, C) fp32                                            */
   cpoly_tensor4 gx;       /* (B,C,H,W) out, or ptr NULL                                */
-  float* gweight;         /* (4f^2, C) fp32, ZERO-INITIALISED by the caller, or NULL   */
+  float* gweight;         /* (4f^2, C) fp32, or NULL.  Without a workspace it must be ZERO-INITIALISED by the caller
+                           * (fp32 atomics, summation order varies at the 1e-7 level) */
+  void* workspace;        /* ABI v10: >= cpoly_idaup_upsample_backward_workspace_bytes(&args), 16-byte aligned: the weight
+                           * gradient is then summed in a fixed order (bit-reproducible, no atomics); NULL keeps the atomics */
+  size_t workspace_bytes;
 } cpoly_upsample_bwd_args;
 
+size_t cpoly_idaup_upsample_backward_workspace_bytes(const cpoly_upsample_bwd_args* args);
 int cpoly_idaup_upsample_backward(const cpoly_upsample_bwd_args* args, cpoly_stream_t stream);
 
 /* --------------------------------------------------------------------------------------- decode */

@@ -152,3 +152,24 @@ def test_idaup_upsample_backward_vs_conv_transpose(f, dtype, C):
     m(xd).backward(gy.cuda().to(dtype))
     assert m.weight.grad is None
     gate(xd.grad.float().cpu().numpy(), xr.grad.numpy(), tol, "grad_x (frozen weight)")
+
+
+def test_idaup_upsample_weight_gradient_is_bit_reproducible_at_training_size():
+    """The weight gradient with a workspace is summed in a fixed order: two runs give the same bits (the atomics form, kept
+    for callers without a workspace, varies at the 1e-7 level), and it matches fp64 at a training-size map."""
+    from centerpoly_b200.neck import IDAUpsampleTrain
+    torch.manual_seed(9)
+    B, C, H, W, f = 4, 64, 32, 64, 4
+    deconv = torch.nn.ConvTranspose2d(C, C, 2 * f, stride=f, padding=f // 2, groups=C, bias=False).cuda()
+    m = IDAUpsampleTrain(deconv)
+    x = torch.randn(B, C, H, W, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    gy = torch.randn(B, C, H * f, W * f, device="cuda").to(torch.bfloat16)
+    grads = []
+    for _ in range(2):
+        m.weight.grad = None
+        m(x).backward(gy)
+        grads.append(m.weight.grad.clone())
+    assert torch.equal(grads[0], grads[1])
+    wr = m.weight.detach().double().requires_grad_(True)
+    F.conv_transpose2d(x.double(), wr, stride=f, padding=f // 2, groups=C).backward(gy.double())
+    gate(grads[0].double().cpu().numpy(), wr.grad.cpu().numpy(), 1e-4, "grad_w")
