@@ -306,9 +306,15 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
     }
     uint32_t s_idx = (uint32_t)grp % nstages, s_ph = ((uint32_t)grp / nstages) & 1u;
     while (cur.t < total) {
+      // Look ahead to the group's next step only when its parameters can exist before this step is finished: the
+      // parameter buffers hold two items, so a step two or more items ahead (items of fewer than GROUPS steps: tap-split
+      // schedules of narrow layers) is produced only after THIS step has released its item - seeking to it now would wait
+      // for ourselves.  Such a step is looked up after the arrive below, at the price of an empty pipeline.
       Cur nxt = cur;
-      seek(nxt, GROUPS);
-      const bool more = nxt.t < total;
+      const int nt = cur.t + GROUPS;
+      const bool ahead = nt >= total || nt / chunks_per_item <= cur.j + 1;
+      if (ahead) seek(nxt, GROUPS);
+      const bool more = ahead && nxt.t < total;
       mbar_wait(bar_empty + 8 * s_idx, s_ph ^ 1u);
       if (warp == SAMPLER_WARP0) tr(0, 1); else if (warp == SAMPLER_WARP0 + SAMPLER_WARPS - 1) tr(4, 1);
       const uint32_t a_st = smem_base + p.stage_off + s_idx * A_STAGE_BYTES + st_off;
@@ -325,6 +331,13 @@ __global__ void __maxnreg__(80) dcn_fwd_tc_kernel(const TcParams p) {
         mbar_arrive(bar_pempty + 8 * (cur.j & 1));   // this warp has consumed the step's parameters
       }
       if (warp == SAMPLER_WARP0) tr(0, 2); else if (warp == SAMPLER_WARP0 + SAMPLER_WARPS - 1) tr(4, 2);
+      if (!ahead) {
+        seek(nxt, GROUPS);
+        if (nxt.t < total) {
+          issue(c[0], pw[0], nxt, 0);
+          issue(c[1], pw[1], nxt, 1);
+        }
+      }
       cur = nxt;
       s_idx += (uint32_t)GROUPS;
       while (s_idx >= nstages) { s_idx -= nstages; s_ph ^= 1u; }
@@ -690,8 +703,16 @@ int pow2_at_least(int v) {
 }
 
 // Tap split of the schedule: 1 when the pixel tiles alone fill the machine, else 3 or 9.
-int choose_split(int num_tiles) {
+int choose_split(int num_tiles, int Cout) {
+  if (const char* e = getenv("CPOLY_TC_SPLIT")) {   // profiling knob
+    const int v = atoi(e);
+    if (v == 1 || v == 3 || v == 9) return v;
+  }
   if (num_tiles >= 148) return 1;
+  // 64..147 tiles with wide outputs: the unsplit schedule on fewer SMs beats 3 tap groups, whose fp32 partial tiles
+  // (Cout x 512 B per item, written and re-read by the combine kernel) cost more than the idle SMs (r02, 64x128 maps:
+  // 256->256 36.1 vs 42.2 us, 256->128 31.6 vs 32.1, 256->64 27.8 vs 26.6)
+  if (num_tiles >= 64 && Cout >= 128) return 1;
   if (num_tiles * 3 >= 148) return 3;
   return 9;
 }
@@ -719,7 +740,7 @@ bool dcn_tc_eligible(const cpoly_dcn_fwd_args& a) {
 
 size_t dcn_tc_forward_workspace(const cpoly_dcn_fwd_args& a) {
   const int tiles = a.B * ((a.W + TILE_W - 1) / TILE_W) * ((a.H + TILE_H - 1) / TILE_H);
-  return split_workspace(choose_split(tiles), (int64_t)a.B * a.H * a.W, a.Cout) + 256;
+  return split_workspace(choose_split(tiles, a.Cout), (int64_t)a.B * a.H * a.W, a.Cout) + 256;
 }
 
 size_t dcn_tc_packed_bytes(int Cin, int Cout, int kh, int kw, int dtype) {
@@ -761,7 +782,7 @@ int dcn_forward_tc(const cpoly_dcn_fwd_args& a, cudaStream_t stream) {
   p.num_tiles = a.B * p.tiles_x * p.tiles_y;
   if (p.num_tiles == 0) return CPOLY_OK;
   const int64_t npix = (int64_t)a.B * a.H * a.W;
-  p.split = choose_split(p.num_tiles);
+  p.split = choose_split(p.num_tiles, a.Cout);
   const size_t need = split_workspace(p.split, npix, a.Cout);
   if (p.split > 1 && (!a.workspace || a.workspace_bytes < need || (reinterpret_cast<uintptr_t>(a.workspace) & 15)))
     p.split = 1;  // no scratch supplied: unsplit schedule (same result, fewer busy SMs)

@@ -74,6 +74,10 @@ TC_SHAPES = [  # (B, Cin, Cout, H, W) — reduced-resolution versions of the 7 I
     (1, 256, 128, 9, 21), (1, 256, 256, 8, 16), (1, 512, 256, 8, 16), (3, 64, 64, 5, 7),
     (1, 128, 64, 72, 100),    # 63 tiles  -> tap split 3
     (1, 64, 64, 100, 200),    # 169 tiles -> unsplit persistent schedule, ragged right/bottom tiles
+    # three tap-split items per CTA whose items have fewer steps than there are sampler groups: a group's next step lies
+    # two items ahead, which the look-ahead must not wait for (it deadlocked on its own item before the fix)
+    (1, 64, 64, 88, 144),     # 99 tiles, split 3: 3 steps per item, 297 items on 148 CTAs
+    (1, 128, 128, 40, 128),   # 40 tiles, split 9: 2 steps per item, 360 items
 ]
 
 
