@@ -342,3 +342,26 @@ def test_fused_module_backward_returns_offset_gradients_in_the_producers_dtype()
         assert omr.grad.dtype == om.dtype
         res.append(omr.grad.float().cpu().numpy())
     gate(res[1], res[0], 1e-2, "d/d(om) bf16 vs fp32")
+
+
+def test_tcgen05_schedules_over_random_shapes_match_the_simt_path():
+    """Every (tile count, tap split, channel chunks, items per CTA) combination takes a different walk through the forward
+    and backward kernels' barrier rings; 16 seeded random shapes against the oracle-verified CUDA-core path (both ours, same
+    inputs), so that a schedule that hangs or mis-orders shows up here and not at a user's image size."""
+    import random
+    rng = random.Random(20261105)
+    for i in range(16):
+        Cin = rng.choice([64, 64, 128, 256])
+        Cout = rng.choice([16, 64, 64, 128, 256])
+        B = rng.choice([1, 1, 2, 3])
+        H, W = rng.randint(5, 150), rng.randint(5, 170)
+        if B * H * W > 40000:
+            H = max(5, 40000 // (B * W))
+        case = make_dcn_case(1000 + i, B, Cin, Cout, H, W, dtype=torch.bfloat16)
+        bwd = i % 4 == 0 and B * H * W < 12000
+        tc = run_ours(case, "tcgen05", dtype=torch.bfloat16, channels_last=True, backward=bwd)
+        ref = run_ours(case, "simt", dtype=torch.bfloat16, channels_last=True, backward=bwd)
+        gate(tc["y"], ref["y"], 1e-2, f"y {B}x{Cin}->{Cout}@{H}x{W}")
+        if bwd:
+            gate(tc["gw"], ref["gw"], 1e-2, f"gw {B}x{Cin}->{Cout}@{H}x{W}")
+            gate(tc["gx"], ref["gx"], 1e-2, f"gx {B}x{Cin}->{Cout}@{H}x{W}")
