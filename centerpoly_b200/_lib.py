@@ -29,6 +29,7 @@ EXPORTED_SYMBOLS = (
     "cpoly_decode_static_max_bytes", "cpoly_decode_static",
     "cpoly_bn_eligible", "cpoly_bn_workspace_bytes", "cpoly_bn_train_forward", "cpoly_bn_train_backward",
     "cpoly_idaup_upsample_backward_workspace_bytes",
+    "cpoly_rasterise_fill_workspace_bytes", "cpoly_rasterise_fill",
 )
 
 
@@ -93,6 +94,12 @@ class OffsetConvArgs(Structure):
         ("x", c_void_p), ("weight_packed", c_void_p), ("bias", c_void_p), ("om", c_void_p)]
 
 
+class RasterFillArgs(Structure):
+    _fields_ = [(n, c_int32) for n in ("B", "K", "N", "W", "H", "inclusive")] + [
+        ("thresh", c_double), ("occluder_score", c_double), ("dets", c_void_p), ("count", c_void_p), ("slot_det", c_void_p),
+        ("area", c_void_p), ("status", c_void_p), ("masks", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t)]
+
+
 class BnFwdArgs(Structure):
     _fields_ = [("N", c_int64), ("C", c_int32), ("dtype", c_int32), ("relu", c_int32), ("reserved0", c_int32),
                 ("x", c_void_p), ("y", c_void_p), ("weight", c_void_p), ("bias", c_void_p), ("running_mean", c_void_p),
@@ -153,6 +160,10 @@ def lib():
         L.cpoly_decode_static_max_bytes.argtypes = []
         L.cpoly_decode_static.restype = c_int32
         L.cpoly_decode_static.argtypes = [POINTER(DecodeArgs), c_void_p]
+        L.cpoly_rasterise_fill_workspace_bytes.restype = c_size_t
+        L.cpoly_rasterise_fill_workspace_bytes.argtypes = [c_int32] * 3
+        L.cpoly_rasterise_fill.restype = c_int32
+        L.cpoly_rasterise_fill.argtypes = [POINTER(RasterFillArgs), c_void_p]
         L.cpoly_bn_eligible.restype = c_int32
         L.cpoly_bn_eligible.argtypes = [c_int32, c_int32]
         L.cpoly_bn_workspace_bytes.restype = c_size_t

@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcpoly.so")
-SOURCES = ["api.cu", "dcn_simt.cu", "dcn_tc.cu", "dcn_tc_win.cu", "dcn_tc_bwd.cu", "dcn_col2im.cu", "offset_conv.cu", "neck.cu", "decode.cu", "raster.cu", "poly_iou.cu", "backbone.cu", "batchnorm.cu"]
+SOURCES = ["api.cu", "dcn_simt.cu", "dcn_tc.cu", "dcn_tc_win.cu", "dcn_tc_bwd.cu", "dcn_col2im.cu", "offset_conv.cu", "neck.cu", "decode.cu", "raster.cu", "poly_iou.cu", "backbone.cu", "batchnorm.cu", "raster_fill.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xptxas=-v",

@@ -164,6 +164,21 @@ int cpoly_decode(const cpoly_decode_args* a, cpoly_stream_t stream) {
   return decode_launch(*a, reinterpret_cast<cudaStream_t>(stream));
 }
 
+size_t cpoly_rasterise_fill_workspace_bytes(int32_t B, int32_t K, int32_t N) { return raster_fill_workspace_bytes(B, K, N); }
+
+int cpoly_rasterise_fill(const cpoly_raster_fill_args* a, cpoly_stream_t stream) {
+  CPOLY_REQUIRE(a, CPOLY_EINVAL, "NULL args");
+  CPOLY_REQUIRE(a->B >= 0 && a->K >= 1 && a->K <= 256 && a->N >= 3 && a->N <= 64, CPOLY_EINVAL, "need 1 <= K <= 256 and 3 <= N <= 64 (got K=%d N=%d)", a->K, a->N);
+  CPOLY_REQUIRE(a->W >= 1 && a->W <= 8192 && a->H >= 1 && a->H <= 8192, CPOLY_EINVAL, "mask size must be within 8192 x 8192");
+  CPOLY_REQUIRE((int64_t)a->B * a->K <= 65535, CPOLY_EINVAL, "B * K must not exceed 65535");
+  CPOLY_REQUIRE(a->dets && a->count && a->slot_det && a->area && a->status, CPOLY_EINVAL, "NULL pointer");
+  CPOLY_REQUIRE(!a->masks || (reinterpret_cast<uintptr_t>(a->masks) & 15) == 0, CPOLY_EINVAL, "masks must be 16-byte aligned");
+  CPOLY_REQUIRE(a->workspace && a->workspace_bytes >= raster_fill_workspace_bytes(a->B, a->K, a->N) && (reinterpret_cast<uintptr_t>(a->workspace) & 255) == 0,
+                CPOLY_EWORKSPACE, "rasterise_fill workspace too small or misaligned: need %zu bytes", raster_fill_workspace_bytes(a->B, a->K, a->N));
+  if (a->B == 0) return CPOLY_OK;
+  return raster_fill_launch(*a, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int cpoly_bn_eligible(int32_t C, int32_t dtype) { return bn_eligible(C, dtype) ? 1 : 0; }
 size_t cpoly_bn_workspace_bytes(int32_t C) { return bn_workspace_bytes(C); }
 

@@ -147,6 +147,8 @@ int idaup_upsample_backward_launch(const cpoly_upsample_bwd_args& a, cudaStream_
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K);
 int decode_launch(const cpoly_decode_args& a, cudaStream_t stream);
 int decode_static_scratch(void** ptr);
+size_t raster_fill_workspace_bytes(int B, int K, int N);
+int raster_fill_launch(const cpoly_raster_fill_args& a, cudaStream_t stream);
 bool bn_eligible(int C, int dtype);
 size_t bn_workspace_bytes(int C);
 int bn_train_forward_launch(const cpoly_bn_fwd_args& a, cudaStream_t stream);

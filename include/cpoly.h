@@ -353,6 +353,38 @@ size_t cpoly_offset_conv_packed_bytes(int32_t Cin);   /* 0 when the shape has no
 int cpoly_offset_conv_pack_weights(const float* weight, void* packed, int32_t Cin, int32_t n_out, cpoly_stream_t stream);
 int cpoly_offset_conv_forward(const cpoly_offset_conv_args* args, cpoly_stream_t stream);
 
+/* ---- instance masks of the IDD / KITTI writers (ABI v10) ---------------------------------------------------------------
+ * The mask construction inside `IDD.format_and_write_to_IDD` (src/lib/datasets/dataset/IDD.py:123-170) and
+ * `KITTIPOLY.format_and_write_to_kitti` (src/lib/datasets/dataset/kitti_poly.py:95-136), i.e. what those functions do
+ * between reading `all_bboxes` and writing the PNG / txt files:
+ *   - keep detections with score >= thresh (IDD :141, inclusive = 1) or score > thresh (KITTI :113, inclusive = 0);
+ *     file slot = the reference's counter: classes ascending, detection order inside a class;
+ *   - vertices int(float("{:.2f}".format(v))) (:62-63,159-160); per class, stable depth order;
+ *   - mask = PIL `polygon(points, outline=0, fill=255)` (scan-line fill of Pillow's polygon_generic minus the line8
+ *     Bresenham outline) times the class's running `to_remove_mask`, which instances with score >= occluder_score clear
+ *     with `polygon(points, outline=0, fill=0)` (the bare fill).
+ * Pillow's algorithms are restated in oracle/raster_fill_oracle.py and pinned to the unmodified reference writers run with
+ * Pillow 12.2 (tests/golden/fillraster_*.npz).  Vertices outside [-8192, 8191] are clamped and counted in status[b].
+ * W, H <= 8192; K <= 256; N <= 64; B * K <= 65535. */
+typedef struct {
+  int32_t B, K, N;        /* dets is (B,K,2N+7) fp32 as written by cpoly_decode (with post_affine) */
+  int32_t W, H;           /* mask size = image size */
+  int32_t inclusive;      /* 1: score >= thresh (IDD), 0: score > thresh (KITTI) */
+  double thresh;          /* opt.thresh, compared in fp64 like the reference's Python float */
+  double occluder_score;  /* 0.5 */
+  const float* dets;
+  int32_t* count;         /* (B)   instances written */
+  int32_t* slot_det;      /* (B,K) file slot -> detection index; -1 past count[b] */
+  int32_t* area;          /* (B,K) visible pixels per slot */
+  int32_t* status;        /* (B)   vertices that had to be clamped (0 => exact) */
+  uint8_t* masks;         /* (B,K,H,W) 0 / 255 in file-slot order, slots >= count[b] untouched; NULL => count / slot_det only */
+  void* workspace;        /* >= cpoly_rasterise_fill_workspace_bytes(B,K,N), 256-byte aligned */
+  size_t workspace_bytes;
+} cpoly_raster_fill_args;
+
+size_t cpoly_rasterise_fill_workspace_bytes(int32_t B, int32_t K, int32_t N);
+int cpoly_rasterise_fill(const cpoly_raster_fill_args* args, cpoly_stream_t stream);
+
 /* ---- training-mode BatchNorm2d (+ fused ReLU) on dense NHWC activations (ABI v10) -----------------------------------
  * Replaces `nn.BatchNorm2d(planes, momentum=BN_MOMENTUM)` in training mode at the sites of the DLA-34 / DLAUp / IDAUp
  * network (src/lib/models/networks/pose_dla_dcn.py:31-47 BasicBlock, :143-160 Root, :231-236 base_layer, :247-252 conv
