@@ -11,3 +11,4 @@ from .post_process import batch_inverse_affine, group_by_class, inverse_affine, 
 __version__ = "0.1.0"
 from .poly_loss import IOU_STATUS, PolyLoss, poly_iou_loss, poly_order_loss  # noqa: F401
 from .batchnorm import BatchNorm2dTrain, batch_norm_train, use_training_batchnorm  # noqa: F401
+from .raster_fill import FillRasterResult, rasterise_fill_instances, write_idd, write_kitti  # noqa: F401
