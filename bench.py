@@ -387,11 +387,32 @@ def idd_polar_bench(torch, dist, world, rank, local_rank, steps=5, warmup=3, per
         t = torch.tensor([ms, e2e_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, e2e_ms = t.tolist()
+    # the IDD writer's instance masks for the batch (compute half of IDD.format_and_write_to_IDD: csrc/raster_fill.cu) on
+    # the detections the last step left on the device; opt.thresh = 0.3 (the reference's demo default)
+    masks = None
+    try:
+        from centerpoly_b200.raster_fill import rasterise_fill_instances
+        dets = eng.slots[0]["dets"]
+        buf = torch.empty((dets.shape[0], dets.shape[1], 1080, 1920), dtype=torch.uint8, device=dets.device)
+        for _ in range(2):
+            r = rasterise_fill_instances(dets, 1920, 1080, 0.3, inclusive=True, out=buf)
+        torch.cuda.synchronize()
+        m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        m0.record()
+        r = rasterise_fill_instances(dets, 1920, 1080, 0.3, inclusive=True, out=buf)
+        m1.record()
+        torch.cuda.synchronize()
+        masks = dict(ms=m0.elapsed_time(m1), images=int(dets.shape[0]), instances=int(r.count.sum()), mask_bytes=int(r.count.sum()) * 1080 * 1920,
+                     note="cpoly_rasterise_fill on the step's detections, score >= 0.3, 1920x1080 masks; not inside the timed steps")
+        del buf, r
+    except Exception as e:   # reported, never fatal for the headline line
+        masks = dict(error=repr(e)[:200])
     out = dict(workload="configs[4]: polar-vertex polydet inference, IDD-shape 1920x1080 (padded 1952x1088), 9 classes, %d images/GPU" % per_gpu,
                value=world * per_gpu * steps / (ms / 1000.0), unit="images/s", n_gpus=world, global_batch=world * per_gpu,
                ms_per_step=ms / steps, steps=steps, rep="polar", scaling="weak",
                e2e=dict(value=world * per_gpu * steps / (e2e_ms / 1000.0), unit="images/s", ms_per_step=e2e_ms / steps,
-                        h2d_bytes_per_step=eng.h2d_bytes_per_step, d2h_bytes_per_step=eng.d2h_bytes_per_step))
+                        h2d_bytes_per_step=eng.h2d_bytes_per_step, d2h_bytes_per_step=eng.d2h_bytes_per_step),
+               idd_writer_masks=masks)
     del eng, host
     torch.cuda.empty_cache()
     return out

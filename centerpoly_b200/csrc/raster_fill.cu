@@ -192,6 +192,9 @@ __global__ void __launch_bounds__(32 * FR_WARPS) fill_rows_kernel(const FillPara
             const FEdge oth = make_edge(v, k, n);
             if ((cur.dx > 0.f && oth.dx <= 0.f) || (cur.dx < 0.f && oth.dx >= 0.f)) continue;
             if (xv != edge_x(oth, y)) continue;
+            const int xi = (int)xv;
+            if (!(((cur.x0 == xi && cur.y0 == y) || (cur.x1 == xi && cur.y1 == y)) && ((oth.x0 == xi && oth.y0 == y) || (oth.x1 == xi && oth.y1 == y))))
+              continue;                                // two edges that merely cross at an integer x are not a corner
             const int ya = y == gymax ? y - 1 : y + 1;
             if (ya < cur.ymin || ya > cur.ymax || ya < oth.ymin || ya > oth.ymax) continue;
             const float a = edge_x(cur, ya), bq = edge_x(oth, ya);
