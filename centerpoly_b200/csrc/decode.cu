@@ -55,6 +55,8 @@ struct DecodeParams {
   int* tbin;                   // [B] score bin (bits [30:18]) of T0, the lower bound of the K-th best peak (decode_t0_kernel)
   unsigned int* item_max;      // [B][items_per_image] upper bound (float bits) of the peak scores of every scan item
   unsigned int* item_cert;     // [B][items_per_image] that maximum when it is certainly an NMS peak, else 0 (float bits)
+  unsigned int* todo_count;    // [1] items on the re-scan list (decode_t0_kernel appends, decode_collect_kernel walks)
+  unsigned int* todo;          // [B * items_per_image] b * items_per_image + item of every item whose bound reaches its image's threshold bin
   int rh;                      // rows per warp work item
   int nbands, nrowchunks, items_per_image;
   int b0, nb;                  // image group handled by this launch (kernels 1 and 2)
@@ -425,13 +427,57 @@ __global__ void __launch_bounds__(DNT) decode_t0_kernel(DecodeParams p) {
     tb = t0 > 0.f ? score_bin(t0) : 0;
   }
   if (tid == 0) p.tbin[b] = tb;
+  // the items of this image whose best peak can reach the threshold bin go on ONE batch-wide list: the collection pass
+  // then deals them out one per warp, whatever their distribution over the images (a warp used to re-scan the flagged
+  // ones among ITS 22 consecutive items serially: 34 us at B = 64).  The list order depends on the atomics; the
+  // candidate list it feeds is unordered anyway (select sorts).
+  if (!p.todo) return;          // small batch: decode_collect_direct_kernel needs no list
+  const unsigned int* imax = p.item_max + (int64_t)b * p.items_per_image;
+  for (int i0 = 0; i0 < p.items_per_image; i0 += DNT) {
+    const int i = i0 + tid;
+    bool need = false;
+    if (i < p.items_per_image) {
+      const float mx = __uint_as_float(__ldcg(imax + i));
+      need = mx > 0.f && score_bin(mx) >= tb;
+    }
+    const unsigned int m = __ballot_sync(0xffffffffu, need);
+    if (m) {
+      unsigned int base = 0;
+      if ((tid & 31) == 0) base = atomicAdd(p.todo_count, (unsigned int)__popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (need) p.todo[base + __popc(m & ((1u << (tid & 31)) - 1u))] = (unsigned int)b * (unsigned int)p.items_per_image + (unsigned int)i;
+    }
+  }
 }
 
 // ------------------------------------------------------------------ launch 3: candidate collection
 // Only the items whose best peak reaches the image's threshold bin are re-scanned (about K + one bin's worth of peaks
 // per image lie there), so this pass touches a few percent of the heat map instead of all of it again.
 template <typename T>
-__global__ void __launch_bounds__(DNT, 3) decode_collect_kernel(DecodeParams p, int ipw) {
+__global__ void __launch_bounds__(DNT, 3) decode_collect_kernel(DecodeParams p) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned int n_todo = __ldcg(p.todo_count);
+  for (unsigned int w = blockIdx.x * DWARPS + warp; w < n_todo; w += gridDim.x * DWARPS) {   // one listed item per warp and round
+    const unsigned int e = __ldcg(p.todo + w);
+    const int b = (int)(e / (unsigned int)p.items_per_image), item = (int)(e - (unsigned int)b * (unsigned int)p.items_per_image);
+    const int tb = __ldcg(p.tbin + b);
+    unsigned long long* cand = p.cand + (int64_t)b * CAND_CAP;
+    unsigned int* cnt = p.cand_count + b;
+    scan_item<T, SCAN_RH>(p, b, item, lane, [&](bool pk, float s, float, unsigned int flat) {
+      const bool take = pk && score_bin(s) >= tb;
+      if (__any_sync(0xffffffffu, take)) {
+        if (take) {
+          const unsigned int pos = atomicAdd(cnt, 1u);   // the compiler aggregates same-address atomics per warp
+          if (pos < (unsigned)CAND_CAP) cand[pos] = make_key(s, flat);
+        }
+      }
+    });
+  }
+}
+
+// Small batches (every item can have a warp of its own): no list, the warp of an item tests its bound itself.
+template <typename T>
+__global__ void __launch_bounds__(DNT, 3) decode_collect_direct_kernel(DecodeParams p, int ipw) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t total = (int64_t)p.nb * p.items_per_image;
   // a warp looks at `ipw` (<= 32) consecutive items at once (one per lane: coalesced reads of item_max) and re-scans
@@ -675,13 +721,13 @@ size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 
 }  // namespace
 
-static size_t decode_zero_bytes(int B) { return 2 * (size_t)B * sizeof(unsigned int); }   // cand_count + tbin
+static size_t decode_zero_bytes(int B) { return (2 * (size_t)B + 1) * sizeof(unsigned int); }   // cand_count + tbin + todo_count
 static size_t decode_items_per_image(int C, int H, int W) {
   return (size_t)C * ((H + SCAN_RH - 1) / SCAN_RH) * ((W + BAND - 1) / BAND);
 }
 size_t decode_workspace_bytes(int B, int C, int H, int W, int K) {
   (void)K;
-  return align256(decode_zero_bytes(B)) + 2 * align256((size_t)B * decode_items_per_image(C, H, W) * sizeof(unsigned int)) +
+  return align256(decode_zero_bytes(B)) + 3 * align256((size_t)B * decode_items_per_image(C, H, W) * sizeof(unsigned int)) +
          align256((size_t)B * CAND_CAP * sizeof(unsigned long long)) + 256;
 }
 
@@ -696,14 +742,18 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
   CPOLY_REQUIRE(a.workspace && a.workspace_bytes >= need, CPOLY_EWORKSPACE,
                 "decode workspace too small: need %zu bytes, have %zu", need, a.workspace_bytes);
   CPOLY_REQUIRE((reinterpret_cast<uintptr_t>(a.workspace) & 255) == 0, CPOLY_EINVAL, "decode workspace must be 256-byte aligned");
+  CPOLY_REQUIRE((uint64_t)a.B * decode_items_per_image(a.C, a.H, a.W) < 0xffffffffull, CPOLY_EINVAL, "too many scan items for 32-bit work-list entries");
   char* ws = reinterpret_cast<char*>(a.workspace);
   const size_t zero_bytes = decode_zero_bytes(a.B);
   p.cand_count = reinterpret_cast<unsigned int*>(ws);
   p.tbin = reinterpret_cast<int*>(p.cand_count + a.B);
+  p.todo_count = p.cand_count + 2 * a.B;
   ws += align256(zero_bytes);
   p.item_max = reinterpret_cast<unsigned int*>(ws);
   ws += align256((size_t)a.B * decode_items_per_image(a.C, a.H, a.W) * sizeof(unsigned int));
   p.item_cert = reinterpret_cast<unsigned int*>(ws);
+  ws += align256((size_t)a.B * decode_items_per_image(a.C, a.H, a.W) * sizeof(unsigned int));
+  p.todo = reinterpret_cast<unsigned int*>(ws);
   ws += align256((size_t)a.B * decode_items_per_image(a.C, a.H, a.W) * sizeof(unsigned int));
   p.cand = reinterpret_cast<unsigned long long*>(ws);
   CPOLY_CUDA_OK(cudaMemsetAsync(p.cand_count, 0, zero_bytes, stream));
@@ -717,6 +767,9 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
     p.b0 = 0;
     p.nb = a.B;
     const int64_t items = (int64_t)p.nb * p.items_per_image;
+    // every item gets a warp of its own in one resident wave? then the collection needs no work list
+    const bool use_list = items > (int64_t)3 * sms * DWARPS;
+    if (!use_list) p.todo = nullptr;
     int64_t ctas = (items + DWARPS - 1) / DWARPS;
     if (ctas > 3 * sms) ctas = 3 * sms;   // one resident wave: 24 warps per SM, each with (SCAN_RH + 2) x 512 B of loads in flight
     if (bf) decode_bound_kernel<__nv_bfloat16><<<(unsigned)ctas, DNT, 0, stream>>>(p);
@@ -725,13 +778,16 @@ int decode_launch(const cpoly_decode_args& a, cudaStream_t stream) {
     if (bf) decode_t0_kernel<__nv_bfloat16><<<(unsigned)a.B, DNT, 0, stream>>>(p);
     else decode_t0_kernel<float><<<(unsigned)a.B, DNT, 0, stream>>>(p);
     if (int rc = check_launch("decode_t0_kernel")) return rc;
-    const int64_t warps_wanted = (int64_t)3 * sms * DWARPS;
-    int ipw = (int)((items + warps_wanted - 1) / warps_wanted);
-    ipw = ipw < 1 ? 1 : (ipw > 32 ? 32 : ipw);
-    int64_t cctas = (items + (int64_t)ipw * DWARPS - 1) / ((int64_t)ipw * DWARPS);
-    if (cctas > 3 * sms) cctas = 3 * sms;
-    if (bf) decode_collect_kernel<__nv_bfloat16><<<(unsigned)cctas, DNT, 0, stream>>>(p, ipw);
-    else decode_collect_kernel<float><<<(unsigned)cctas, DNT, 0, stream>>>(p, ipw);
+    if (use_list) {
+      int64_t cctas = (items + DWARPS - 1) / DWARPS;      // at most one listed item per warp in the first round
+      if (cctas > 3 * sms) cctas = 3 * sms;
+      if (bf) decode_collect_kernel<__nv_bfloat16><<<(unsigned)cctas, DNT, 0, stream>>>(p);
+      else decode_collect_kernel<float><<<(unsigned)cctas, DNT, 0, stream>>>(p);
+    } else {
+      const int64_t cctas = (items + DWARPS - 1) / DWARPS;   // one item per warp
+      if (bf) decode_collect_direct_kernel<__nv_bfloat16><<<(unsigned)cctas, DNT, 0, stream>>>(p, 1);
+      else decode_collect_direct_kernel<float><<<(unsigned)cctas, DNT, 0, stream>>>(p, 1);
+    }
     if (int rc = check_launch("decode_collect_kernel")) return rc;
   }
   if (bf) decode_select_kernel<__nv_bfloat16><<<(unsigned)a.B, DNT, 0, stream>>>(p);
