@@ -291,7 +291,7 @@ def dcn_layer_sweep(torch, peaks, batches=(1, 4, 16), iters=5):
                 timing="median of %d, CUDA events, L2 flushed before every call" % iters, best=best, rows=rows)
 
 
-def train_step_bench(torch, dist, world, rank, steps=5, warmup=3, batch=16):
+def train_step_bench(torch, dist, world, rank, steps=12, warmup=5, batch=16):
     """BASELINE.json configs[3]: data-parallel polydet training step, 16 crops of 1024x512 per GPU, bf16 autocast, focal +
     polar L1 + polygon IoU loss (PolydetLoss l1+iou), Adam; the one exchange step is the bucketed NCCL gradient all-reduce."""
     from centerpoly_b200.harness.dla34 import PolydetDLA34, calibrate_random_init
